@@ -1,0 +1,80 @@
+// Shared device/host helpers for libkpms_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+
+#include "../../include/kpms_b200.h"
+
+#define KPMS_REQUIRE(cond, code) \
+  do {                           \
+    if (!(cond)) return (code);  \
+  } while (0)
+
+#define KPMS_CUDA(call)                      \
+  do {                                       \
+    cudaError_t e__ = (call);                \
+    if (e__ != cudaSuccess) return (int)e__; \
+  } while (0)
+
+// host-side count of kernel launches issued by this library (one bump per launch site)
+extern unsigned long long kpms_launch_counter;
+static inline int kpms_last_launch() {
+  ++kpms_launch_counter;
+  return (int)cudaGetLastError();
+}
+static inline bool kpms_aligned(const void* p, size_t a) { return ((uintptr_t)p % a) == 0; }
+static inline size_t kpms_round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+#define KPMS_PI 3.14159265358979323846
+#define KPMS_LOG_2PI 1.8378770664093454835606594728112
+
+// ---------------------------------------------------------------- warp helpers
+__device__ __forceinline__ float warp_max_f(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ long long warp_sum_ll(long long v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ---------------------------------------------------------------- Philox4x32-10
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int i = 0; i < 10; i++) {
+    uint32_t hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
+    uint32_t hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
+    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+    key.x += W0;
+    key.y += W1;
+  }
+  return ctr;
+}
+// [0,1) with 24 random bits (exactly representable in fp32)
+__device__ __forceinline__ float u01(uint32_t r) { return (float)(r >> 8) * (1.0f / 16777216.0f); }
+// (0,1]
+__device__ __forceinline__ float u01_open0(uint32_t r) {
+  return ((float)(r >> 8) + 1.0f) * (1.0f / 16777216.0f);
+}
+__device__ __forceinline__ float2 box_muller(uint32_t a, uint32_t b) {
+  float r = sqrtf(-2.0f * logf(u01_open0(a)));
+  float s, c;
+  sincospif(2.0f * u01(b), &s, &c);
+  return make_float2(r * c, r * s);
+}
+
+// R(-h)(y - v) in the first two coordinates (reference util.py:140-166)
+__device__ __forceinline__ void rot_inv(double c, double s, double y0, double y1, double& o0,
+                                        double& o1) {
+  o0 = c * y0 + s * y1;
+  o1 = -s * y0 + c * y1;
+}

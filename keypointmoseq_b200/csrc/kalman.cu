@@ -1,0 +1,791 @@
+// a5-a7: continuous latents — Kalman filter + backward sampler for the switching AR model.
+// Reference: gibbs.py:10-23 (resample_latents), kalman.py:80-156 (kalman_filter,
+// kalman_sample), util.py:214-230 (ar_to_lds).
+//
+// The reference conditions in covariance form with four dense n x n inversions and one
+// Cholesky per step (n = D*L).  This file computes the SAME Gaussian conditionals in
+// information form (prototype + proof of equivalence: tools/proto_kalman_info.py):
+//
+//   carry (Lam_p, eta_p) = (S_pred^-1, S_pred^-1 m_pred), start Lam = I/10, eta = 0 (gibbs.py:18)
+//   update   Lam_c = Lam_p + C^T R^-1 C         (touches only the newest D x D block, because
+//            eta_c = eta_p + C^T R^-1 (y - d)    C is zero outside the last D columns, util.py:228)
+//   smooth   Lam_s = Lam_c + A_z^T Qinv_z A_z  = inverse of kalman.py:131's S_cond
+//            Lam_s = M^T M (M lower, factored bottom-up)  =>  L = M^-1 is exactly
+//            cholesky(S_cond) of kalman.py:138 (lower, positive diagonal, unique)
+//   predict  V = L^T [A_z^T Qinv_z | eta_c - A_z^T Qinv_z B_z]
+//            Lam_p' = Qinv_z - V^T V,  eta_p' = Qinv_z B_z + V^T u            (Woodbury)
+//   backward x_t = L (L^T (eta_c + A_z^T Qinv_z (x_{t+1} - B_z)) + w_t)       (kalman.py:129-140)
+//
+// The companion structure (util.py:214-230) makes A^T Qinv = [100 E | F_D] with E a shifted
+// identity, so its first n-D columns of V are 100x columns of L^T that the triangular inverse
+// produces anyway.  Per step: one bottom-up Cholesky, one 41-column triangular solve, one
+// symmetric rank-n update — ~25k fp64 FMAs instead of the reference's ~250k flops.
+//
+// Kernels: per-state tables -> per-frame observation information (frame-parallel) ->
+// forward filter (CTA per session or per session chunk) -> backward sampler (warp per
+// session/chunk).  Masked steps leave the carry untouched and emit zeros; the final update
+// is unconditional (kalman.py:109-117,142-143).
+#include "common.cuh"
+#include "dispatch.cuh"
+
+template <int NN, int DD>
+struct KL {
+  static constexpr int NTRI = NN * (NN + 1) / 2;
+  static constexpr int NS = NN | 1;        // odd row stride (doubles) for W / Lp / Lfull
+  static constexpr int NV = (NN + 1) | 1;  // odd row stride for V
+  static constexpr int NC = NN + DD + 1;   // columns solved per step
+  static constexpr int NJ = DD * (DD + 1) / 2;
+  // per-state table
+  static constexpr int TAB_G = 0;
+  static constexpr int TAB_FD = TAB_G + NN * NN;
+  static constexpr int TAB_QI = TAB_FD + NN * DD;
+  static constexpr int TAB_F = TAB_QI + DD * DD;
+  static constexpr int TAB_QB = TAB_F + NN;
+  static constexpr int TAB_B = TAB_QB + DD;
+  static constexpr int TAB_SC = TAB_B + DD;  // c_z, logdet Q_
+  static constexpr int TAB_SIZE = (TAB_SC + 2 + 1) / 2 * 2;
+  // per-frame observation information
+  static constexpr int OBS_J = 0;
+  static constexpr int OBS_E = NJ;
+  static constexpr int OBS_C = NJ + DD;
+  static constexpr int OBS_SIZE = (OBS_C + 1 + 1) / 2 * 2;
+  // per-frame filter output
+  static constexpr int FW_L = 0;
+  static constexpr int FW_ETA = NTRI;
+  static constexpr int FW_SIZE = (NTRI + NN + 1) / 2 * 2;
+  static constexpr int BND = NTRI + NN;
+};
+
+struct KalWs {
+  double* tab;
+  double* obs;
+  double* fw;
+  double* llpart;
+  double* bndf;
+  double* bndx;
+  unsigned long long* errs;
+  int* tv;
+};
+
+__host__ __device__ static inline int kal_nchunks(int Tt, int chunk_len) {
+  if (chunk_len <= 0 || chunk_len >= Tt) return 1;
+  return (Tt + chunk_len - 1) / chunk_len;
+}
+
+static size_t kal_layout(int N, int T, int D, int L, int K, int chunk_len, void* base, KalWs* ws) {
+  const int NN = D * L, NTRI = NN * (NN + 1) / 2, NJ = D * (D + 1) / 2;
+  const int TAB = (NN * NN + NN * D + D * D + NN + D + D + 2 + 1) / 2 * 2;
+  const int OBS = (NJ + D + 1 + 1) / 2 * 2;
+  const int FW = (NTRI + NN + 1) / 2 * 2;
+  const int Tp = T - L + 1, Tt = Tp - 1;
+  const int nch = kal_nchunks(Tt, chunk_len);
+  size_t off = 0;
+  char* b = (char*)base;
+  auto take = [&](size_t bytes) {
+    size_t o = off;
+    off += kpms_round_up(bytes, 256);
+    return b ? (void*)(b + o) : nullptr;
+  };
+  void* p;
+  p = take((size_t)K * TAB * 8); if (ws) ws->tab = (double*)p;
+  p = take((size_t)N * Tp * OBS * 8); if (ws) ws->obs = (double*)p;
+  p = take((size_t)N * Tp * FW * 8); if (ws) ws->fw = (double*)p;
+  p = take((size_t)N * nch * 8); if (ws) ws->llpart = (double*)p;
+  p = take((size_t)N * nch * 2 * (NTRI + NN) * 8); if (ws) ws->bndf = (double*)p;
+  p = take((size_t)N * nch * 2 * NN * 8); if (ws) ws->bndx = (double*)p;
+  p = take(2 * 8); if (ws) ws->errs = (unsigned long long*)p;
+  p = take((size_t)N * 4); if (ws) ws->tv = (int*)p;
+  return off;
+}
+
+extern "C" size_t kpms_resample_latents_workspace_bytes(int N, int T, int k, int dk, int D, int L,
+                                                        int K, int chunk_len) {
+  if (N <= 0 || T <= L || D <= 0 || L <= 0 || K <= 0) return 0;
+  (void)k; (void)dk;
+  return kal_layout(N, T, D, L, K, chunk_len, nullptr, nullptr);
+}
+
+// ------------------------------------------------------------------ per-state tables
+template <int NN, int DD>
+__global__ void kalman_tables_kernel(const double* __restrict__ Ab, const double* __restrict__ Q,
+                                     double* __restrict__ tab) {
+  using Y = KL<NN, DD>;
+  const int k = blockIdx.x, lane = threadIdx.x;
+  __shared__ double Lq[DD * DD], Li[DD * DD], Qi[DD * DD], QA[DD * NN], bb[DD], qb[DD];
+  const double* Abk = Ab + (size_t)k * DD * (NN + 1);
+  const double* Qk = Q + (size_t)k * DD * DD;
+  double* t = tab + (size_t)k * Y::TAB_SIZE;
+  if (lane == 0) {
+    double ls = 0.0;
+    for (int j = 0; j < DD; j++) {
+      double s = Qk[j * DD + j];
+      for (int m = 0; m < j; m++) s -= Lq[j * DD + m] * Lq[j * DD + m];
+      const double d = sqrt(s);
+      Lq[j * DD + j] = d;
+      ls += log(d);
+      for (int i = j + 1; i < DD; i++) {
+        double v = Qk[i * DD + j];
+        for (int m = 0; m < j; m++) v -= Lq[i * DD + m] * Lq[j * DD + m];
+        Lq[i * DD + j] = v / d;
+      }
+    }
+    // Li = Lq^-1 (lower)
+    for (int c = 0; c < DD; c++) {
+      for (int i = 0; i < DD; i++) {
+        double v = (i == c) ? 1.0 : 0.0;
+        for (int m = c; m < i; m++) v -= Lq[i * DD + m] * Li[m * DD + c];
+        Li[i * DD + c] = (i < c) ? 0.0 : v / Lq[i * DD + i];
+      }
+    }
+    t[Y::TAB_SC + 1] = 2.0 * ls + (double)(NN - DD) * log(1e-2);
+  }
+  __syncwarp();
+  for (int e = lane; e < DD * DD; e += 32) {
+    const int a = e / DD, b = e % DD;
+    double s = 0.0;
+    for (int m = (a > b ? a : b); m < DD; m++) s += Li[m * DD + a] * Li[m * DD + b];
+    Qi[e] = s;
+    t[Y::TAB_QI + e] = s;
+  }
+  for (int a = lane; a < DD; a += 32) bb[a] = Abk[a * (NN + 1) + NN];
+  __syncwarp();
+  for (int e = lane; e < DD * NN; e += 32) {
+    const int a = e / NN, c = e % NN;
+    double s = 0.0;
+    for (int b = 0; b < DD; b++) s += Qi[a * DD + b] * Abk[b * (NN + 1) + c];
+    QA[e] = s;
+  }
+  for (int a = lane; a < DD; a += 32) {
+    double s = 0.0;
+    for (int b = 0; b < DD; b++) s += Qi[a * DD + b] * bb[b];
+    qb[a] = s;
+    t[Y::TAB_QB + a] = s;
+    t[Y::TAB_B + a] = bb[a];
+  }
+  __syncwarp();
+  for (int e = lane; e < NN * NN; e += 32) {
+    const int r = e / NN, c = e % NN;
+    double s = (r == c && r >= DD) ? 100.0 : 0.0;
+    for (int a = 0; a < DD; a++) s += Abk[a * (NN + 1) + r] * QA[a * NN + c];
+    t[Y::TAB_G + e] = s;
+  }
+  for (int e = lane; e < NN * DD; e += 32) {
+    const int r = e / DD, a = e % DD;
+    t[Y::TAB_FD + e] = QA[a * NN + r];
+  }
+  for (int r = lane; r < NN; r += 32) {
+    double s = 0.0;
+    for (int a = 0; a < DD; a++) s += QA[a * NN + r] * bb[a];
+    t[Y::TAB_F + r] = s;
+  }
+  if (lane == 0) {
+    double s = 0.0;
+    for (int a = 0; a < DD; a++) s += bb[a] * qb[a];
+    t[Y::TAB_SC + 0] = s;
+  }
+}
+
+// ------------------------------------------------------------------ observation information
+// One thread per LDS step tau (frame tau+L-1):  J = C_D^T R^-1 C_D (packed lower),
+// e = C_D^T R^-1 (ytild - d),  c = -1/2 sum_p [log(2 pi R_p) + (ytild_p - d_p)^2 / R_p],
+// ytild = R(-h)(Y - v) (util.py:140-166), R_p = s_kp sigmasq_kp repeated over dk (gibbs.py:17).
+template <int NN, int DD>
+__global__ void __launch_bounds__(128)
+    kalman_obs_kernel(const float* __restrict__ Y, const float* __restrict__ v,
+                      const float* __restrict__ h, const float* __restrict__ s,
+                      const double* __restrict__ Cdfull, const double* __restrict__ sigmasq,
+                      int N, int T, int k, int dk, int Lg, double* __restrict__ obs) {
+  using Y_ = KL<NN, DD>;
+  extern __shared__ __align__(16) double sm[];
+  double* Cs = sm;                          // (k*dk) x (DD+1)
+  double* CC = Cs + (size_t)k * dk * (DD + 1);  // k x NJ
+  double* sg = CC + (size_t)k * Y_::NJ;     // k
+  for (int i = threadIdx.x; i < k * dk * (DD + 1); i += blockDim.x) Cs[i] = Cdfull[i];
+  for (int i = threadIdx.x; i < k; i += blockDim.x) sg[i] = sigmasq[i];
+  __syncthreads();
+  for (int i = threadIdx.x; i < k * Y_::NJ; i += blockDim.x) {
+    const int kp = i / Y_::NJ, ab = i % Y_::NJ;
+    int a = 0;
+    while ((a + 1) * (a + 2) / 2 <= ab) a++;
+    const int b = ab - a * (a + 1) / 2;
+    double sacc = 0.0;
+    for (int dim = 0; dim < dk; dim++)
+      sacc += Cs[(size_t)(kp * dk + dim) * (DD + 1) + a] * Cs[(size_t)(kp * dk + dim) * (DD + 1) + b];
+    CC[i] = sacc;
+  }
+  __syncthreads();
+  const int Tp = T - Lg + 1;
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= (long long)N * Tp) return;
+  const int n = (int)(g / Tp), tau = (int)(g % Tp);
+  const size_t f = (size_t)n * T + tau + Lg - 1;
+  double J[Y_::NJ], ev[DD];
+#pragma unroll
+  for (int i = 0; i < Y_::NJ; i++) J[i] = 0.0;
+#pragma unroll
+  for (int i = 0; i < DD; i++) ev[i] = 0.0;
+  double ct = 0.0;
+  double sn, cs;
+  sincos((double)h[f], &sn, &cs);
+  const double v0 = (double)v[f * dk], v1 = (double)v[f * dk + 1];
+  const double v2 = (dk > 2) ? (double)v[f * dk + 2] : 0.0;
+  for (int kp = 0; kp < k; kp++) {
+    const double R = (double)s[f * k + kp] * sg[kp];
+    const double ri = 1.0 / R;
+    const float* Yf = Y + (f * k + kp) * dk;
+    double yt[3];
+    rot_inv(cs, sn, (double)Yf[0] - v0, (double)Yf[1] - v1, yt[0], yt[1]);
+    yt[2] = (dk > 2) ? (double)Yf[2] - v2 : 0.0;
+    double q = 0.0;
+    for (int dim = 0; dim < dk; dim++) {
+      const double* row = Cs + (size_t)(kp * dk + dim) * (DD + 1);
+      const double yy = yt[dim] - row[DD];
+      q = fma(yy, yy, q);
+      const double wgt = yy * ri;
+#pragma unroll
+      for (int a = 0; a < DD; a++) ev[a] = fma(row[a], wgt, ev[a]);
+    }
+    ct += -0.5 * (double)dk * (KPMS_LOG_2PI + log(R)) - 0.5 * q * ri;
+    const double* cc = CC + (size_t)kp * Y_::NJ;
+#pragma unroll
+    for (int i = 0; i < Y_::NJ; i++) J[i] = fma(cc[i], ri, J[i]);
+  }
+  double* o = obs + (size_t)g * Y_::OBS_SIZE;
+#pragma unroll
+  for (int i = 0; i < Y_::NJ; i++) o[Y_::OBS_J + i] = J[i];
+#pragma unroll
+  for (int i = 0; i < DD; i++) o[Y_::OBS_E + i] = ev[i];
+  o[Y_::OBS_C] = ct;
+}
+
+// number of unmasked transition steps per session (trailing padding assumed for chunking)
+__global__ void kalman_tv_kernel(const float* __restrict__ mask, int T, int Lg, int Tt,
+                                 int* __restrict__ tv) {
+  const int n = blockIdx.x;
+  __shared__ int cnt;
+  if (threadIdx.x == 0) cnt = 0;
+  __syncthreads();
+  int c = 0;
+  for (int t = threadIdx.x; t < Tt; t += blockDim.x) c += mask[(size_t)n * T + t + Lg - 1] > 0.0f;
+  atomicAdd(&cnt, c);
+  __syncthreads();
+  if (threadIdx.x == 0) tv[n] = cnt;
+}
+
+// Bottom-up Cholesky  W = M^T M  (M lower, stored in the lower triangle of W, row stride NS),
+// dinv[i] = 1 / M[i][i].  All threads of the CTA call this.
+template <int NN, int NS, int NT>
+__device__ __forceinline__ void rev_cholesky(double* W, double* dinv, const unsigned char* ti,
+                                             const unsigned char* tj) {
+  const int tid = threadIdx.x;
+#pragma unroll 1
+  for (int kk = NN - 1; kk >= 1; kk--) {
+    __syncthreads();
+    const double ip = 1.0 / W[kk * NS + kk];
+    const int cnt = kk * (kk + 1) / 2;
+    for (int e = tid; e < cnt; e += NT) {
+      const int i = ti[e], j = tj[e];
+      W[i * NS + j] = fma(-W[kk * NS + i] * ip, W[kk * NS + j], W[i * NS + j]);
+    }
+  }
+  __syncthreads();
+  if (tid < NN) dinv[tid] = 1.0 / sqrt(W[tid * NS + tid]);
+  __syncthreads();
+  for (int e = tid; e < NN * (NN + 1) / 2; e += NT) {
+    const int i = ti[e], j = tj[e];
+    W[i * NS + j] *= dinv[i];  // diagonal: W_ii / sqrt(W_ii) = sqrt(W_ii)
+  }
+  __syncthreads();
+}
+
+#define KAL_NT 128
+
+template <int NN, int DD>
+__global__ void __launch_bounds__(KAL_NT, 1)
+    kalman_forward_kernel(const float* __restrict__ mask, const int* __restrict__ z,
+                          const float* __restrict__ w_last, KalWs ws, int N, int T, int Lg,
+                          int chunk_len, int burn_in, int want_ll) {
+  using Y = KL<NN, DD>;
+  constexpr int NS = Y::NS, NV = Y::NV, NTRI = Y::NTRI, NC = Y::NC, NT = KAL_NT, OFF = NN - DD;
+  static_assert(NC <= NT && Y::OBS_SIZE <= NT, "thread count too small");
+  extern __shared__ __align__(16) double sm[];
+  double* W = sm;                   // NN*NS
+  double* Vm = W + NN * NS;         // NN*NV
+  double* Lp = Vm + NN * NV;        // NN*NS
+  double* eta_p = Lp + NN * NS;     // NN
+  double* eta_c = eta_p + NN;       // NN
+  double* dinv = eta_c + NN;        // NN
+  double* Gs = dinv + NN;           // NN*NN
+  double* FDs = Gs + NN * NN;       // NN*DD
+  double* Qis = FDs + NN * DD;      // DD*DD
+  double* fs = Qis + DD * DD;       // NN
+  double* qbs = fs + NN;            // DD
+  double* scs = qbs + DD;           // 2
+  double* obs_s = scs + 2;          // OBS_SIZE
+  unsigned char* ti = reinterpret_cast<unsigned char*>(obs_s + Y::OBS_SIZE);
+  unsigned char* tj = ti + NTRI;
+  const int tid = threadIdx.x;
+  const int Tp = T - Lg + 1, Tt = Tp - 1;
+  const int nch = kal_nchunks(Tt, chunk_len);
+  const int n = blockIdx.x / nch, c = blockIdx.x % nch;
+  const int t0 = (nch == 1) ? 0 : c * chunk_len;
+  const int t1 = (nch == 1) ? Tt : min(Tt, t0 + chunk_len);
+  int tb = 0;
+  if (c > 0) {
+    const int tvn = ws.tv[n];
+    tb = max(0, min(t0, tvn) - burn_in);
+  }
+  for (int e = tid; e < NTRI; e += NT) {
+    int i = 0;
+    while ((i + 1) * (i + 2) / 2 <= e) i++;
+    ti[e] = (unsigned char)i;
+    tj[e] = (unsigned char)(e - i * (i + 1) / 2);
+  }
+  // prior carry (gibbs.py:18: mu0 = 0, S0 = 10 I)
+  for (int e = tid; e < NN * NS; e += NT) Lp[e] = 0.0;
+  __syncthreads();
+  if (tid < NN) {
+    Lp[tid * NS + tid] = 0.1;
+    eta_p[tid] = 0.0;
+  }
+  double llacc = (c == 0) ? 0.5 * (double)NN * log(0.1) : 0.0;
+  const float* mk = mask + (size_t)n * T + (Lg - 1);
+  const int* zn = z + (size_t)n * Tt;
+  const double* obs_n = ws.obs + (size_t)n * Tp * Y::OBS_SIZE;
+  double* fw_n = ws.fw + (size_t)n * Tp * Y::FW_SIZE;
+  int cur_z = -1;
+  double obs_reg = 0.0;
+  if (tid < Y::OBS_SIZE && tb < Tp) obs_reg = obs_n[(size_t)tb * Y::OBS_SIZE + tid];
+  __syncthreads();
+
+  for (int tau = tb; tau < t1; tau++) {
+    if (tau == t0 && c > 0) {  // warmed-up carry at the chunk start, for verification
+      double* bd = ws.bndf + ((size_t)(n * nch + c) * 2 + 0) * Y::BND;
+      for (int e = tid; e < NTRI; e += NT) bd[e] = Lp[ti[e] * NS + tj[e]];
+      if (tid < NN) bd[NTRI + tid] = eta_p[tid];
+    }
+    const bool live = mk[tau] > 0.0f;
+    const double obs_cur = obs_reg;
+    if (tid < Y::OBS_SIZE) obs_reg = obs_n[(size_t)(tau + 1) * Y::OBS_SIZE + tid];  // tau+1 <= Tp-1
+    if (!live) continue;  // kalman.py:109-111: carry unchanged (uniform branch)
+    const bool store = tau >= t0;
+    const int zt = zn[tau];
+    if (zt != cur_z) {
+      const double* tb_ = ws.tab + (size_t)zt * Y::TAB_SIZE;
+      for (int e = tid; e < NN * NN; e += NT) Gs[e] = tb_[Y::TAB_G + e];
+      for (int e = tid; e < NN * DD; e += NT) FDs[e] = tb_[Y::TAB_FD + e];
+      for (int e = tid; e < DD * DD; e += NT) Qis[e] = tb_[Y::TAB_QI + e];
+      if (tid < NN) fs[tid] = tb_[Y::TAB_F + tid];
+      if (tid < DD) qbs[tid] = tb_[Y::TAB_QB + tid];
+      if (tid < 2) scs[tid] = tb_[Y::TAB_SC + tid];
+      cur_z = zt;
+    }
+    if (tid < Y::OBS_SIZE) obs_s[tid] = obs_cur;
+    __syncthreads();
+    // S1: Lam_s = Lam_p + C^T R^-1 C + A^T Qinv A (lower triangle), eta_c
+    for (int e = tid; e < NTRI; e += NT) {
+      const int i = ti[e], j = tj[e];
+      double v = Lp[i * NS + j] + Gs[i * NN + j];
+      if (j >= OFF) v += obs_s[Y::OBS_J + (i - OFF) * (i - OFF + 1) / 2 + (j - OFF)];
+      W[i * NS + j] = v;
+    }
+    if (tid < NN) {
+      const double ec = eta_p[tid] + ((tid >= OFF) ? obs_s[Y::OBS_E + tid - OFF] : 0.0);
+      eta_c[tid] = ec;
+      if (store) fw_n[(size_t)tau * Y::FW_SIZE + Y::FW_ETA + tid] = ec;
+    }
+    // S2
+    rev_cholesky<NN, NS, NT>(W, dinv, ti, tj);
+    // S3: solve M^T X = [I | F_D | eta_c - f]; thread c owns one column in registers
+    if (tid < NC) {
+      double col[NN];
+      int rstart = NN - 1;
+      if (tid < NN) {
+#pragma unroll
+        for (int r = 0; r < NN; r++) col[r] = (r == tid) ? 1.0 : 0.0;
+        rstart = tid;
+      } else if (tid < NN + DD) {
+#pragma unroll
+        for (int r = 0; r < NN; r++) col[r] = FDs[r * DD + (tid - NN)];
+      } else {
+#pragma unroll
+        for (int r = 0; r < NN; r++) col[r] = eta_c[r] - fs[r];
+      }
+#pragma unroll
+      for (int r = NN - 1; r >= 0; r--) {
+        if (r <= rstart) {
+          const double vv = col[r] * dinv[r];
+          col[r] = vv;
+#pragma unroll
+          for (int q = 0; q < r; q++) col[q] = fma(-W[r * NS + q], vv, col[q]);
+        }
+      }
+      if (tid < NN) {
+        if (store) {  // row tid of L = cholesky(S_cond): L[tid][r] = (M^-T)[r][tid]
+          double* lrow = fw_n + (size_t)tau * Y::FW_SIZE + Y::FW_L + tid * (tid + 1) / 2;
+#pragma unroll
+          for (int r = 0; r < NN; r++)
+            if (r <= tid) lrow[r] = col[r];
+        }
+        if (tid >= DD) {
+#pragma unroll
+          for (int r = 0; r < NN; r++) Vm[r * NV + (tid - DD)] = 100.0 * col[r];
+        }
+      } else if (tid < NN + DD) {
+#pragma unroll
+        for (int r = 0; r < NN; r++) Vm[r * NV + OFF + (tid - NN)] = col[r];
+      } else {
+#pragma unroll
+        for (int r = 0; r < NN; r++) Vm[r * NV + NN] = col[r];
+      }
+    }
+    __syncthreads();
+    // S4: Lam_p' = Qinv_ - V^T V,  eta_p' = Qinv_ B_ + V^T u
+    for (int e = tid; e < NTRI + NN; e += NT) {
+      if (e < NTRI) {
+        const int a = ti[e], b = tj[e];          // a >= b
+        const int rmax = (b < OFF) ? DD + b : NN - 1;  // column b of V is zero below this row
+        double acc = 0.0;
+        for (int r = 0; r <= rmax; r++) acc = fma(Vm[r * NV + a], Vm[r * NV + b], acc);
+        double qv;
+        if (a < OFF) qv = (a == b) ? 100.0 : 0.0;
+        else qv = (b >= OFF) ? Qis[(a - OFF) * DD + (b - OFF)] : 0.0;
+        Lp[a * NS + b] = qv - acc;
+      } else {
+        const int a = e - NTRI;
+        const int rmax = (a < OFF) ? DD + a : NN - 1;
+        double acc = 0.0;
+        for (int r = 0; r <= rmax; r++) acc = fma(Vm[r * NV + a], Vm[r * NV + NN], acc);
+        eta_p[a] = ((a >= OFF) ? qbs[a - OFF] : 0.0) + acc;
+      }
+    }
+    if (want_ll && store && tid == NT - 1) {
+      double uu = 0.0, pd = 1.0;
+      for (int r = 0; r < NN; r++) {
+        uu = fma(Vm[r * NV + NN], Vm[r * NV + NN], uu);
+        pd *= dinv[r];
+      }
+      llacc += obs_s[Y::OBS_C] - 0.5 * scs[1] + log(pd) + 0.5 * (uu - scs[0]);
+    }
+    __syncthreads();
+  }
+  // carry at the chunk end, for verification against the next chunk's warmed-up start
+  if (nch > 1) {
+    double* bd = ws.bndf + ((size_t)(n * nch + c) * 2 + 1) * Y::BND;
+    for (int e = tid; e < NTRI; e += NT) bd[e] = Lp[ti[e] * NS + tj[e]];
+    if (tid < NN) bd[NTRI + tid] = eta_p[tid];
+  }
+  if (c == nch - 1) {
+    // unconditional final update (kalman.py:117) and the draw of the last state (kalman.py:150)
+    if (tid < Y::OBS_SIZE) obs_s[tid] = obs_n[(size_t)(Tp - 1) * Y::OBS_SIZE + tid];
+    __syncthreads();
+    for (int e = tid; e < NTRI; e += NT) {
+      const int i = ti[e], j = tj[e];
+      double v = Lp[i * NS + j];
+      if (j >= OFF) v += obs_s[Y::OBS_J + (i - OFF) * (i - OFF + 1) / 2 + (j - OFF)];
+      W[i * NS + j] = v;
+    }
+    if (tid < NN) eta_c[tid] = eta_p[tid] + ((tid >= OFF) ? obs_s[Y::OBS_E + tid - OFF] : 0.0);
+    rev_cholesky<NN, NS, NT>(W, dinv, ti, tj);
+    if (tid == 0) {
+      // runs once per session: serial, shared-memory scratch (column NN of Vm), no unrolling
+      double* col = Vm + NN;  // element r at col[r * NV]
+      double tt = 0.0, pd = 1.0;
+#pragma unroll 1
+      for (int r = 0; r < NN; r++) col[r * NV] = eta_c[r];
+#pragma unroll 1
+      for (int r = NN - 1; r >= 0; r--) {  // t = M^-T eta_c
+        const double vv = col[r * NV] * dinv[r];
+        col[r * NV] = vv;
+        tt = fma(vv, vv, tt);
+        pd *= dinv[r];
+#pragma unroll 1
+        for (int q = 0; q < r; q++) col[q * NV] = fma(-W[r * NS + q], vv, col[q * NV]);
+      }
+#pragma unroll 1
+      for (int r = 0; r < NN; r++) col[r * NV] += (double)w_last[(size_t)n * NN + r];
+      double* xl = fw_n + (size_t)(Tp - 1) * Y::FW_SIZE;
+#pragma unroll 1
+      for (int r = 0; r < NN; r++) {  // x = M^-1 (t + w): forward substitution, column sweep
+        const double xv = col[r * NV] * dinv[r];
+        xl[r] = xv;
+#pragma unroll 1
+        for (int q = r + 1; q < NN; q++) col[q * NV] = fma(-W[q * NS + r], xv, col[q * NV]);
+      }
+      ws.llpart[(size_t)n * nch + c] = obs_s[Y::OBS_C] + log(pd) + 0.5 * tt;
+    }
+    // the running sum lives in thread NT-1
+    __syncthreads();
+    if (tid == NT - 1) ws.llpart[(size_t)n * nch + c] += llacc;
+  } else if (tid == NT - 1) {
+    ws.llpart[(size_t)n * nch + c] = llacc;
+  }
+}
+
+// ------------------------------------------------------------------ backward sampler
+// One warp per session (or session chunk).  x_t = L (L^T h + w_t),
+// h = eta_c + A^T Qinv (x_{t+1} - B) with A^T Qinv = [100 E | F_D] (see file header).
+template <int NN, int DD>
+__global__ void __launch_bounds__(32)
+    kalman_backward_kernel(const float* __restrict__ mask, const int* __restrict__ z,
+                           const float* __restrict__ w, KalWs ws, int N, int T, int Lg,
+                           int chunk_len, int burn_in, float* __restrict__ x_out) {
+  using Y = KL<NN, DD>;
+  constexpr int NS = Y::NS, NTRI = Y::NTRI, OFF = NN - DD;
+  constexpr int PRE = (Y::FW_SIZE + 31) / 32;
+  extern __shared__ __align__(16) double sm[];
+  double* Lf = sm;             // NN*NS (lower)
+  double* hs = Lf + NN * NS;   // NN
+  double* ys = hs + NN;        // NN
+  double* xs = ys + NN;        // NN
+  double* etas = xs + NN;      // NN
+  double* FDs = etas + NN;     // NN*DD
+  double* bs = FDs + NN * DD;  // DD
+  unsigned char* ti = reinterpret_cast<unsigned char*>(bs + DD);
+  unsigned char* tj = ti + NTRI;
+  const int lane = threadIdx.x;
+  const int Tp = T - Lg + 1, Tt = Tp - 1;
+  const int nch = kal_nchunks(Tt, chunk_len);
+  const int n = blockIdx.x / nch, c = blockIdx.x % nch;
+  const int t0 = (nch == 1) ? 0 : c * chunk_len;
+  const int t1 = (nch == 1) ? Tt : min(Tt, t0 + chunk_len);
+  for (int e = lane; e < NTRI; e += 32) {
+    int i = 0;
+    while ((i + 1) * (i + 2) / 2 <= e) i++;
+    ti[e] = (unsigned char)i;
+    tj[e] = (unsigned char)(e - i * (i + 1) / 2);
+  }
+  for (int e = lane; e < NN * NS; e += 32) Lf[e] = 0.0;
+  const float* mk = mask + (size_t)n * T + (Lg - 1);
+  const int* zn = z + (size_t)n * Tt;
+  const double* fw_n = ws.fw + (size_t)n * Tp * Y::FW_SIZE;
+  const float* w_n = w + (size_t)n * Tt * NN;
+  float* xo = x_out + (size_t)n * T * DD;
+  const double* xlast = fw_n + (size_t)(Tp - 1) * Y::FW_SIZE;
+  int ts = t1;
+  bool exact_start = true;
+  if (c < nch - 1) {
+    ts = min(Tt, t1 + burn_in);
+    exact_start = (ts == Tt) || !(mk[ts] > 0.0f);  // trailing padding: x is still x_last there
+  }
+  if (lane < NN) xs[lane] = exact_start ? xlast[lane] : 0.0;
+  if (c == nch - 1 && lane < DD) xo[(size_t)(T - 1) * DD + lane] = (float)xlast[OFF + lane];
+  __syncwarp();
+  int cur_z = -1;
+  double pre[PRE];
+  float wpre = 0.0f;
+  {
+    const int tau = ts - 1;
+    if (tau >= t0) {
+#pragma unroll
+      for (int i = 0; i < PRE; i++) {
+        const int e = lane + 32 * i;
+        pre[i] = (e < Y::FW_SIZE) ? fw_n[(size_t)tau * Y::FW_SIZE + e] : 0.0;
+      }
+      if (lane < NN) wpre = w_n[(size_t)tau * NN + lane];
+    }
+  }
+  for (int tau = ts - 1; tau >= t0; tau--) {
+    if (tau == t1 - 1 && c < nch - 1 && lane < NN)
+      ws.bndx[((size_t)(n * nch + c) * 2 + 0) * NN + lane] = xs[lane];
+    const bool live = mk[tau] > 0.0f;
+    // unpack this step's factor, then prefetch the next step's
+    if (live) {
+#pragma unroll
+      for (int i = 0; i < PRE; i++) {
+        const int e = lane + 32 * i;
+        if (e < NTRI) Lf[ti[e] * NS + tj[e]] = pre[i];
+        else if (e < NTRI + NN) etas[e - NTRI] = pre[i];
+      }
+    }
+    const float wcur = wpre;
+    if (tau - 1 >= t0) {
+#pragma unroll
+      for (int i = 0; i < PRE; i++) {
+        const int e = lane + 32 * i;
+        pre[i] = (e < Y::FW_SIZE) ? fw_n[(size_t)(tau - 1) * Y::FW_SIZE + e] : 0.0;
+      }
+      if (lane < NN) wpre = w_n[(size_t)(tau - 1) * NN + lane];
+    }
+    if (live) {
+      const int zt = zn[tau];
+      if (zt != cur_z) {
+        const double* tb_ = ws.tab + (size_t)zt * Y::TAB_SIZE;
+        for (int e = lane; e < NN * DD; e += 32) FDs[e] = tb_[Y::TAB_FD + e];
+        if (lane < DD) bs[lane] = tb_[Y::TAB_B + lane];
+        cur_z = zt;
+      }
+      __syncwarp();
+      if (lane < NN) {
+        double hh = etas[lane] + ((lane >= DD) ? 100.0 * xs[lane - DD] : 0.0);
+#pragma unroll
+        for (int a = 0; a < DD; a++) hh = fma(FDs[lane * DD + a], xs[OFF + a] - bs[a], hh);
+        hs[lane] = hh;
+      }
+      __syncwarp();
+      if (lane < NN) {
+        double t0a = 0.0, t1a = 0.0;
+#pragma unroll
+        for (int q = 0; q < NN; q += 2) {
+          if (q >= lane) t0a = fma(Lf[q * NS + lane], hs[q], t0a);
+          if (q + 1 < NN && q + 1 >= lane) t1a = fma(Lf[(q + 1) * NS + lane], hs[q + 1], t1a);
+        }
+        ys[lane] = (t0a + t1a) + (double)wcur;
+      }
+      __syncwarp();
+      double xn = 0.0;
+      if (lane < NN) {
+        double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+        for (int q = 0; q < NN; q += 2) {
+          if (q <= lane) a0 = fma(Lf[lane * NS + q], ys[q], a0);
+          if (q + 1 < NN && q + 1 <= lane) a1 = fma(Lf[lane * NS + q + 1], ys[q + 1], a1);
+        }
+        xn = a0 + a1;
+        xs[lane] = xn;
+      }
+      __syncwarp();
+    }
+    if (tau < t1) {
+      // gibbs.py:22: x[t] = newest block of LDS state t-L+1; x[0..L-2] = older blocks of state 0
+      if (lane < DD) xo[(size_t)(tau + Lg - 1) * DD + lane] = live ? (float)xs[OFF + lane] : 0.0f;
+      if (tau == 0 && lane < OFF) xo[lane] = live ? (float)xs[lane] : 0.0f;
+    }
+  }
+  if (nch > 1 && c > 0 && lane < NN) ws.bndx[((size_t)(n * nch + c) * 2 + 1) * NN + lane] = xs[lane];
+}
+
+// loglik[n] = sum of chunk partials (fixed order); boundary mismatch of chunked mode.
+__global__ void kalman_finish_kernel(KalWs ws, int nch, int BND, int NN, double* __restrict__ loglik,
+                                     unsigned long long* __restrict__ err_bits) {
+  const int n = blockIdx.x, tid = threadIdx.x;
+  if (tid == 0 && loglik) {
+    double s = 0.0;
+    for (int c = 0; c < nch; c++) s += ws.llpart[(size_t)n * nch + c];
+    loglik[n] = s;
+  }
+  if (!err_bits || nch < 2) return;
+  __shared__ double red[2][32];
+  for (int which = 0; which < 2; which++) {
+    double worst = 0.0;
+    for (int c = 0; c + 1 < nch; c++) {
+      const double *a, *b;
+      int len;
+      if (which == 0) {  // filter: end carry of chunk c vs warmed-up start of chunk c+1
+        a = ws.bndf + ((size_t)(n * nch + c) * 2 + 1) * BND;
+        b = ws.bndf + ((size_t)(n * nch + c + 1) * 2 + 0) * BND;
+        len = BND;
+      } else {           // sampler: warmed-up x of chunk c vs x at the start of chunk c+1
+        a = ws.bndx + ((size_t)(n * nch + c + 1) * 2 + 1) * NN;
+        b = ws.bndx + ((size_t)(n * nch + c) * 2 + 0) * NN;
+        len = NN;
+      }
+      double md = 0.0, ma = 0.0;
+      for (int e = tid; e < len; e += blockDim.x) {
+        md = fmax(md, fabs(a[e] - b[e]));
+        ma = fmax(ma, fabs(a[e]));
+      }
+      for (int o = 16; o > 0; o >>= 1) {
+        md = fmax(md, __shfl_xor_sync(0xffffffffu, md, o));
+        ma = fmax(ma, __shfl_xor_sync(0xffffffffu, ma, o));
+      }
+      __syncthreads();
+      if ((tid & 31) == 0) {
+        red[0][tid >> 5] = md;
+        red[1][tid >> 5] = ma;
+      }
+      __syncthreads();
+      if (tid == 0) {
+        double d = 0.0, m = 0.0;
+        for (int q = 0; q < (int)(blockDim.x >> 5); q++) {
+          d = fmax(d, red[0][q]);
+          m = fmax(m, red[1][q]);
+        }
+        worst = fmax(worst, d / (m + 1e-300));
+      }
+    }
+    if (tid == 0) atomicMax(&err_bits[which], (unsigned long long)__double_as_longlong(worst));
+  }
+}
+
+template <int NN, int DD>
+static int launch_latents(const float* Y, const float* mask, const float* v, const float* h,
+                          const int* z, const float* s, const double* Cdfull, const double* sigmasq,
+                          const double* Ab, const double* Q, const float* w, const float* w_last,
+                          int N, int T, int k, int dk, int Lg, int K, int chunk_len, int burn_in,
+                          float* x, double* loglik, double* boundary_err, KalWs ws,
+                          cudaStream_t st) {
+  using YL = KL<NN, DD>;
+  const int Tp = T - Lg + 1, Tt = Tp - 1;
+  const int nch = kal_nchunks(Tt, chunk_len);
+  kalman_tables_kernel<NN, DD><<<K, 32, 0, st>>>(Ab, Q, ws.tab);
+  int rc = kpms_last_launch();
+  if (rc) return rc;
+  {
+    const size_t smem = ((size_t)k * dk * (DD + 1) + (size_t)k * YL::NJ + k) * sizeof(double);
+    auto kern = kalman_obs_kernel<NN, DD>;
+    KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const long long tot = (long long)N * Tp;
+    kern<<<(unsigned)((tot + 127) / 128), 128, smem, st>>>(Y, v, h, s, Cdfull, sigmasq, N, T, k, dk,
+                                                          Lg, ws.obs);
+    rc = kpms_last_launch();
+    if (rc) return rc;
+  }
+  if (nch > 1) {
+    kalman_tv_kernel<<<N, 256, 0, st>>>(mask, T, Lg, Tt, ws.tv);
+    rc = kpms_last_launch();
+    if (rc) return rc;
+  }
+  {
+    const size_t smem = (size_t)(2 * NN * YL::NS + NN * YL::NV + 3 * NN + NN * NN + NN * DD + DD * DD +
+                                 NN + DD + 2 + YL::OBS_SIZE) * sizeof(double) + 2 * YL::NTRI;
+    auto kern = kalman_forward_kernel<NN, DD>;
+    KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<N * nch, KAL_NT, smem, st>>>(mask, z, w_last, ws, N, T, Lg, chunk_len, burn_in,
+                                        loglik != nullptr);
+    rc = kpms_last_launch();
+    if (rc) return rc;
+  }
+  {
+    const size_t smem = (size_t)(NN * YL::NS + 4 * NN + NN * DD + DD) * sizeof(double) + 2 * YL::NTRI;
+    auto kern = kalman_backward_kernel<NN, DD>;
+    KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<N * nch, 32, smem, st>>>(mask, z, w, ws, N, T, Lg, chunk_len, burn_in, x);
+    rc = kpms_last_launch();
+    if (rc) return rc;
+  }
+  if (boundary_err) KPMS_CUDA(cudaMemsetAsync(boundary_err, 0, 2 * sizeof(double), st));
+  if (loglik || (boundary_err && nch > 1)) {
+    kalman_finish_kernel<<<N, 128, 0, st>>>(ws, nch, YL::BND, NN, loglik,
+                                            (unsigned long long*)boundary_err);
+    rc = kpms_last_launch();
+  }
+  return rc;
+}
+
+extern "C" int kpms_resample_latents(const float* Y, const float* mask, const float* v,
+                                     const float* h, const int32_t* z, const float* s,
+                                     const double* Cdfull, const double* sigmasq, const double* Ab,
+                                     const double* Q, const float* w, const float* w_last, int N,
+                                     int T, int k, int dk, int D, int L, int K, int chunk_len,
+                                     int burn_in, float* x, double* loglik, double* boundary_err,
+                                     void* workspace, size_t workspace_bytes, void* stream) {
+  KPMS_REQUIRE(Y && mask && v && h && z && s && Cdfull && sigmasq && Ab && Q && w && w_last && x &&
+                   workspace,
+               KPMS_ERR_NULL);
+  KPMS_REQUIRE(N > 0 && T > L && k > 0 && D > 0 && L > 0 && K > 0, KPMS_ERR_SHAPE);
+  KPMS_REQUIRE(dk >= 2 && dk <= 3 && kpms_dl_supported(D, L) && k <= 64, KPMS_ERR_UNSUPPORTED);
+  KPMS_REQUIRE(chunk_len <= 0 || burn_in >= 0, KPMS_ERR_SHAPE);
+  KalWs ws;
+  const size_t need = kal_layout(N, T, D, L, K, chunk_len, workspace, &ws);
+  KPMS_REQUIRE(kpms_aligned(workspace, 256) && workspace_bytes >= need, KPMS_ERR_WORKSPACE);
+  cudaStream_t st = (cudaStream_t)stream;
+#define KPMS_X(d, l)                                                                              \
+  if (D == d && L == l)                                                                           \
+    return launch_latents<d * l, d>(Y, mask, v, h, z, s, Cdfull, sigmasq, Ab, Q, w, w_last, N, T, \
+                                    k, dk, L, K, chunk_len, burn_in, x, loglik, boundary_err, ws, \
+                                    st);
+  KPMS_FOR_EACH_DL(KPMS_X)
+#undef KPMS_X
+  return KPMS_ERR_UNSUPPORTED;
+}

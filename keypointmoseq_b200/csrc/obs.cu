@@ -1,0 +1,514 @@
+// Frame-parallel observation passes and the location sampler.
+//   a13 obs-variance statistic  (gibbs.py:84-94)
+//   a14 scales                  (gibbs.py:117-125, distributions.py:8-15)
+//   a15 heading                 (gibbs.py:25-35, util.py:66-82, distributions.py:5-6)
+//   a16 location                (gibbs.py:38-54 + kalman.py:80-156 specialised to the
+//                                isotropic A=I, C=I, Q=sigmasq_loc*I, R=gammasq*I case)
+// All share the prologue  Ybar = Cdfull [x;1]  (Cdfull = kron(Gamma,I) Cd, gibbs.py:14,29)
+// and the rigid transform of util.py:112-166.  Arithmetic is fp64; storage fp32.
+#include "common.cuh"
+
+#define OBS_XMAX 16   // latent dim D <= 16
+#define OBS_KPMAX 32  // keypoints k <= 32
+#define OBS_DKMAX 3   // keypoint dim dk in {2,3}
+
+struct ObsDims {
+  int N, T, k, dk, D;
+};
+
+static inline int obs_check(int N, int T, int k, int dk, int D) {
+  if (N <= 0 || T <= 0 || k <= 0 || D <= 0) return KPMS_ERR_SHAPE;
+  if (dk < 2 || dk > OBS_DKMAX || k > OBS_KPMAX || D > OBS_XMAX) return KPMS_ERR_UNSUPPORTED;
+  return KPMS_OK;
+}
+
+// shared-memory copy of Cdfull (k*dk x (D+1)) and per-keypoint constants
+__device__ __forceinline__ void load_cd(const double* __restrict__ Cdfull, int rows, int D,
+                                        double* Cs) {
+  for (int i = threadIdx.x; i < rows * (D + 1); i += blockDim.x) Cs[i] = Cdfull[i];
+}
+
+__device__ __forceinline__ void load_x(const float* __restrict__ x, size_t frame, int D,
+                                       double (&xr)[OBS_XMAX]) {
+#pragma unroll
+  for (int d = 0; d < OBS_XMAX; d++) xr[d] = (d < D) ? (double)x[frame * D + d] : 0.0;
+}
+
+// Ybar for one keypoint: yb[dim] = Cs[(kp*dk+dim)] . [x;1]
+__device__ __forceinline__ void ybar_kp(const double* Cs, int kp, int dk, int D,
+                                        const double (&xr)[OBS_XMAX], double (&yb)[OBS_DKMAX]) {
+#pragma unroll
+  for (int dim = 0; dim < OBS_DKMAX; dim++) {
+    yb[dim] = 0.0;
+    if (dim < dk) {
+      const double* row = Cs + (size_t)(kp * dk + dim) * (D + 1);
+      double a = row[D];
+#pragma unroll
+      for (int d = 0; d < OBS_XMAX; d++)
+        if (d < D) a = fma(row[d], xr[d], a);
+      yb[dim] = a;
+    }
+  }
+}
+
+// Ytild = R(-h)(Y - v) for one keypoint
+__device__ __forceinline__ void ytild_kp(const float* __restrict__ Yf, const double (&vv)[OBS_DKMAX],
+                                         double c, double s, int dk, double (&yt)[OBS_DKMAX]) {
+  double d0 = (double)Yf[0] - vv[0], d1 = (double)Yf[1] - vv[1];
+  rot_inv(c, s, d0, d1, yt[0], yt[1]);
+  yt[2] = (dk > 2) ? (double)Yf[2] - vv[2] : 0.0;
+}
+
+// ======================================================================== a13
+#define OV_BLOCKS (148 * 2)
+#define OV_THREADS 256
+
+extern "C" size_t kpms_obs_variance_stats_workspace_bytes(int N, int T, int k) {
+  if (N <= 0 || T <= 0 || k <= 0) return 0;
+  return kpms_round_up((size_t)OV_BLOCKS * (OBS_KPMAX + 1) * sizeof(double), 256);
+}
+
+__global__ void __launch_bounds__(OV_THREADS)
+    obs_variance_kernel(const float* __restrict__ Y, const float* __restrict__ mask,
+                        const float* __restrict__ v, const float* __restrict__ h,
+                        const float* __restrict__ x, const float* __restrict__ s,
+                        const double* __restrict__ Cdfull, ObsDims dm,
+                        double* __restrict__ partial) {
+  extern __shared__ __align__(16) double Cs[];
+  __shared__ double red[OV_THREADS / 32];
+  const int k = dm.k, dk = dm.dk, D = dm.D;
+  load_cd(Cdfull, k * dk, D, Cs);
+  __syncthreads();
+  double acc[OBS_KPMAX + 1];
+#pragma unroll
+  for (int i = 0; i <= OBS_KPMAX; i++) acc[i] = 0.0;
+  const long long frames = (long long)dm.N * dm.T;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < frames;
+       g += (long long)gridDim.x * blockDim.x) {
+    const double m = (double)mask[g];
+    if (m > 0.0) {
+      double xr[OBS_XMAX];
+      load_x(x, (size_t)g, D, xr);
+      double sn, cs;
+      sincos((double)h[g], &sn, &cs);
+      double vv[OBS_DKMAX];
+#pragma unroll
+      for (int dim = 0; dim < OBS_DKMAX; dim++) vv[dim] = (dim < dk) ? (double)v[g * dk + dim] : 0.0;
+#pragma unroll
+      for (int kp = 0; kp < OBS_KPMAX; kp++) {
+        if (kp < k) {
+          double yb[OBS_DKMAX], yt[OBS_DKMAX];
+          ybar_kp(Cs, kp, dk, D, xr, yb);
+          ytild_kp(Y + ((size_t)g * k + kp) * dk, vv, cs, sn, dk, yt);
+          double e = 0.0;
+#pragma unroll
+          for (int dim = 0; dim < OBS_DKMAX; dim++) {
+            const double r = yt[dim] - yb[dim];
+            e = fma(r, r, e);
+          }
+          acc[kp] += m * e / (double)s[(size_t)g * k + kp];
+        }
+      }
+      acc[OBS_KPMAX] += m;
+    }
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int i = 0; i <= OBS_KPMAX; i++) {
+    if (i < k || i == OBS_KPMAX) {
+      double w = warp_sum_d(acc[i]);
+      __syncthreads();
+      if (lane == 0) red[warp] = w;
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int q = 0; q < OV_THREADS / 32; q++) t += red[q];
+        partial[(size_t)blockIdx.x * (OBS_KPMAX + 1) + i] = t;
+      }
+    }
+  }
+}
+
+__global__ void obs_variance_reduce_kernel(const double* __restrict__ partial, int blocks, int k,
+                                           double* __restrict__ S_y, double* __restrict__ msum) {
+  const int i = threadIdx.x;
+  if (i < k) {
+    double t = 0.0;
+    for (int b = 0; b < blocks; b++) t += partial[(size_t)b * (OBS_KPMAX + 1) + i];
+    S_y[i] = t;
+  } else if (i == OBS_KPMAX) {
+    double t = 0.0;
+    for (int b = 0; b < blocks; b++) t += partial[(size_t)b * (OBS_KPMAX + 1) + OBS_KPMAX];
+    msum[0] = t;
+  }
+}
+
+extern "C" int kpms_obs_variance_stats(const float* Y, const float* mask, const float* v,
+                                       const float* h, const float* x, const float* s,
+                                       const double* Cdfull, int N, int T, int k, int dk, int D,
+                                       double* S_y, double* mask_sum, void* workspace,
+                                       size_t workspace_bytes, void* stream) {
+  KPMS_REQUIRE(Y && mask && v && h && x && s && Cdfull && S_y && mask_sum && workspace,
+               KPMS_ERR_NULL);
+  int rc = obs_check(N, T, k, dk, D);
+  if (rc) return rc;
+  KPMS_REQUIRE(kpms_aligned(workspace, 256) &&
+                   workspace_bytes >= kpms_obs_variance_stats_workspace_bytes(N, T, k),
+               KPMS_ERR_WORKSPACE);
+  cudaStream_t st = (cudaStream_t)stream;
+  ObsDims dm{N, T, k, dk, D};
+  const size_t smem = (size_t)k * dk * (D + 1) * sizeof(double);
+  obs_variance_kernel<<<OV_BLOCKS, OV_THREADS, smem, st>>>(Y, mask, v, h, x, s, Cdfull, dm,
+                                                          (double*)workspace);
+  rc = kpms_last_launch();
+  if (rc) return rc;
+  obs_variance_reduce_kernel<<<1, OBS_KPMAX + 1, 0, st>>>((const double*)workspace, OV_BLOCKS, k,
+                                                         S_y, mask_sum);
+  return kpms_last_launch();
+}
+
+// ======================================================================== a14
+__global__ void __launch_bounds__(256)
+    scales_kernel(const float* __restrict__ Y, const float* __restrict__ v,
+                  const float* __restrict__ h, const float* __restrict__ x,
+                  const double* __restrict__ Cdfull, const double* __restrict__ sigmasq,
+                  double nu_s, double s_0, const float* __restrict__ g, ObsDims dm,
+                  float* __restrict__ s_out) {
+  extern __shared__ __align__(16) double Cs[];
+  const int k = dm.k, dk = dm.dk, D = dm.D;
+  double* isig = Cs + (size_t)k * dk * (D + 1);
+  load_cd(Cdfull, k * dk, D, Cs);
+  for (int i = threadIdx.x; i < k; i += blockDim.x) isig[i] = 1.0 / sigmasq[i];
+  __syncthreads();
+  const long long frames = (long long)dm.N * dm.T;
+  const long long f = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= frames) return;
+  double xr[OBS_XMAX];
+  load_x(x, (size_t)f, D, xr);
+  double sn, cs;
+  sincos((double)h[f], &sn, &cs);
+  double vv[OBS_DKMAX];
+#pragma unroll
+  for (int dim = 0; dim < OBS_DKMAX; dim++) vv[dim] = (dim < dk) ? (double)v[f * dk + dim] : 0.0;
+  const double base = s_0 * nu_s;
+  for (int kp = 0; kp < k; kp++) {
+    double yb[OBS_DKMAX], yt[OBS_DKMAX];
+    ybar_kp(Cs, kp, dk, D, xr, yb);
+    ytild_kp(Y + ((size_t)f * k + kp) * dk, vv, cs, sn, dk, yt);
+    double e = 0.0;
+#pragma unroll
+    for (int dim = 0; dim < OBS_DKMAX; dim++) {
+      const double r = yt[dim] - yb[dim];
+      e = fma(r, r, e);
+    }
+    const double gg = (double)g[(size_t)f * k + kp];
+    s_out[(size_t)f * k + kp] = (float)((e * isig[kp] + base) * 0.5 / gg);
+  }
+}
+
+extern "C" int kpms_resample_scales(const float* Y, const float* v, const float* h, const float* x,
+                                    const double* Cdfull, const double* sigmasq, double nu_s,
+                                    double s_0, const float* g, int N, int T, int k, int dk, int D,
+                                    float* s_out, void* stream) {
+  KPMS_REQUIRE(Y && v && h && x && Cdfull && sigmasq && g && s_out, KPMS_ERR_NULL);
+  int rc = obs_check(N, T, k, dk, D);
+  if (rc) return rc;
+  ObsDims dm{N, T, k, dk, D};
+  const size_t smem = ((size_t)k * dk * (D + 1) + k) * sizeof(double);
+  const long long frames = (long long)N * T;
+  scales_kernel<<<(unsigned)((frames + 255) / 256), 256, smem, (cudaStream_t)stream>>>(
+      Y, v, h, x, Cdfull, sigmasq, nu_s, s_0, g, dm, s_out);
+  return kpms_last_launch();
+}
+
+// ======================================================================== a15
+// Best & Fisher (1979) von Mises rejection sampler on injected uniforms; contract shared
+// with oracle/kpms_oracle.py:sample_vonmises.
+__device__ __forceinline__ double vonmises_dev(double kappa, const float* __restrict__ u,
+                                               int rounds) {
+  if (kappa < 1e-8) return KPMS_PI * (2.0 * (double)u[2] - 1.0);
+  const double tau = 1.0 + sqrt(1.0 + 4.0 * kappa * kappa);
+  const double rho = (tau - sqrt(2.0 * tau)) / (2.0 * kappa);
+  const double r = (1.0 + rho * rho) / (2.0 * rho);
+  for (int rd = 0; rd < rounds; rd++) {
+    const double u1 = (double)u[rd * 3 + 0], u2 = (double)u[rd * 3 + 1], u3 = (double)u[rd * 3 + 2];
+    const double zc = cospi(u1);
+    double f = (1.0 + r * zc) / (r + zc);
+    const double c = kappa * (r - f);
+    if (c * (2.0 - c) - u2 > 0.0 || log(c / u2) + 1.0 - c >= 0.0) {
+      f = fmin(1.0, fmax(-1.0, f));
+      return (u3 > 0.5) ? acos(f) : -acos(f);
+    }
+  }
+  return 0.0;
+}
+
+__global__ void __launch_bounds__(256)
+    heading_kernel(const float* __restrict__ Y, const float* __restrict__ v,
+                   const float* __restrict__ x, const float* __restrict__ s,
+                   const double* __restrict__ Cdfull, const double* __restrict__ sigmasq,
+                   const float* __restrict__ u, int rounds, ObsDims dm, float* __restrict__ h_out,
+                   double* __restrict__ theta_out, double* __restrict__ kappa_out) {
+  extern __shared__ __align__(16) double Cs[];
+  const int k = dm.k, dk = dm.dk, D = dm.D;
+  double* isig = Cs + (size_t)k * dk * (D + 1);
+  load_cd(Cdfull, k * dk, D, Cs);
+  for (int i = threadIdx.x; i < k; i += blockDim.x) isig[i] = sigmasq[i];
+  __syncthreads();
+  const long long frames = (long long)dm.N * dm.T;
+  const long long f = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= frames) return;
+  double xr[OBS_XMAX];
+  load_x(x, (size_t)f, D, xr);
+  const double v0 = (double)v[f * dk + 0], v1 = (double)v[f * dk + 1];
+  double S00 = 0.0, S01 = 0.0, S10 = 0.0, S11 = 0.0;
+  for (int kp = 0; kp < k; kp++) {
+    double yb[OBS_DKMAX];
+    ybar_kp(Cs, kp, dk, D, xr, yb);
+    const float* Yf = Y + ((size_t)f * k + kp) * dk;
+    const double w = 1.0 / ((double)s[(size_t)f * k + kp] * isig[kp]);
+    const double y0 = ((double)Yf[0] - v0) * w, y1 = ((double)Yf[1] - v1) * w;
+    S00 = fma(yb[0], y0, S00);
+    S01 = fma(yb[0], y1, S01);
+    S10 = fma(yb[1], y0, S10);
+    S11 = fma(yb[1], y1, S11);
+  }
+  const double kc = S00 + S11, ks = S01 - S10;
+  // util.py:80-82 vector_to_angle
+  const double xx = kc + 1e-10;
+  double ang = atan(ks / xx) + ((xx > 0.0) ? KPMS_PI : 0.0);
+  ang = ang - 2.0 * KPMS_PI * floor(ang / (2.0 * KPMS_PI)) - KPMS_PI;
+  const double kappa = sqrt(kc * kc + ks * ks);
+  if (theta_out) theta_out[f] = ang;
+  if (kappa_out) kappa_out[f] = kappa;
+  double hh = ang + vonmises_dev(kappa, u + (size_t)f * rounds * 3, rounds);
+  hh = hh - 2.0 * KPMS_PI * rint(hh / (2.0 * KPMS_PI));
+  h_out[f] = (float)hh;
+}
+
+extern "C" int kpms_resample_heading(const float* Y, const float* v, const float* x, const float* s,
+                                     const double* Cdfull, const double* sigmasq, const float* u,
+                                     int rounds, int N, int T, int k, int dk, int D, float* h_out,
+                                     double* theta_out, double* kappa_out, void* stream) {
+  KPMS_REQUIRE(Y && v && x && s && Cdfull && sigmasq && u && h_out, KPMS_ERR_NULL);
+  int rc = obs_check(N, T, k, dk, D);
+  if (rc) return rc;
+  KPMS_REQUIRE(rounds > 0, KPMS_ERR_SHAPE);
+  ObsDims dm{N, T, k, dk, D};
+  const size_t smem = ((size_t)k * dk * (D + 1) + k) * sizeof(double);
+  const long long frames = (long long)N * T;
+  heading_kernel<<<(unsigned)((frames + 255) / 256), 256, smem, (cudaStream_t)stream>>>(
+      Y, v, x, s, Cdfull, sigmasq, u, rounds, dm, h_out, theta_out, kappa_out);
+  return kpms_last_launch();
+}
+
+// ======================================================================== a16
+// Stage 1 (frame-parallel, gibbs.py:40-46): gammasq = 1/sum_k 1/(s sigmasq),
+//   mu = sum_k (Y_k - R(h) Ybar_k) gammasq/(s sigmasq); stored in information form
+//   rg = 1/gammasq, em = mu/gammasq, ct = sum_dim -1/2 log(2 pi gammasq) - 1/2 mu^2/gammasq.
+// Stage 2 (one thread per session): the isotropic model keeps every covariance a multiple of
+//   the identity, so kalman_sample reduces to scalar recursions (information form, same
+//   algebra as kalman.cu): lam_c = lam_p + rg, eta_c = eta_p + em,
+//   S_cond = 1/(lam_c + 1/q) (q = sigmasq_loc), lam_p' = lam_c/(q lam_c + 1), eta_p' likewise;
+//   backward x = S_cond (eta_c + x'/q) + sqrt(S_cond) w.
+#define LOC_UNROLL 8
+
+extern "C" size_t kpms_resample_location_workspace_bytes(int N, int T, int dk) {
+  if (N <= 0 || T <= 0 || dk <= 0) return 0;
+  // stats: (2+dk) doubles per frame; filter: (1+dk) doubles per frame
+  return kpms_round_up((size_t)N * T * (2 + dk) * sizeof(double), 256) +
+         kpms_round_up((size_t)N * T * (1 + dk) * sizeof(double), 256);
+}
+
+__global__ void __launch_bounds__(256)
+    location_stats_kernel(const float* __restrict__ Y, const float* __restrict__ h,
+                          const float* __restrict__ x, const float* __restrict__ s,
+                          const double* __restrict__ Cdfull, const double* __restrict__ sigmasq,
+                          ObsDims dm, double* __restrict__ st) {
+  extern __shared__ __align__(16) double Cs[];
+  const int k = dm.k, dk = dm.dk, D = dm.D;
+  double* sig = Cs + (size_t)k * dk * (D + 1);
+  load_cd(Cdfull, k * dk, D, Cs);
+  for (int i = threadIdx.x; i < k; i += blockDim.x) sig[i] = sigmasq[i];
+  __syncthreads();
+  const long long frames = (long long)dm.N * dm.T;
+  const long long f = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= frames) return;
+  double xr[OBS_XMAX];
+  load_x(x, (size_t)f, D, xr);
+  double sn, cs;
+  sincos((double)h[f], &sn, &cs);
+  double wsum = 0.0, acc[OBS_DKMAX] = {0.0, 0.0, 0.0};
+  for (int kp = 0; kp < k; kp++) {
+    double yb[OBS_DKMAX];
+    ybar_kp(Cs, kp, dk, D, xr, yb);
+    const float* Yf = Y + ((size_t)f * k + kp) * dk;
+    const double w = 1.0 / ((double)s[(size_t)f * k + kp] * sig[kp]);
+    // R(h) Ybar  (util.py:85-109): [c -s; s c] on the first two coordinates
+    const double r0 = cs * yb[0] - sn * yb[1], r1 = sn * yb[0] + cs * yb[1];
+    acc[0] = fma((double)Yf[0] - r0, w, acc[0]);
+    acc[1] = fma((double)Yf[1] - r1, w, acc[1]);
+    if (dk > 2) acc[2] = fma((double)Yf[2] - yb[2], w, acc[2]);
+    wsum += w;
+  }
+  // mu = acc * gammasq with gammasq = 1/wsum  ->  em = mu/gammasq = acc, rg = wsum
+  const double g2 = 1.0 / wsum;
+  double ct = 0.0;
+  double* o = st + (size_t)f * (2 + dk);
+  o[0] = wsum;
+  for (int dim = 0; dim < dk; dim++) {
+    const double mu = acc[dim] * g2;
+    o[1 + dim] = mu * wsum;  // == (mu/gammasq), computed from the rounded mu as the reference does
+    ct += -0.5 * (KPMS_LOG_2PI + log(g2)) - 0.5 * mu * mu * wsum;
+  }
+  o[1 + dk] = ct;
+}
+
+template <int DK>
+__global__ void __launch_bounds__(32)
+    location_sample_kernel(const double* __restrict__ st, const float* __restrict__ mask,
+                           const float* __restrict__ w, const float* __restrict__ w_last,
+                           double q, int N, int T, double* __restrict__ fw,
+                           float* __restrict__ v_out, double* __restrict__ loglik) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  const double* st_n = st + (size_t)n * T * (2 + DK);
+  double* fw_n = fw + (size_t)n * T * (1 + DK);
+  const float* mk = mask + (size_t)n * T;
+  const double iq = 1.0 / q, lq = log(q);
+  double lam = 1e-6, eta[DK];
+#pragma unroll
+  for (int d = 0; d < DK; d++) eta[d] = 0.0;
+  double ll = 0.5 * DK * log(1e-6);
+  const bool want_ll = loglik != nullptr;
+  for (int tb = 0; tb < T - 1; tb += LOC_UNROLL) {
+    double rg[LOC_UNROLL], em[LOC_UNROLL][DK], ct[LOC_UNROLL];
+    float m[LOC_UNROLL];
+#pragma unroll
+    for (int i = 0; i < LOC_UNROLL; i++) {
+      const int t = tb + i;
+      m[i] = 0.0f;
+      if (t < T - 1) {
+        m[i] = mk[t];
+        const double* o = st_n + (size_t)t * (2 + DK);
+        rg[i] = o[0];
+#pragma unroll
+        for (int d = 0; d < DK; d++) em[i][d] = o[1 + d];
+        ct[i] = o[1 + DK];
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < LOC_UNROLL; i++) {
+      const int t = tb + i;
+      if (t < T - 1 && m[i] > 0.0f) {
+        const double lc = lam + rg[i];
+        const double r = 1.0 / fma(q, lc, 1.0);
+        const double Sc = q * r;
+        const double Lc = sqrt(Sc);
+        double* o = fw_n + (size_t)t * (1 + DK);
+        o[0] = Lc;
+        double uu = 0.0;
+#pragma unroll
+        for (int d = 0; d < DK; d++) {
+          const double ec = eta[d] + em[i][d];
+          o[1 + d] = ec;
+          eta[d] = ec * r;
+          uu = fma(Lc * ec, Lc * ec, uu);
+        }
+        lam = lc * r;
+        if (want_ll) ll += ct[i] - 0.5 * DK * lq + DK * log(Lc) + 0.5 * uu;
+      }
+    }
+  }
+  // unconditional final update (kalman.py:117) and draw of the last state (kalman.py:150)
+  double xv[DK];
+  {
+    const double* o = st_n + (size_t)(T - 1) * (2 + DK);
+    const double lc = lam + o[0];
+    const double Ll = 1.0 / sqrt(lc);
+    double tt = 0.0;
+#pragma unroll
+    for (int d = 0; d < DK; d++) {
+      const double ec = eta[d] + o[1 + d];
+      const double td = Ll * ec;
+      tt = fma(td, td, tt);
+      xv[d] = Ll * (td + (double)w_last[(size_t)n * DK + d]);
+      v_out[((size_t)n * T + (T - 1)) * DK + d] = (float)xv[d];
+    }
+    if (want_ll) loglik[n] = ll + o[1 + DK] + DK * log(Ll) + 0.5 * tt;
+  }
+  const float* w_n = w + (size_t)n * (T - 1) * DK;
+  for (int tb = T - 2; tb >= 0; tb -= LOC_UNROLL) {
+    double Lc[LOC_UNROLL], ec[LOC_UNROLL][DK];
+    float wv[LOC_UNROLL][DK], m[LOC_UNROLL];
+#pragma unroll
+    for (int i = 0; i < LOC_UNROLL; i++) {
+      const int t = tb - i;
+      m[i] = 0.0f;
+      if (t >= 0) {
+        m[i] = mk[t];
+        if (m[i] > 0.0f) {
+          const double* o = fw_n + (size_t)t * (1 + DK);
+          Lc[i] = o[0];
+#pragma unroll
+          for (int d = 0; d < DK; d++) {
+            ec[i][d] = o[1 + d];
+            wv[i][d] = w_n[(size_t)t * DK + d];
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < LOC_UNROLL; i++) {
+      const int t = tb - i;
+      if (t >= 0) {
+        if (m[i] > 0.0f) {
+#pragma unroll
+          for (int d = 0; d < DK; d++) {
+            const double hh = fma(xv[d], iq, ec[i][d]);
+            xv[d] = Lc[i] * fma(Lc[i], hh, (double)wv[i][d]);
+            v_out[((size_t)n * T + t) * DK + d] = (float)xv[d];
+          }
+        } else {
+#pragma unroll
+          for (int d = 0; d < DK; d++) v_out[((size_t)n * T + t) * DK + d] = 0.0f;  // kalman.py:142-143
+        }
+      }
+    }
+  }
+}
+
+extern "C" int kpms_resample_location(const float* Y, const float* mask, const float* h,
+                                      const float* x, const float* s, const double* Cdfull,
+                                      const double* sigmasq, double sigmasq_loc, const float* w,
+                                      const float* w_last, int N, int T, int k, int dk, int D,
+                                      float* v_out, double* loglik, void* workspace,
+                                      size_t workspace_bytes, void* stream) {
+  KPMS_REQUIRE(Y && mask && h && x && s && Cdfull && sigmasq && w && w_last && v_out && workspace,
+               KPMS_ERR_NULL);
+  int rc = obs_check(N, T, k, dk, D);
+  if (rc) return rc;
+  KPMS_REQUIRE(T >= 2 && sigmasq_loc > 0.0, KPMS_ERR_SHAPE);
+  KPMS_REQUIRE(kpms_aligned(workspace, 256) &&
+                   workspace_bytes >= kpms_resample_location_workspace_bytes(N, T, dk),
+               KPMS_ERR_WORKSPACE);
+  cudaStream_t st = (cudaStream_t)stream;
+  ObsDims dm{N, T, k, dk, D};
+  double* stats = (double*)workspace;
+  double* fw = (double*)((char*)workspace +
+                         kpms_round_up((size_t)N * T * (2 + dk) * sizeof(double), 256));
+  const size_t smem = ((size_t)k * dk * (D + 1) + k) * sizeof(double);
+  const long long frames = (long long)N * T;
+  location_stats_kernel<<<(unsigned)((frames + 255) / 256), 256, smem, st>>>(Y, h, x, s, Cdfull,
+                                                                           sigmasq, dm, stats);
+  rc = kpms_last_launch();
+  if (rc) return rc;
+  const unsigned grid = (unsigned)((N + 31) / 32);
+  if (dk == 2)
+    location_sample_kernel<2><<<grid, 32, 0, st>>>(stats, mask, w, w_last, sigmasq_loc, N, T, fw,
+                                                   v_out, loglik);
+  else
+    location_sample_kernel<3><<<grid, 32, 0, st>>>(stats, mask, w, w_last, sigmasq_loc, N, T, fw,
+                                                   v_out, loglik);
+  return kpms_last_launch();
+}

@@ -1,0 +1,398 @@
+"""Blocked Gibbs steps of the keypoint-SLDS — same names, keyword arguments and return
+values as the reference's `keypoint_moseq/gibbs.py`, on torch CUDA tensors, calling the
+sm_100a kernels of libkpms_b200.so through the C-ABI (include/kpms_b200.h).
+
+Conventions kept from the reference: `resample_X(key, *, <named arrays>, **kwargs)`;
+unknown keyword arguments are swallowed so callers can splat the data / states / params /
+hyper-parameter dicts; inputs are never mutated; outputs are fresh tensors.
+
+Differences: per-frame arrays are stored float32 (parameters and
+statistics float64, state sequences int32); `key` is an int / tuple / torch.Generator;
+every step takes an optional `draws={...}` dict of pre-generated variates (parity tests
+inject the oracle's draws) and an optional `Gamma=` centering basis.  There is no CPU
+fallback: a missing library or a CPU tensor raises.
+"""
+import torch
+
+from . import _lib
+from . import distributions as dist
+from .util import center_embedding, expand_Cd, f32, f64, i32
+
+VONMISES_ROUNDS = 8          # Best-Fisher rejection rounds pre-drawn per frame
+THIN_CAP = 16384             # max tables per state handled by the sticky thinning
+LATENTS_CHUNKING = {"chunk_len": 0, "burn_in": 0}   # module default: exact, one CTA per session
+
+
+def _dims(Ab):
+    K, D = Ab.shape[0], Ab.shape[1]
+    L = Ab.shape[2] // Ab.shape[1]          # gibbs.py:12,102,109
+    return K, D, L
+
+
+def _gamma(Gamma, k, dev):
+    return center_embedding(k, dev) if Gamma is None else f64(Gamma, dev)
+
+
+# ------------------------------------------------------------------------ a1-a4
+def ar_log_likelihood(*, x, Ab, Q, impl=0, **kwargs):
+    """gibbs.py:100-104,110 -> ll (N, T-L, K) float32."""
+    lib = _lib.load()
+    x = f32(x)
+    dev = x.device
+    Ab, Q = f64(Ab, dev), f64(Q, dev)
+    K, D, L = _dims(Ab)
+    N, T, _ = x.shape
+    ll = torch.empty((N, T - L, K), dtype=torch.float32, device=dev)
+    nbytes = lib.kpms_ar_loglik_workspace_bytes(K, D, L)
+    ws = _lib.WORKSPACE.get("ar_loglik", nbytes, dev)
+    _lib.check(lib.kpms_ar_loglik(_lib.ptr(x), _lib.ptr(Ab), _lib.ptr(Q), N, T, D, L, K, _lib.ptr(ll),
+                                  _lib.ptr(ws), ws.numel(), int(impl), _lib.stream_ptr(dev)),
+               "kpms_ar_loglik")
+    return ll
+
+
+def sample_hmm_stateseqs(*, ll, mask, pi, u):
+    """distributions.py:46-79 batched over sessions: ll (N,Tm,K), mask (N,Tm), u (N,Tm)."""
+    lib = _lib.load()
+    ll = f32(ll)
+    dev = ll.device
+    N, Tm, K = ll.shape
+    mask, pi, u = f32(mask, dev), f64(pi, dev), f32(u, dev)
+    z = torch.empty((N, Tm), dtype=torch.int32, device=dev)
+    loglik = torch.empty((N,), dtype=torch.float64, device=dev)
+    ws = _lib.WORKSPACE.get("hmm", lib.kpms_hmm_ffbs_workspace_bytes(N, Tm, K), dev)
+    _lib.check(lib.kpms_hmm_ffbs(_lib.ptr(ll), _lib.ptr(mask), Tm, _lib.ptr(pi), _lib.ptr(u), N, Tm, K,
+                                 _lib.ptr(z), _lib.ptr(loglik), _lib.ptr(ws), ws.numel(),
+                                 _lib.stream_ptr(dev)), "kpms_hmm_ffbs")
+    return z, loglik
+
+
+def resample_stateseqs(key, *, x, mask, Ab, Q, pi, draws=None, impl=0, **kwargs):
+    """gibbs.py:107-115 -> (z (N,T-L) int32, marginal log-likelihood (N,) float64)."""
+    lib = _lib.load()
+    x = f32(x)
+    dev = x.device
+    mask, Ab, Q, pi = f32(mask, dev), f64(Ab, dev), f64(Q, dev), f64(pi, dev)
+    K, D, L = _dims(Ab)
+    N, T, _ = x.shape
+    if draws is not None:
+        u = f32(draws["u"], dev)
+    else:
+        u = dist.fill_uniform((N, T - L), dist.seed_of(key), dist.STREAM_Z, dev)
+    z = torch.empty((N, T - L), dtype=torch.int32, device=dev)
+    loglik = torch.empty((N,), dtype=torch.float64, device=dev)
+    ws = _lib.WORKSPACE.get("stateseqs", lib.kpms_resample_stateseqs_workspace_bytes(N, T, D, L, K), dev)
+    _lib.check(lib.kpms_resample_stateseqs(
+        _lib.ptr(x), _lib.ptr(mask), _lib.ptr(Ab), _lib.ptr(Q), _lib.ptr(pi), _lib.ptr(u), N, T, D, L, K,
+        _lib.ptr(z), _lib.ptr(loglik), _lib.ptr(ws), ws.numel(), int(impl), _lib.stream_ptr(dev)),
+        "kpms_resample_stateseqs")
+    return z, loglik
+
+
+# ------------------------------------------------------------------------ a5-a7
+def resample_latents(key, *, Y, mask, v, h, z, s, Cd, sigmasq, Ab, Q, Gamma=None, draws=None,
+                     chunk_len=None, burn_in=None, return_info=False, **kwargs):
+    """gibbs.py:10-23 -> x (N,T,D) float32.  With `return_info=True` also returns a dict with
+    the innovation-form marginal log-likelihood (N,) and the chunk-boundary mismatch (2,)."""
+    lib = _lib.load()
+    Y = f32(Y)
+    dev = Y.device
+    N, T, k, dk = Y.shape
+    mask, v, h, s = f32(mask, dev), f32(v, dev), f32(h, dev), f32(s, dev)
+    z = i32(z, dev)
+    Ab, Q, sigmasq = f64(Ab, dev), f64(Q, dev), f64(sigmasq, dev)
+    K, D, L = _dims(Ab)
+    n = D * L
+    Cdfull = expand_Cd(f64(Cd, dev), _gamma(Gamma, k, dev), dk)
+    if draws is not None:
+        w, w_last = f32(draws["w"], dev), f32(draws["w_last"], dev)
+    else:
+        seed = dist.seed_of(key)
+        w = dist.fill_normal((N, T - L, n), seed, dist.STREAM_X, dev)
+        w_last = dist.fill_normal((N, n), seed, dist.STREAM_X_LAST, dev)
+    chunk_len = LATENTS_CHUNKING["chunk_len"] if chunk_len is None else chunk_len
+    burn_in = LATENTS_CHUNKING["burn_in"] if burn_in is None else burn_in
+    x = torch.empty((N, T, D), dtype=torch.float32, device=dev)
+    loglik = torch.empty((N,), dtype=torch.float64, device=dev) if return_info else None
+    berr = torch.zeros((2,), dtype=torch.float64, device=dev) if return_info else None
+    nbytes = lib.kpms_resample_latents_workspace_bytes(N, T, k, dk, D, L, K, int(chunk_len))
+    ws = _lib.WORKSPACE.get("latents", nbytes, dev)
+    _lib.check(lib.kpms_resample_latents(
+        _lib.ptr(Y), _lib.ptr(mask), _lib.ptr(v), _lib.ptr(h), _lib.ptr(z), _lib.ptr(s), _lib.ptr(Cdfull),
+        _lib.ptr(sigmasq), _lib.ptr(Ab), _lib.ptr(Q), _lib.ptr(w), _lib.ptr(w_last), N, T, k, dk, D, L, K,
+        int(chunk_len), int(burn_in), _lib.ptr(x), _lib.ptr(loglik), _lib.ptr(berr), _lib.ptr(ws),
+        ws.numel(), _lib.stream_ptr(dev)), "kpms_resample_latents")
+    if return_info:
+        return x, {"loglik": loglik, "boundary_err": berr}
+    return x
+
+
+# ------------------------------------------------------------------------ a15
+def resample_heading(key, *, Y, v, x, s, Cd, sigmasq, Gamma=None, draws=None, return_info=False,
+                     **kwargs):
+    """gibbs.py:25-35 -> h (N,T) float32 in [-pi, pi]."""
+    lib = _lib.load()
+    Y = f32(Y)
+    dev = Y.device
+    N, T, k, dk = Y.shape
+    v, x, s, sigmasq = f32(v, dev), f32(x, dev), f32(s, dev), f64(sigmasq, dev)
+    D = x.shape[-1]
+    Cdfull = expand_Cd(f64(Cd, dev), _gamma(Gamma, k, dev), dk)
+    if draws is not None:
+        u = f32(draws["u"], dev)
+    else:
+        u = dist.fill_uniform((N, T, VONMISES_ROUNDS, 3), dist.seed_of(key), dist.STREAM_H, dev)
+    rounds = u.shape[2]
+    hout = torch.empty((N, T), dtype=torch.float32, device=dev)
+    theta = torch.empty((N, T), dtype=torch.float64, device=dev) if return_info else None
+    kappa = torch.empty((N, T), dtype=torch.float64, device=dev) if return_info else None
+    _lib.check(lib.kpms_resample_heading(
+        _lib.ptr(Y), _lib.ptr(v), _lib.ptr(x), _lib.ptr(s), _lib.ptr(Cdfull), _lib.ptr(sigmasq), _lib.ptr(u),
+        rounds, N, T, k, dk, D, _lib.ptr(hout), _lib.ptr(theta), _lib.ptr(kappa), _lib.stream_ptr(dev)),
+        "kpms_resample_heading")
+    if return_info:
+        return hout, {"theta": theta, "kappa": kappa}
+    return hout
+
+
+# ------------------------------------------------------------------------ a16
+def resample_location(key, *, mask, Y, h, x, s, Cd, sigmasq, sigmasq_loc, Gamma=None, draws=None,
+                      return_info=False, **kwargs):
+    """gibbs.py:38-54 -> v (N,T,dk) float32."""
+    lib = _lib.load()
+    Y = f32(Y)
+    dev = Y.device
+    N, T, k, dk = Y.shape
+    mask, h, x, s, sigmasq = f32(mask, dev), f32(h, dev), f32(x, dev), f32(s, dev), f64(sigmasq, dev)
+    D = x.shape[-1]
+    Cdfull = expand_Cd(f64(Cd, dev), _gamma(Gamma, k, dev), dk)
+    if draws is not None:
+        w, w_last = f32(draws["w"], dev), f32(draws["w_last"], dev)
+    else:
+        seed = dist.seed_of(key)
+        w = dist.fill_normal((N, T - 1, dk), seed, dist.STREAM_V, dev)
+        w_last = dist.fill_normal((N, dk), seed, dist.STREAM_V_LAST, dev)
+    vout = torch.empty((N, T, dk), dtype=torch.float32, device=dev)
+    loglik = torch.empty((N,), dtype=torch.float64, device=dev) if return_info else None
+    ws = _lib.WORKSPACE.get("location", lib.kpms_resample_location_workspace_bytes(N, T, dk), dev)
+    _lib.check(lib.kpms_resample_location(
+        _lib.ptr(Y), _lib.ptr(mask), _lib.ptr(h), _lib.ptr(x), _lib.ptr(s), _lib.ptr(Cdfull),
+        _lib.ptr(sigmasq), float(sigmasq_loc), _lib.ptr(w), _lib.ptr(w_last), N, T, k, dk, D,
+        _lib.ptr(vout), _lib.ptr(loglik), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)),
+        "kpms_resample_location")
+    if return_info:
+        return vout, {"loglik": loglik}
+    return vout
+
+
+# ------------------------------------------------------------------------ a13
+def obs_variance_stats(*, Y, mask, Cd, v, h, x, s, Gamma=None, **kwargs):
+    """gibbs.py:86-94 -> (S_y (k,) float64, mask.sum() (1,) float64)."""
+    lib = _lib.load()
+    Y = f32(Y)
+    dev = Y.device
+    N, T, k, dk = Y.shape
+    mask, v, h, x, s = f32(mask, dev), f32(v, dev), f32(h, dev), f32(x, dev), f32(s, dev)
+    D = x.shape[-1]
+    Cdfull = expand_Cd(f64(Cd, dev), _gamma(Gamma, k, dev), dk)
+    S_y = torch.empty((k,), dtype=torch.float64, device=dev)
+    msum = torch.empty((1,), dtype=torch.float64, device=dev)
+    ws = _lib.WORKSPACE.get("obsvar", lib.kpms_obs_variance_stats_workspace_bytes(N, T, k), dev)
+    _lib.check(lib.kpms_obs_variance_stats(
+        _lib.ptr(Y), _lib.ptr(mask), _lib.ptr(v), _lib.ptr(h), _lib.ptr(x), _lib.ptr(s), _lib.ptr(Cdfull),
+        N, T, k, dk, D, _lib.ptr(S_y), _lib.ptr(msum), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)),
+        "kpms_obs_variance_stats")
+    return S_y, msum
+
+
+def sample_obs_variance(key, S_y, msum, *, nu_sigma, sigmasq_0, draws=None):
+    """gibbs.py:94-96 given the (possibly all-reduced) statistics."""
+    variance = (nu_sigma * sigmasq_0 + S_y) / (nu_sigma + 3 * msum)   # literal 3: gibbs.py:94
+    degs = (nu_sigma + 3 * msum) * torch.ones_like(variance)
+    if draws is not None:
+        g = f64(draws["g"], S_y.device)
+    else:
+        g = dist.sample_gamma(dist.torch_generator(dist.seed_of(key), 13, S_y.device), degs / 2)
+    return dist.sample_scaled_inv_chi2(degs, variance, g)
+
+
+def resample_obs_variance(key, *, Y, mask, Cd, v, h, x, s, nu_sigma, sigmasq_0, Gamma=None, draws=None,
+                          **kwargs):
+    """gibbs.py:84-96 -> sigmasq (k,) float64."""
+    S_y, msum = obs_variance_stats(Y=Y, mask=mask, Cd=Cd, v=v, h=h, x=x, s=s, Gamma=Gamma)
+    return sample_obs_variance(key, S_y, msum, nu_sigma=nu_sigma, sigmasq_0=sigmasq_0, draws=draws)
+
+
+# ------------------------------------------------------------------------ a14
+def resample_scales(key, *, x, v, h, Y, Cd, sigmasq, nu_s, s_0, Gamma=None, draws=None, **kwargs):
+    """gibbs.py:117-125 -> s (N,T,k) float32 (no mask, as the reference)."""
+    lib = _lib.load()
+    Y = f32(Y)
+    dev = Y.device
+    N, T, k, dk = Y.shape
+    x, v, h, sigmasq = f32(x, dev), f32(v, dev), f32(h, dev), f64(sigmasq, dev)
+    D = x.shape[-1]
+    Cdfull = expand_Cd(f64(Cd, dev), _gamma(Gamma, k, dev), dk)
+    if draws is not None:
+        g = f32(draws["g"], dev)
+    else:
+        g = dist.fill_gamma((N, T, k), (nu_s + 3) / 2, dist.seed_of(key), dist.STREAM_S, dev)
+    sout = torch.empty((N, T, k), dtype=torch.float32, device=dev)
+    _lib.check(lib.kpms_resample_scales(
+        _lib.ptr(Y), _lib.ptr(v), _lib.ptr(h), _lib.ptr(x), _lib.ptr(Cdfull), _lib.ptr(sigmasq),
+        float(nu_s), float(s_0), _lib.ptr(g), N, T, k, dk, D, _lib.ptr(sout), _lib.stream_ptr(dev)),
+        "kpms_resample_scales")
+    return sout
+
+
+# ------------------------------------------------------------------------ a8-a9
+def ar_sufficient_stats(*, nlags, num_states, mask, x, z, **kwargs):
+    """gibbs.py:129-131,141-143 -> F (K,P,P) float64 over f = [x_in, 1, x_out]."""
+    lib = _lib.load()
+    x = f32(x)
+    dev = x.device
+    mask, z = f32(mask, dev), i32(z, dev)
+    N, T, D = x.shape
+    L, K = int(nlags), int(num_states)
+    P = D * L + 1 + D
+    F = torch.empty((K, P, P), dtype=torch.float64, device=dev)
+    ws = _lib.WORKSPACE.get("arstats", lib.kpms_ar_stats_workspace_bytes(N, T, D, L, K), dev)
+    _lib.check(lib.kpms_ar_stats(_lib.ptr(x), _lib.ptr(z), _lib.ptr(mask), N, T, D, L, K, _lib.ptr(F),
+                                 _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)), "kpms_ar_stats")
+    return F
+
+
+def sample_ar_params(key, F, *, nlags, nu_0, S_0, M_0, K_0, draws=None):
+    """gibbs.py:132-136 + distributions.py:23-42 from the (possibly all-reduced) statistics."""
+    dev = F.device
+    K, P, _ = F.shape
+    D = S_0.shape[-1] if torch.is_tensor(S_0) else len(S_0)
+    P1 = D * int(nlags) + 1
+    S_0, M_0, K_0 = f64(S_0, dev), f64(M_0, dev), f64(K_0, dev)
+    S_in_in, S_out_in, S_out_out = F[:, :P1, :P1], F[:, P1:, :P1], F[:, P1:, P1:]
+    count = F[:, P1 - 1, P1 - 1]
+    K_0_inv = torch.linalg.inv(K_0)
+    K_n = torch.linalg.inv(K_0_inv + S_in_in)
+    M_n = (M_0 @ K_0_inv + S_out_in) @ K_n
+    S_n = S_0 + S_out_out + (M_0 @ K_0_inv @ M_0.T - M_n @ torch.linalg.inv(K_n) @ M_n.transpose(-1, -2))
+    nu = nu_0 + count
+    if draws is not None:
+        chi2, normals, G = f64(draws["chi2"], dev), f64(draws["normals"], dev), f64(draws["G"], dev)
+    else:
+        gen = dist.torch_generator(dist.seed_of(key), 11, dev)
+        dof = nu[:, None] - torch.arange(D, dtype=torch.float64, device=dev)[None, :]
+        chi2 = dist.sample_gamma(gen, dof / 2) * 2                     # distributions.py:17-18
+        normals = torch.randn((K, D * (D - 1) // 2), dtype=torch.float64, device=dev, generator=gen)
+        G = torch.randn((K, D, P1), dtype=torch.float64, device=dev, generator=gen)
+    Ab, Q = dist.sample_mniw(nu, S_n, M_n, K_n, chi2, normals, G)
+    return Ab.contiguous(), Q.contiguous()
+
+
+def resample_ar_params(key, *, nlags, num_states, mask, x, z, nu_0, S_0, M_0, K_0, draws=None, **kwargs):
+    """gibbs.py:139-145 -> (Ab (K,D,D*L+1), Q (K,D,D)) float64."""
+    F = ar_sufficient_stats(nlags=nlags, num_states=num_states, mask=mask, x=x, z=z)
+    return sample_ar_params(key, F, nlags=nlags, nu_0=nu_0, S_0=S_0, M_0=M_0, K_0=K_0, draws=draws)
+
+
+def resample_regression_params(key, mask, x_in, x_out, nu_0, S_0, M_0, K_0, draws=None):
+    """gibbs.py:127-136 for one state with explicit regressors (small-problem utility; the
+    sweep uses `resample_ar_params`, which never materialises x_in)."""
+    x_in, x_out = f64(x_in), f64(x_out, x_in.device)
+    m = f64(mask, x_in.device)
+    f = torch.cat([x_in, x_out], dim=1) * torch.sqrt(m)[:, None]
+    P1 = x_in.shape[1]
+    F = (f.T @ f)[None]
+    F[0, P1 - 1, P1 - 1] = m.sum()
+    nl = (P1 - 1) // x_out.shape[1]
+    Ab, Q = sample_ar_params(key, F, nlags=nl, nu_0=nu_0, S_0=S_0, M_0=M_0, K_0=K_0, draws=draws)
+    return Ab[0], Q[0]
+
+
+# ------------------------------------------------------------------------ a10-a12
+def transition_counts(*, z, mask, num_states, **kwargs):
+    """util.py:178-189 on mask[..., -z.shape[-1]:] (gibbs.py:149) -> (K,K) int64."""
+    lib = _lib.load()
+    z = i32(z)
+    dev = z.device
+    mask = f32(mask, dev)
+    N, Tm = z.shape
+    T = mask.shape[-1]
+    counts = torch.empty((num_states, num_states), dtype=torch.int64, device=dev)
+    mview = mask[:, T - Tm:]
+    _lib.check(lib.kpms_count_transitions(_lib.ptr(z), _lib.c_void_p(mview.data_ptr()), T, N, Tm,
+                                          int(num_states), _lib.ptr(counts), _lib.stream_ptr(dev)),
+               "kpms_count_transitions")
+    return counts
+
+
+def sample_ms(key, counts, betas, alpha, kappa, draws=None, max_customers=None):
+    """transitions.py:23-33 -> ms (K,K) int64 (CRP table counts, sticky diagonal thinned)."""
+    lib = _lib.load()
+    dev = counts.device
+    K = counts.shape[0]
+    counts = counts.to(torch.int64).contiguous()
+    betas = f64(betas, dev)
+    flat = counts.flatten()
+    starts = (torch.cumsum(flat, 0) - flat).reshape(K, K).contiguous()   # transitions.py:12-15
+    if draws is not None:
+        randseq, u_thin = f32(draws["randseq"], dev), f32(draws["u_thin"], dev)
+        if randseq.numel() == 0:
+            randseq = torch.zeros(1, dtype=torch.float32, device=dev)
+    else:
+        if max_customers is None:
+            max_customers = int(flat.sum().item())
+        seed = dist.seed_of(key)
+        randseq = dist.fill_uniform((max(int(max_customers), 1),), seed, dist.STREAM_CRP, dev)
+        u_thin = dist.fill_uniform((K, THIN_CAP), seed, dist.STREAM_THIN, dev)
+    ms = torch.empty((K, K), dtype=torch.int64, device=dev)
+    ms_raw = torch.empty((K, K), dtype=torch.int64, device=dev)
+    overflow = torch.zeros((1,), dtype=torch.int32, device=dev)
+    _lib.check(lib.kpms_crp_tablecounts(
+        _lib.ptr(counts), _lib.ptr(starts), _lib.ptr(betas), float(alpha), float(kappa), _lib.ptr(randseq),
+        _lib.ptr(u_thin), int(u_thin.shape[1]), K, _lib.ptr(ms), _lib.ptr(ms_raw), _lib.ptr(overflow),
+        _lib.stream_ptr(dev)), "kpms_crp_tablecounts")
+    return ms, ms_raw, overflow
+
+
+def sample_hdp_transitions(key, counts, betas, alpha, kappa, gamma, draws=None, max_customers=None):
+    """transitions.py:35-40 -> (betas (K,), pi (K,K)) float64."""
+    dev = counts.device
+    K = counts.shape[0]
+    ms, _, _ = sample_ms(key, counts, betas, alpha, kappa, draws=draws, max_customers=max_customers)
+    gen = dist.torch_generator(dist.seed_of(key), 12, dev)
+    if draws is not None and "betas_g" in draws:
+        gb = f64(draws["betas_g"], dev)
+        betas_new = gb / gb.sum()
+    else:
+        betas_new = dist.sample_dirichlet(gen, ms.sum(0).to(torch.float64) + gamma / K)
+    conc = alpha * betas_new[None, :] + counts.to(torch.float64) + kappa * torch.eye(
+        K, dtype=torch.float64, device=dev)
+    if draws is not None and "pi_g" in draws:
+        gp = f64(draws["pi_g"], dev)
+        pi = gp / gp.sum(-1, keepdim=True)
+    else:
+        pi = dist.sample_dirichlet(gen, conc)
+    return betas_new, pi
+
+
+def sample_transitions(key, counts, alpha, kappa):
+    """transitions.py:42-44."""
+    dev = counts.device
+    K = counts.shape[0]
+    conc = counts.to(torch.float64) + alpha + kappa * torch.eye(K, dtype=torch.float64, device=dev)
+    return dist.sample_dirichlet(dist.torch_generator(dist.seed_of(key), 14, dev), conc)
+
+
+def resample_hdp_transitions(key, *, z, mask, betas, alpha, kappa, gamma, num_states, draws=None, **kwargs):
+    """gibbs.py:148-151 -> (betas, pi).  No device->host copy of z / mask: the histogram and
+    the CRP table counts run on the GPU (the reference round-trips through numba)."""
+    counts = transition_counts(z=z, mask=mask, num_states=num_states)
+    N, Tm = z.shape
+    return sample_hdp_transitions(key, counts, betas, alpha, kappa, gamma, draws=draws,
+                                  max_customers=N * max(Tm - 1, 1))
+
+
+def resample_transitions(key, *, z, mask, alpha, kappa, num_states, **kwargs):
+    """gibbs.py:153-156 -> pi."""
+    counts = transition_counts(z=z, mask=mask, num_states=num_states)
+    return sample_transitions(key, counts, alpha, kappa)
