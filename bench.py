@@ -46,8 +46,8 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--sessions-per-gpu", type=int, default=125)
     ap.add_argument("--frames", type=int, default=36000)
-    ap.add_argument("--chunk-len", type=int, default=None)
-    ap.add_argument("--burn-in", type=int, default=None)
+    ap.add_argument("--chunk-len", type=int, default=1024, help="Kalman chunk length (0 = one CTA per session)")
+    ap.add_argument("--burn-in", type=int, default=256, help="Kalman chunk warm-up steps")
     ap.add_argument("--cpu-sessions", type=int, default=0, help="0 = one per host core (max 16)")
     ap.add_argument("--cpu-frames", type=int, default=6000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -277,6 +277,8 @@ def main():
     w = torch.randn((N, T - sh["L"], n), device=dev)
     wl = torch.randn((N, n), device=dev)
     lat_ms = timed(lambda: G.resample_latents(1, **d, **ss, **pp, **kw, draws={"w": w, "w_last": wl}), reps)
+    _, linfo = G.resample_latents(1, **d, **ss, **pp, **kw, draws={"w": w, "w_last": wl}, return_info=True)
+    boundary_err = [float(v) for v in linfo["boundary_err"].cpu().tolist()]
     del w, wl
     pdim = sh["k"] * sh["dk"]
     bytes_per_frame = 4 * (pdim + sh["k"] + sh["dk"] + 3 + sh["D"]) + 4 * n + 2 * 8 * (n + n * (n + 1) // 2)
@@ -345,6 +347,7 @@ def main():
                 "config": {"workload": "cfg4-shard", "sessions_per_gpu": N, "frames": T, **sh,
                            "total_sessions": N * world, "kalman_chunk_len": G.LATENTS_CHUNKING["chunk_len"],
                            "kalman_burn_in": G.LATENTS_CHUNKING["burn_in"],
+                           "kalman_boundary_err": boundary_err,
                            "l2": "per-step working set (>= 20 GB of filter workspace + ll/alphan) far exceeds the 126 MB L2"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline,
                 "cpu_baseline": cpu, "breakdown_ms": bd}
