@@ -27,6 +27,7 @@
 // is unconditional (kalman.py:109-117,142-143).
 #include "common.cuh"
 #include "dispatch.cuh"
+#include <stdlib.h>
 
 template <int NN, int DD>
 struct KL {
@@ -58,6 +59,7 @@ struct KL {
 
 struct KalWs {
   double* tab;
+  double* tabw;  // packed per-state tables for the warp kernel (KW layout)
   double* obs;
   double* fw;
   double* llpart;
@@ -88,6 +90,8 @@ static size_t kal_layout(int N, int T, int D, int L, int K, int chunk_len, void*
   };
   void* p;
   p = take((size_t)K * TAB * 8); if (ws) ws->tab = (double*)p;
+  const int TABW = (NTRI + NN * D + D * D + NN + D + 2 + 1) / 2 * 2;
+  p = take((size_t)K * TABW * 8); if (ws) ws->tabw = (double*)p;
   p = take((size_t)N * Tp * OBS * 8); if (ws) ws->obs = (double*)p;
   p = take((size_t)N * Tp * FW * 8); if (ws) ws->fw = (double*)p;
   p = take((size_t)N * nch * 8); if (ws) ws->llpart = (double*)p;
@@ -107,9 +111,30 @@ extern "C" size_t kpms_resample_latents_workspace_bytes(int N, int T, int k, int
 
 // ------------------------------------------------------------------ per-state tables
 template <int NN, int DD>
+struct KW {  // packed per-state table + per-warp shared-memory layout of the warp kernel
+  static constexpr int NTRI = NN * (NN + 1) / 2;
+  static constexpr int G = 0;                  // packed lower: [i(i+1)/2 + c]
+  static constexpr int FD = G + NTRI;          // [q*DD + a]
+  static constexpr int QI = FD + NN * DD;      // [a*DD + b]
+  static constexpr int F = QI + DD * DD;       // NN
+  static constexpr int QB = F + NN;            // DD
+  static constexpr int SC = QB + DD;           // c_z, logdet Q_
+  static constexpr int SIZE = (SC + 2 + 1) / 2 * 2;
+  static constexpr int RS = 32;                // row stride (doubles) of the M / L / T row buffers
+  static constexpr int SM_MS = 0;
+  static constexpr int SM_LS = SM_MS + NN * RS;
+  static constexpr int SM_TAB = SM_LS + NN * RS;
+  static constexpr int SM_DV = SM_TAB + SIZE;
+  static constexpr int SM_HV = SM_DV + 32;
+  static constexpr int SM_TOTAL = SM_HV + 32;
+};
+
+template <int NN, int DD>
 __global__ void kalman_tables_kernel(const double* __restrict__ Ab, const double* __restrict__ Q,
-                                     double* __restrict__ tab) {
+                                     double* __restrict__ tab, double* __restrict__ tabw) {
   using Y = KL<NN, DD>;
+  using Wt = KW<NN, DD>;
+  double* tw = tabw + (size_t)blockIdx.x * Wt::SIZE;
   const int k = blockIdx.x, lane = threadIdx.x;
   __shared__ double Lq[DD * DD], Li[DD * DD], Qi[DD * DD], QA[DD * NN], bb[DD], qb[DD];
   const double* Abk = Ab + (size_t)k * DD * (NN + 1);
@@ -138,6 +163,7 @@ __global__ void kalman_tables_kernel(const double* __restrict__ Ab, const double
       }
     }
     t[Y::TAB_SC + 1] = 2.0 * ls + (double)(NN - DD) * log(1e-2);
+    tw[Wt::SC + 1] = t[Y::TAB_SC + 1];
   }
   __syncwarp();
   for (int e = lane; e < DD * DD; e += 32) {
@@ -146,6 +172,7 @@ __global__ void kalman_tables_kernel(const double* __restrict__ Ab, const double
     for (int m = (a > b ? a : b); m < DD; m++) s += Li[m * DD + a] * Li[m * DD + b];
     Qi[e] = s;
     t[Y::TAB_QI + e] = s;
+    tw[Wt::QI + e] = s;
   }
   for (int a = lane; a < DD; a += 32) bb[a] = Abk[a * (NN + 1) + NN];
   __syncwarp();
@@ -160,6 +187,7 @@ __global__ void kalman_tables_kernel(const double* __restrict__ Ab, const double
     for (int b = 0; b < DD; b++) s += Qi[a * DD + b] * bb[b];
     qb[a] = s;
     t[Y::TAB_QB + a] = s;
+    tw[Wt::QB + a] = s;
     t[Y::TAB_B + a] = bb[a];
   }
   __syncwarp();
@@ -168,20 +196,24 @@ __global__ void kalman_tables_kernel(const double* __restrict__ Ab, const double
     double s = (r == c && r >= DD) ? 100.0 : 0.0;
     for (int a = 0; a < DD; a++) s += Abk[a * (NN + 1) + r] * QA[a * NN + c];
     t[Y::TAB_G + e] = s;
+    if (c <= r) tw[Wt::G + r * (r + 1) / 2 + c] = s;
   }
   for (int e = lane; e < NN * DD; e += 32) {
     const int r = e / DD, a = e % DD;
     t[Y::TAB_FD + e] = QA[a * NN + r];
+    tw[Wt::FD + e] = QA[a * NN + r];
   }
   for (int r = lane; r < NN; r += 32) {
     double s = 0.0;
     for (int a = 0; a < DD; a++) s += QA[a * NN + r] * bb[a];
     t[Y::TAB_F + r] = s;
+    tw[Wt::F + r] = s;
   }
   if (lane == 0) {
     double s = 0.0;
     for (int a = 0; a < DD; a++) s += bb[a] * qb[a];
     t[Y::TAB_SC + 0] = s;
+    tw[Wt::SC + 0] = s;
   }
 }
 
@@ -522,6 +554,269 @@ __global__ void __launch_bounds__(KAL_NT, 1)
   }
 }
 
+// ------------------------------------------------------------------ forward filter, warp per chunk
+// One WARP walks one session (or session chunk); no block barriers.  Lane c owns COLUMN c of
+// every n x n matrix in registers (static indexing, loops fully unrolled); a row is handed to
+// the other lanes by publishing it to a per-warp shared-memory row buffer (one store, every lane
+// writes its own element) and is consumed with broadcast loads.  Per step:
+//   W = Lam_p + G_z + J                      (column c, rows >= c)
+//   bottom-up Cholesky  W = M^T M            (30 pivots: shuffle pivot, rsqrt, publish row)
+//   L = M^-1                                 (forward substitution against the published rows)
+//   T = L^T [F | eta_c - f]                  (lane c: column c of F; lane NN: the mean column)
+//   Lam_p' = Qinv_ - T^T T, eta_p' = qb_ + T^T u      (rows of T published, broadcast back)
+// ~4.2 k warp instructions per step, of which ~2.1 k are DFMA; eight such warps per SM.
+#define KW_WARPS 4
+
+template <int NN, int DD>
+__global__ void __launch_bounds__(KW_WARPS * 32, 2)
+    kalman_forward_warp_kernel(const float* __restrict__ mask, const int* __restrict__ z,
+                               const float* __restrict__ w_last, KalWs ws, int N, int T, int Lg,
+                               int chunk_len, int burn_in, int want_ll) {
+  using Y = KL<NN, DD>;
+  using Wt = KW<NN, DD>;
+  static_assert(NN <= 30, "lane NN carries the mean column");
+  constexpr int OFF = NN - DD, RS = Wt::RS, NTRI = Y::NTRI;
+  constexpr unsigned FULL = 0xffffffffu;
+  extern __shared__ __align__(16) double sm[];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  double* S = sm + (size_t)wib * Wt::SM_TOTAL;
+  double* Ms = S + Wt::SM_MS;   // rows of M, later rows of T
+  double* Ls = S + Wt::SM_LS;   // rows of L
+  double* Tb = S + Wt::SM_TAB;  // packed tables of the current state
+  double* dv = S + Wt::SM_DV;   // 1 / M[i][i]
+  double* hv = S + Wt::SM_HV;   // eta_c - f  (then scratch)
+  const int Tp = T - Lg + 1, Tt = Tp - 1;
+  const int nch = kal_nchunks(Tt, chunk_len);
+  const int unit = blockIdx.x * KW_WARPS + wib;
+  if (unit >= N * nch) return;  // whole warp leaves; the kernel has no block-wide barrier
+  const int n = unit / nch, cc = unit % nch;
+  const int t0 = (nch == 1) ? 0 : cc * chunk_len;
+  const int t1 = (nch == 1) ? Tt : min(Tt, t0 + chunk_len);
+  int tb = 0;
+  if (cc > 0) tb = max(0, min(t0, ws.tv[n]) - burn_in);
+  const int c = lane;
+  const bool col = c < NN;
+  const int ca = min(max(c - OFF, 0), DD - 1);  // clamped index into the D-blocks
+
+  double Lp[NN];
+#pragma unroll
+  for (int i = 0; i < NN; i++) Lp[i] = (i == c) ? 0.1 : 0.0;  // gibbs.py:18: S0 = 10 I
+  double eta_p = 0.0;
+  double llacc = (cc == 0) ? 0.5 * (double)NN * log(0.1) : 0.0;
+  const float* mk = mask + (size_t)n * T + (Lg - 1);
+  const int* zn = z + (size_t)n * Tt;
+  const double* obs_n = ws.obs + (size_t)n * Tp * Y::OBS_SIZE;
+  double* fw_n = ws.fw + (size_t)n * Tp * Y::FW_SIZE;
+  int cur_z = -1;
+
+  // observation information of the next step, prefetched one step ahead
+  double Jn[DD], en, ctn;
+  auto load_obs = [&](int tau) {
+    const double* o = obs_n + (size_t)tau * Y::OBS_SIZE;
+#pragma unroll
+    for (int a = 0; a < DD; a++) Jn[a] = (c >= OFF && col && a >= c - OFF) ? o[Y::OBS_J + a * (a + 1) / 2 + (c - OFF)] : 0.0;
+    en = (c >= OFF && col) ? o[Y::OBS_E + c - OFF] : 0.0;
+    ctn = o[Y::OBS_C];
+  };
+  load_obs(tb);
+
+  for (int tau = tb; tau < t1; tau++) {
+    if (tau == t0 && cc > 0) {
+      double* bd = ws.bndf + ((size_t)(n * nch + cc) * 2 + 0) * Y::BND;
+#pragma unroll
+      for (int i = 0; i < NN; i++)
+        if (c <= i) bd[i * (i + 1) / 2 + c] = Lp[i];
+      if (col) bd[NTRI + c] = eta_p;
+    }
+    const bool live = mk[tau] > 0.0f;
+    double Jc[DD];
+#pragma unroll
+    for (int a = 0; a < DD; a++) Jc[a] = Jn[a];
+    const double ec = en, ct = ctn;
+    load_obs(tau + 1);  // tau + 1 <= Tp - 1
+    if (!live) continue;  // kalman.py:109-111
+    const bool store = tau >= t0;
+    const int zt = zn[tau];
+    if (zt != cur_z) {
+      __syncwarp();
+      const double2* src = reinterpret_cast<const double2*>(ws.tabw + (size_t)zt * Wt::SIZE);
+      double2* dst = reinterpret_cast<double2*>(Tb);
+      for (int e = lane; e < Wt::SIZE / 2; e += 32) dst[e] = src[e];
+      cur_z = zt;
+      __syncwarp();
+    }
+    // ---- S1: column c of Lam_s = Lam_p + A^T Qinv A + C^T R^-1 C
+    double Wc[NN];
+#pragma unroll
+    for (int i = 0; i < NN; i++) Wc[i] = Lp[i] + ((i >= c) ? Tb[Wt::G + i * (i + 1) / 2 + c] : 0.0);
+#pragma unroll
+    for (int a = 0; a < DD; a++) Wc[OFF + a] += Jc[a];
+    const double eta_c = eta_p + ec;
+    // ---- S2: bottom-up Cholesky, rows of M published to Ms
+    double pd = 1.0;
+#pragma unroll
+    for (int k = NN - 1; k >= 0; k--) {
+      const double piv = __shfl_sync(FULL, Wc[k], k);
+      const double rs = rsqrt(piv);
+      const double m = Wc[k] * rs;
+      if (c <= k) Ms[k * RS + c] = m;
+      if (c == 0) dv[k] = rs;
+      pd *= rs;
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i + 1 < k; i += 2) {
+        const double2 mm = *reinterpret_cast<const double2*>(Ms + k * RS + i);
+        Wc[i] = fma(-mm.x, m, Wc[i]);
+        Wc[i + 1] = fma(-mm.y, m, Wc[i + 1]);
+      }
+      if (k & 1) Wc[k - 1] = fma(-Ms[k * RS + k - 1], m, Wc[k - 1]);
+    }
+    // ---- S3: L = M^-1, column c (zero above the diagonal by construction)
+    double Lc[NN];
+#pragma unroll
+    for (int i = 0; i < NN; i++) {
+      double a0 = (i == c) ? 1.0 : 0.0, a1 = 0.0;
+#pragma unroll
+      for (int q = 0; q + 1 < i; q += 2) {
+        const double2 mm = *reinterpret_cast<const double2*>(Ms + i * RS + q);
+        a0 = fma(-mm.x, Lc[q], a0);
+        a1 = fma(-mm.y, Lc[q + 1], a1);
+      }
+      if (i & 1) a0 = fma(-Ms[i * RS + i - 1], Lc[i - 1], a0);
+      Lc[i] = (a0 + a1) * dv[i];
+    }
+    // rows of L to shared memory, eta_c - f for the mean column, L and eta_c to the workspace
+#pragma unroll
+    for (int i = 0; i < NN; i++)
+      if (col) Ls[i * RS + c] = Lc[i];
+    if (col) hv[c] = eta_c - Tb[Wt::F + c];
+    if (store) {
+      double* fwp = fw_n + (size_t)tau * Y::FW_SIZE;
+#pragma unroll
+      for (int i = 0; i < NN; i++)
+        if (c <= i) fwp[Y::FW_L + i * (i + 1) / 2 + c] = Lc[i];
+      if (col) fwp[Y::FW_ETA + c] = eta_c;
+    }
+    __syncwarp();
+    // ---- T = L^T Fcol : lane c < OFF: 100 e_{D+c}; OFF <= c < NN: column of F_D; lane NN: eta_c - f
+    double Tc[NN];
+#pragma unroll
+    for (int r = 0; r < NN; r++) Tc[r] = 0.0;
+#pragma unroll
+    for (int q = 0; q < NN; q++) {
+      const double fdv = Tb[Wt::FD + q * DD + ca];
+      const double hq = hv[q];
+      const double fq = (c < OFF) ? ((q == DD + c) ? 100.0 : 0.0) : (col ? fdv : hq);
+#pragma unroll
+      for (int r = 0; r + 1 <= q; r += 2) {
+        const double2 ll2 = *reinterpret_cast<const double2*>(Ls + q * RS + r);
+        Tc[r] = fma(ll2.x, fq, Tc[r]);
+        Tc[r + 1] = fma(ll2.y, fq, Tc[r + 1]);
+      }
+      if (!(q & 1)) Tc[q] = fma(Ls[q * RS + q], fq, Tc[q]);
+    }
+    // rows of T (31 columns: NN of V and u) into the M buffer
+#pragma unroll
+    for (int r = 0; r < NN; r++)
+      if (c <= NN) Ms[r * RS + c] = Tc[r];
+    __syncwarp();
+    // ---- S4: Lam_p' = Qinv_ - T^T T, eta_p' = qb_ + T^T u
+#pragma unroll
+    for (int i = 0; i < NN; i++) Lp[i] = 0.0;
+    double ea = 0.0;
+#pragma unroll
+    for (int r = 0; r < NN; r++) {
+      const double tr = Tc[r];
+      constexpr int dummy = 0;
+      (void)dummy;
+      const int i0 = (r > DD) ? ((r - DD) & ~1) : 0;  // row r of T is zero in columns < r - D
+#pragma unroll
+      for (int i = 0; i + 1 < NN + 1; i += 2) {
+        if (i >= i0 && i < NN) {
+          const double2 tt = *reinterpret_cast<const double2*>(Ms + r * RS + i);
+          Lp[i] = fma(tt.x, tr, Lp[i]);
+          if (i + 1 < NN) Lp[i + 1] = fma(tt.y, tr, Lp[i + 1]);
+        }
+      }
+      ea = fma(Ms[r * RS + NN], tr, ea);
+    }
+#pragma unroll
+    for (int i = 0; i < NN; i++) {
+      double qv;
+      if (c < OFF) qv = (i == c) ? 100.0 : 0.0;
+      else qv = (i >= OFF) ? Tb[Wt::QI + (i - OFF) * DD + ca] : 0.0;
+      Lp[i] = qv - Lp[i];
+    }
+    eta_p = ((c >= OFF) ? Tb[Wt::QB + ca] : 0.0) + ea;
+    if (want_ll && store) {
+      double uu = 0.0;  // meaningful in lane NN (its column of T is u)
+#pragma unroll
+      for (int r = 0; r < NN; r++) uu = fma(Tc[r], Tc[r], uu);
+      llacc += ct - 0.5 * Tb[Wt::SC + 1] + log(pd) + 0.5 * (uu - Tb[Wt::SC + 0]);
+    }
+    __syncwarp();
+  }
+  if (nch > 1) {
+    double* bd = ws.bndf + ((size_t)(n * nch + cc) * 2 + 1) * Y::BND;
+#pragma unroll
+    for (int i = 0; i < NN; i++)
+      if (c <= i) bd[i * (i + 1) / 2 + c] = Lp[i];
+    if (col) bd[NTRI + c] = eta_p;
+  }
+  if (cc == nch - 1) {
+    // unconditional final update (kalman.py:117) and the draw of the last state (kalman.py:150)
+    double Wc[NN];
+#pragma unroll
+    for (int i = 0; i < NN; i++) Wc[i] = Lp[i];
+#pragma unroll
+    for (int a = 0; a < DD; a++) Wc[OFF + a] += Jn[a];
+    const double eta_c = eta_p + en;
+    double pd = 1.0;
+    __syncwarp();
+#pragma unroll
+    for (int k = NN - 1; k >= 0; k--) {
+      const double piv = __shfl_sync(FULL, Wc[k], k);
+      const double rs = rsqrt(piv);
+      const double m = Wc[k] * rs;
+      if (c <= k) Ms[k * RS + c] = m;
+      if (c == 0) dv[k] = rs;
+      pd *= rs;
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < k; i++) Wc[i] = fma(-Ms[k * RS + i], m, Wc[i]);
+    }
+    double Lc[NN];
+#pragma unroll
+    for (int i = 0; i < NN; i++) {
+      double a0 = (i == c) ? 1.0 : 0.0;
+#pragma unroll
+      for (int q = 0; q < i; q++) a0 = fma(-Ms[i * RS + q], Lc[q], a0);
+      Lc[i] = a0 * dv[i];
+    }
+    if (col) hv[c] = eta_c;
+    __syncwarp();
+    // t_c = sum_q L[q][c] eta_c[q];  y = t + w_last;  x_i = sum_c L[i][c] y_c
+    double tc = 0.0;
+#pragma unroll
+    for (int q = 0; q < NN; q++) tc = fma(Lc[q], hv[q], tc);
+    if (!col) tc = 0.0;
+    double tt = tc * tc;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tt += __shfl_xor_sync(FULL, tt, o);
+    const double yc = col ? tc + (double)w_last[(size_t)n * NN + c] : 0.0;
+    double* xl = fw_n + (size_t)(Tp - 1) * Y::FW_SIZE;
+#pragma unroll
+    for (int i = 0; i < NN; i++) {
+      double v = Lc[i] * yc;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+      if (lane == 0) xl[i] = v;
+    }
+    llacc += ctn + log(pd) + 0.5 * tt;
+  }
+  if (lane == NN) ws.llpart[(size_t)n * nch + cc] = llacc;
+}
+
 // ------------------------------------------------------------------ backward sampler
 // One warp per session (or session chunk).  x_t = L (L^T h + w_t),
 // h = eta_c + A^T Qinv (x_{t+1} - B) with A^T Qinv = [100 E | F_D] (see file header).
@@ -718,7 +1013,7 @@ static int launch_latents(const float* Y, const float* mask, const float* v, con
   using YL = KL<NN, DD>;
   const int Tp = T - Lg + 1, Tt = Tp - 1;
   const int nch = kal_nchunks(Tt, chunk_len);
-  kalman_tables_kernel<NN, DD><<<K, 32, 0, st>>>(Ab, Q, ws.tab);
+  kalman_tables_kernel<NN, DD><<<K, 32, 0, st>>>(Ab, Q, ws.tab, ws.tabw);
   int rc = kpms_last_launch();
   if (rc) return rc;
   {
@@ -739,10 +1034,21 @@ static int launch_latents(const float* Y, const float* mask, const float* v, con
   {
     const size_t smem = (size_t)(2 * NN * YL::NS + NN * YL::NV + 3 * NN + NN * NN + NN * DD + DD * DD +
                                  NN + DD + 2 + YL::OBS_SIZE) * sizeof(double) + 2 * YL::NTRI;
-    auto kern = kalman_forward_kernel<NN, DD>;
-    KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<N * nch, KAL_NT, smem, st>>>(mask, z, w_last, ws, N, T, Lg, chunk_len, burn_in,
-                                        loglik != nullptr);
+    const char* env = getenv("KPMS_KALMAN_IMPL");
+    if (env && env[0] == '0') {  // CTA-per-chunk shared-memory kernel (kept for cross-checks)
+      auto kern = kalman_forward_kernel<NN, DD>;
+      KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      kern<<<N * nch, KAL_NT, smem, st>>>(mask, z, w_last, ws, N, T, Lg, chunk_len, burn_in,
+                                          loglik != nullptr);
+    } else {
+      if constexpr (NN <= 30) {
+        const size_t smw = (size_t)KW_WARPS * KW<NN, DD>::SM_TOTAL * sizeof(double);
+        auto kern = kalman_forward_warp_kernel<NN, DD>;
+        KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smw));
+        kern<<<(N * nch + KW_WARPS - 1) / KW_WARPS, KW_WARPS * 32, smw, st>>>(
+            mask, z, w_last, ws, N, T, Lg, chunk_len, burn_in, loglik != nullptr);
+      }
+    }
     rc = kpms_last_launch();
     if (rc) return rc;
   }
