@@ -26,6 +26,7 @@ SIGNATURES = {
     "kpms_fill_gamma": (c_int, [P, c_size_t, c_double, c_uint64, c_uint64, P]),
     "kpms_ar_loglik_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "kpms_ar_loglik": (c_int, [P, P, P, c_int, c_int, c_int, c_int, c_int, P, P, c_size_t, c_int, P]),
+    "kpms_ar_loglik_static": (c_int, [P, P, P, c_int, c_int, c_int, c_int, c_int, P, c_int, P]),
     "kpms_hmm_ffbs_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "kpms_hmm_ffbs": (c_int, [P, P, c_int64, P, P, c_int, c_int, c_int, P, P, P, c_size_t, P]),
     "kpms_resample_stateseqs_workspace_bytes": (c_size_t, [c_int] * 5),

@@ -14,6 +14,8 @@ extern "C" const char* kpms_status_string(int status) {
     case KPMS_ERR_UNSUPPORTED: return "kpms: size not supported by the compiled kernels";
     case KPMS_ERR_WORKSPACE: return "kpms: workspace too small or misaligned";
     case KPMS_ERR_ALIGN: return "kpms: pointer not aligned as required";
+    case KPMS_ERR_TOO_LARGE:
+      return "kpms: problem too large for the built-in fixed-size scratch; use the entry point that takes a workspace";
     default: break;
   }
   if (status > 0) return cudaGetErrorString((cudaError_t)status);

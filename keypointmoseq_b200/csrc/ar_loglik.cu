@@ -166,3 +166,87 @@ extern "C" int kpms_ar_loglik(const float* x, const double* Ab, const double* Q,
 #undef KPMS_X
   return KPMS_ERR_UNSUPPORTED;
 }
+
+// ======================================================================================
+// Allocation-free variant of kpms_ar_loglik.
+//
+// Who needs it: a caller that is handed its buffers by someone else and is not allowed to
+// create device memory of its own.  The obvious case for this library is the reference itself:
+// it is a JAX program, and the natural way to plug these kernels into it is an XLA custom call.
+// Such a handler receives operand and result buffers from XLA and nothing more; XLA has usually
+// claimed most of the GPU's memory for its own pool already, so a cudaMalloc from inside the
+// handler can fail outright, and when it succeeds it stalls the whole device while the driver
+// maps the memory.  The same holds for any host loop that must not block on the driver.
+//
+// kpms_ar_loglik needs a few hundred kilobytes of scratch for the whitened weights; here that
+// scratch is a fixed array that lives in the library image on every GPU that loads it (and stays
+// there until the process exits), so the caller passes only inputs and the output.
+//
+// Rules of use
+//   * Limit: the weights of all states must fit KPMS_AR_STATIC_FLOATS floats
+//     (round_up(K*D*PP, 64) + K <= 65536, PP = D*L+D+1 rounded up to 4; K = 128 states at
+//     D = 10, L = 3 fit).  Larger problems are refused with KPMS_ERR_TOO_LARGE before anything
+//     is launched; use kpms_ar_loglik with a caller workspace instead.
+//   * The first call on each device looks up the device address of the array (with that
+//     device current).  Make that first call outside of any stream capture.
+//   * There is ONE array per device and every call writes it.  Two calls whose kernels can be
+//     in flight together on the same GPU (different streams, different host threads) race on
+//     it; order them on one stream or with events.  The array keeps whatever the previous call
+//     left behind; this entry point never depends on that, because the prepare kernel rewrites
+//     every weight and constant it later reads, so nothing has to be cleared.
+#define KPMS_AR_STATIC_FLOATS (64 * 1024)
+#define KPMS_AR_STATIC_MAX_DEVICES 64
+
+static __device__ __align__(256) float g_ar_static_scratch[KPMS_AR_STATIC_FLOATS];
+
+#include <mutex>
+static std::mutex g_ar_static_mutex;
+static float* g_ar_static_dev_ptr[KPMS_AR_STATIC_MAX_DEVICES] = {nullptr};
+
+// Device address of the scratch array on the current device.  In host code the name
+// `g_ar_static_scratch` is only a handle for the runtime, never an address a kernel may use;
+// the real address comes from cudaGetSymbolAddress and is cached per device.
+static int ar_static_scratch_ptr(float** out) {
+  int dev = -1;
+  KPMS_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= KPMS_AR_STATIC_MAX_DEVICES) return KPMS_ERR_UNSUPPORTED;
+  std::lock_guard<std::mutex> lock(g_ar_static_mutex);
+  if (g_ar_static_dev_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_ar_static_scratch);
+    if (e != cudaSuccess) return (int)e;
+    if (p == nullptr) return KPMS_ERR_NULL;
+    g_ar_static_dev_ptr[dev] = static_cast<float*>(p);
+  }
+  *out = g_ar_static_dev_ptr[dev];
+  return KPMS_OK;
+}
+
+extern "C" int kpms_ar_loglik_static(const float* x, const double* Ab, const double* Q, int N,
+                                     int T, int D, int L, int K, float* ll, int impl,
+                                     void* stream) {
+  KPMS_REQUIRE(x && Ab && Q && ll, KPMS_ERR_NULL);
+  KPMS_REQUIRE(N > 0 && T > L && D > 0 && L > 0 && K > 0, KPMS_ERR_SHAPE);
+  KPMS_REQUIRE(D <= AR_DMAX && kpms_dl_supported(D, L), KPMS_ERR_UNSUPPORTED);
+  const int PP = ar_pp(D, L);
+  const size_t wfloats = kpms_round_up((size_t)K * D * PP, 64);  // keeps cst 256-byte aligned
+  if (wfloats + (size_t)K > (size_t)KPMS_AR_STATIC_FLOATS) return KPMS_ERR_TOO_LARGE;
+  float* base = nullptr;
+  int rc = ar_static_scratch_ptr(&base);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  float* Wf = base;
+  float* cst = base + wfloats;
+  ar_prepare_kernel<<<K, 32, 0, st>>>(Ab, Q, D, L, PP, Wf, cst);
+  rc = kpms_last_launch();
+  if (rc) return rc;
+  if (impl == 0) {
+    rc = kpms_ar_loglik_tc(x, Wf, cst, N, T, D, L, K, ll, st);
+    if (rc != KPMS_ERR_UNSUPPORTED) return rc;
+  }
+#define KPMS_X(d, l) \
+  if (D == d && L == l) return launch_simt<d, l>(x, Wf, cst, N, T, K, ll, st);
+  KPMS_FOR_EACH_DL(KPMS_X)
+#undef KPMS_X
+  return KPMS_ERR_UNSUPPORTED;
+}
