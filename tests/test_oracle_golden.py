@@ -66,7 +66,8 @@ def test_cuda_path_matches_golden(g):
     S, m = G.obs_variance_stats(**common)
     assert np.allclose(N_(S), g['S_y'], rtol=1e-11) and float(m) == float(g['mask_sum'])
     hh = G.resample_heading(0, **common, draws={'u': T_(g['dr_h_u'])})
-    assert np.abs(np.angle(np.exp(1j * (N_(hh) - g['h'])))).max() < 1e-6
+    ok = g['kappa'] > 1e-6   # zero-padded frames have kappa ~ 1e-14: the mean direction is rounding noise there
+    assert np.abs(np.angle(np.exp(1j * (N_(hh) - g['h']))))[ok].max() < 1e-6
     v = G.resample_location(0, **common, sigmasq_loc=0.5, draws={'w': T_(g['dr_v_w']), 'w_last': T_(g['dr_v_w_last'])})
     assert np.abs(N_(v) - g['v']).max() < 3e-7 * max(1.0, np.abs(g['v']).max())
     hp = H.hyp(int(g['D']), L, K)
