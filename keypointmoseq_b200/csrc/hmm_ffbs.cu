@@ -81,18 +81,28 @@ __global__ void __launch_bounds__(KP)
         // refill this ring slot with ll[t+RING]
         ring[i] = (j < K && t + HMM_RING < Tm) ? ll_n[(size_t)(t + HMM_RING) * K + j] : -INFINITY;
         __syncthreads();
-        float acc0 = 0.0f, acc1 = 0.0f, s0 = 0.0f, s1 = 0.0f;
+        // normaliser: every warp reduces the KP shared values itself (identical order in
+        // every warp, so all threads agree bit-for-bit); the shuffles overlap the FMA stream
+        float part = 0.0f;
+#pragma unroll
+        for (int q = 0; q < NW; q++) part += a_s[buf][lane + 32 * q];
+        float acc[8];
+#pragma unroll
+        for (int q = 0; q < 8; q++) acc[q] = 0.0f;
         const float4* av = reinterpret_cast<const float4*>(a_s[buf]);
 #pragma unroll
         for (int q = 0; q < KP / 4; q++) {
-          float4 v = av[q];
-          acc0 = fmaf(v.x, pcol[4 * q + 0], acc0);
-          acc1 = fmaf(v.y, pcol[4 * q + 1], acc1);
-          acc0 = fmaf(v.z, pcol[4 * q + 2], acc0);
-          acc1 = fmaf(v.w, pcol[4 * q + 3], acc1);
-          s0 += v.x + v.z;
-          s1 += v.y + v.w;
+          const float4 v = av[q];
+          acc[(4 * q + 0) & 7] = fmaf(v.x, pcol[4 * q + 0], acc[(4 * q + 0) & 7]);
+          acc[(4 * q + 1) & 7] = fmaf(v.y, pcol[4 * q + 1], acc[(4 * q + 1) & 7]);
+          acc[(4 * q + 2) & 7] = fmaf(v.z, pcol[4 * q + 2], acc[(4 * q + 2) & 7]);
+          acc[(4 * q + 3) & 7] = fmaf(v.w, pcol[4 * q + 3], acc[(4 * q + 3) & 7]);
         }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+        const float acc0 = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+        const float acc1 = (acc[4] + acc[5]) + (acc[6] + acc[7]);
+        const float s0 = part, s1 = 0.0f;
         const float norm = (s0 + s1) + 1e-16f;
         const float inv = 1.0f / norm;
         if (j < K) al_n[(size_t)t * K + j] = a * inv;

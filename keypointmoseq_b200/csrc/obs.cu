@@ -312,12 +312,21 @@ extern "C" int kpms_resample_heading(const float* Y, const float* v, const float
 //   S_cond = 1/(lam_c + 1/q) (q = sigmasq_loc), lam_p' = lam_c/(q lam_c + 1), eta_p' likewise;
 //   backward x = S_cond (eta_c + x'/q) + sqrt(S_cond) w.
 #define LOC_UNROLL 8
+#define LOC_CHUNK 256   // steps per independent chunk
+#define LOC_BURN 128    // warm-up steps: the scalar filter forgets by >= 1/(q*rg+1) per step
+
+__host__ __device__ static inline int loc_nchunks(int T) {
+  const int Tt = T - 1;
+  return Tt <= LOC_CHUNK ? 1 : (Tt + LOC_CHUNK - 1) / LOC_CHUNK;
+}
 
 extern "C" size_t kpms_resample_location_workspace_bytes(int N, int T, int dk) {
   if (N <= 0 || T <= 0 || dk <= 0) return 0;
-  // stats: (2+dk) doubles per frame; filter: (1+dk) doubles per frame
+  // stats: (2+dk) doubles per frame; filter: (1+dk) doubles per frame; ll partials; tv
   return kpms_round_up((size_t)N * T * (2 + dk) * sizeof(double), 256) +
-         kpms_round_up((size_t)N * T * (1 + dk) * sizeof(double), 256);
+         kpms_round_up((size_t)N * T * (1 + dk) * sizeof(double), 256) +
+         kpms_round_up((size_t)N * loc_nchunks(T) * sizeof(double), 256) +
+         kpms_round_up((size_t)N * sizeof(int), 256);
 }
 
 __global__ void __launch_bounds__(256)
@@ -351,44 +360,65 @@ __global__ void __launch_bounds__(256)
     if (dk > 2) acc[2] = fma((double)Yf[2] - yb[2], w, acc[2]);
     wsum += w;
   }
-  // mu = acc * gammasq with gammasq = 1/wsum  ->  em = mu/gammasq = acc, rg = wsum
+  // mu = acc * gammasq with gammasq = 1/wsum  ->  em = mu/gammasq, rg = wsum
   const double g2 = 1.0 / wsum;
   double ct = 0.0;
   double* o = st + (size_t)f * (2 + dk);
   o[0] = wsum;
   for (int dim = 0; dim < dk; dim++) {
     const double mu = acc[dim] * g2;
-    o[1 + dim] = mu * wsum;  // == (mu/gammasq), computed from the rounded mu as the reference does
+    o[1 + dim] = mu * wsum;
     ct += -0.5 * (KPMS_LOG_2PI + log(g2)) - 0.5 * mu * mu * wsum;
   }
   o[1 + dk] = ct;
 }
 
+// unmasked steps per session (mask[:, :-1]); trailing padding assumed for the warm-up start
+__global__ void location_tv_kernel(const float* __restrict__ mask, int T, int* __restrict__ tv) {
+  const int n = blockIdx.x;
+  __shared__ int cnt;
+  if (threadIdx.x == 0) cnt = 0;
+  __syncthreads();
+  int c = 0;
+  for (int t = threadIdx.x; t < T - 1; t += blockDim.x) c += mask[(size_t)n * T + t] > 0.0f;
+  atomicAdd(&cnt, c);
+  __syncthreads();
+  if (threadIdx.x == 0) tv[n] = cnt;
+}
+
+// Forward filter: one thread per (session, chunk).  A chunk other than the first is warmed up
+// from the prior over LOC_BURN earlier steps; with a contraction of at least 1/(q*rg+1) per
+// step (~0.1 here) the carry it reaches is the sequential one to the last bit.
 template <int DK>
-__global__ void __launch_bounds__(32)
-    location_sample_kernel(const double* __restrict__ st, const float* __restrict__ mask,
-                           const float* __restrict__ w, const float* __restrict__ w_last,
-                           double q, int N, int T, double* __restrict__ fw,
-                           float* __restrict__ v_out, double* __restrict__ loglik) {
-  const int n = blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= N) return;
+__global__ void __launch_bounds__(64)
+    location_forward_kernel(const double* __restrict__ st, const float* __restrict__ mask,
+                            const float* __restrict__ w_last, const int* __restrict__ tv, double q,
+                            int N, int T, int want_ll, double* __restrict__ fw,
+                            double* __restrict__ llpart, float* __restrict__ v_out) {
+  const int nch = loc_nchunks(T);
+  const int unit = blockIdx.x * blockDim.x + threadIdx.x;
+  if (unit >= N * nch) return;
+  const int n = unit / nch, cc = unit % nch;
+  const int Tt = T - 1;
+  const int t0 = (nch == 1) ? 0 : cc * LOC_CHUNK;
+  const int t1 = (nch == 1) ? Tt : min(Tt, t0 + LOC_CHUNK);
+  const int tb = (cc > 0) ? max(0, min(t0, tv[n]) - LOC_BURN) : 0;
   const double* st_n = st + (size_t)n * T * (2 + DK);
   double* fw_n = fw + (size_t)n * T * (1 + DK);
   const float* mk = mask + (size_t)n * T;
-  const double iq = 1.0 / q, lq = log(q);
-  double lam = 1e-6, eta[DK];
+  const double lq = log(q);
+  double lam = 1e-6, eta[DK];   // gibbs.py:48: m0 = 0, S0 = 1e6 I
 #pragma unroll
   for (int d = 0; d < DK; d++) eta[d] = 0.0;
-  double ll = 0.5 * DK * log(1e-6);
-  const bool want_ll = loglik != nullptr;
-  for (int tb = 0; tb < T - 1; tb += LOC_UNROLL) {
+  double ll = (cc == 0) ? 0.5 * DK * log(1e-6) : 0.0;
+  for (int tbk = tb; tbk < t1; tbk += LOC_UNROLL) {
     double rg[LOC_UNROLL], em[LOC_UNROLL][DK], ct[LOC_UNROLL];
     float m[LOC_UNROLL];
 #pragma unroll
     for (int i = 0; i < LOC_UNROLL; i++) {
-      const int t = tb + i;
+      const int t = tbk + i;
       m[i] = 0.0f;
-      if (t < T - 1) {
+      if (t < t1) {
         m[i] = mk[t];
         const double* o = st_n + (size_t)t * (2 + DK);
         rg[i] = o[0];
@@ -399,53 +429,91 @@ __global__ void __launch_bounds__(32)
     }
 #pragma unroll
     for (int i = 0; i < LOC_UNROLL; i++) {
-      const int t = tb + i;
-      if (t < T - 1 && m[i] > 0.0f) {
+      const int t = tbk + i;
+      if (t < t1 && m[i] > 0.0f) {
         const double lc = lam + rg[i];
         const double r = 1.0 / fma(q, lc, 1.0);
         const double Sc = q * r;
         const double Lc = sqrt(Sc);
+        const bool store = t >= t0;
         double* o = fw_n + (size_t)t * (1 + DK);
-        o[0] = Lc;
+        if (store) o[0] = Lc;
         double uu = 0.0;
 #pragma unroll
         for (int d = 0; d < DK; d++) {
           const double ec = eta[d] + em[i][d];
-          o[1 + d] = ec;
+          if (store) o[1 + d] = ec;
           eta[d] = ec * r;
           uu = fma(Lc * ec, Lc * ec, uu);
         }
         lam = lc * r;
-        if (want_ll) ll += ct[i] - 0.5 * DK * lq + DK * log(Lc) + 0.5 * uu;
+        if (want_ll && store) ll += ct[i] - 0.5 * DK * lq + DK * log(Lc) + 0.5 * uu;
       }
     }
   }
-  // unconditional final update (kalman.py:117) and draw of the last state (kalman.py:150)
-  double xv[DK];
-  {
+  if (cc == nch - 1) {
+    // unconditional final update (kalman.py:117) and draw of the last state (kalman.py:150)
     const double* o = st_n + (size_t)(T - 1) * (2 + DK);
     const double lc = lam + o[0];
     const double Ll = 1.0 / sqrt(lc);
     double tt = 0.0;
+    double* xl = fw_n + (size_t)(T - 1) * (1 + DK);
 #pragma unroll
     for (int d = 0; d < DK; d++) {
       const double ec = eta[d] + o[1 + d];
       const double td = Ll * ec;
       tt = fma(td, td, tt);
-      xv[d] = Ll * (td + (double)w_last[(size_t)n * DK + d]);
-      v_out[((size_t)n * T + (T - 1)) * DK + d] = (float)xv[d];
+      const double xv = Ll * (td + (double)w_last[(size_t)n * DK + d]);
+      xl[1 + d] = xv;
+      v_out[((size_t)n * T + (T - 1)) * DK + d] = (float)xv;
     }
-    if (want_ll) loglik[n] = ll + o[1 + DK] + DK * log(Ll) + 0.5 * tt;
+    ll += o[1 + DK] + DK * log(Ll) + 0.5 * tt;
   }
-  const float* w_n = w + (size_t)n * (T - 1) * DK;
-  for (int tb = T - 2; tb >= 0; tb -= LOC_UNROLL) {
+  llpart[(size_t)n * nch + cc] = ll;
+}
+
+// Backward sampler, one thread per (session, chunk): x_t = S_cond (eta_c + x_{t+1}/q) + sqrt(S_cond) w_t.
+// A chunk other than the last starts LOC_BURN steps later from 0 (or from x_last inside the
+// trailing padding) and couples to the sequential path at the same geometric rate.
+template <int DK>
+__global__ void __launch_bounds__(64)
+    location_backward_kernel(const double* __restrict__ fw, const float* __restrict__ mask,
+                             const float* __restrict__ w, double q, int N, int T,
+                             const double* __restrict__ llpart, float* __restrict__ v_out,
+                             double* __restrict__ loglik) {
+  const int nch = loc_nchunks(T);
+  const int unit = blockIdx.x * blockDim.x + threadIdx.x;
+  if (unit >= N * nch) return;
+  const int n = unit / nch, cc = unit % nch;
+  const int Tt = T - 1;
+  const int t0 = (nch == 1) ? 0 : cc * LOC_CHUNK;
+  const int t1 = (nch == 1) ? Tt : min(Tt, t0 + LOC_CHUNK);
+  const double* fw_n = fw + (size_t)n * T * (1 + DK);
+  const float* mk = mask + (size_t)n * T;
+  const float* w_n = w + (size_t)n * Tt * DK;
+  const double iq = 1.0 / q;
+  if (cc == 0 && loglik != nullptr) {
+    double s = 0.0;
+    for (int c = 0; c < nch; c++) s += llpart[(size_t)n * nch + c];
+    loglik[n] = s;
+  }
+  int ts = t1;
+  bool exact = true;
+  if (cc < nch - 1) {
+    ts = min(Tt, t1 + LOC_BURN);
+    exact = (ts == Tt) || !(mk[ts] > 0.0f);
+  }
+  double xv[DK];
+#pragma unroll
+  for (int d = 0; d < DK; d++) xv[d] = exact ? fw_n[(size_t)(T - 1) * (1 + DK) + 1 + d] : 0.0;
+  for (int tbk = ts - 1; tbk >= t0; tbk -= LOC_UNROLL) {
     double Lc[LOC_UNROLL], ec[LOC_UNROLL][DK];
     float wv[LOC_UNROLL][DK], m[LOC_UNROLL];
 #pragma unroll
     for (int i = 0; i < LOC_UNROLL; i++) {
-      const int t = tb - i;
+      const int t = tbk - i;
       m[i] = 0.0f;
-      if (t >= 0) {
+      if (t >= t0) {
         m[i] = mk[t];
         if (m[i] > 0.0f) {
           const double* o = fw_n + (size_t)t * (1 + DK);
@@ -460,16 +528,16 @@ __global__ void __launch_bounds__(32)
     }
 #pragma unroll
     for (int i = 0; i < LOC_UNROLL; i++) {
-      const int t = tb - i;
-      if (t >= 0) {
+      const int t = tbk - i;
+      if (t >= t0) {
         if (m[i] > 0.0f) {
 #pragma unroll
           for (int d = 0; d < DK; d++) {
             const double hh = fma(xv[d], iq, ec[i][d]);
             xv[d] = Lc[i] * fma(Lc[i], hh, (double)wv[i][d]);
-            v_out[((size_t)n * T + t) * DK + d] = (float)xv[d];
+            if (t < t1) v_out[((size_t)n * T + t) * DK + d] = (float)xv[d];
           }
-        } else {
+        } else if (t < t1) {
 #pragma unroll
           for (int d = 0; d < DK; d++) v_out[((size_t)n * T + t) * DK + d] = 0.0f;  // kalman.py:142-143
         }
@@ -503,12 +571,28 @@ extern "C" int kpms_resample_location(const float* Y, const float* mask, const f
                                                                            sigmasq, dm, stats);
   rc = kpms_last_launch();
   if (rc) return rc;
-  const unsigned grid = (unsigned)((N + 31) / 32);
-  if (dk == 2)
-    location_sample_kernel<2><<<grid, 32, 0, st>>>(stats, mask, w, w_last, sigmasq_loc, N, T, fw,
-                                                   v_out, loglik);
-  else
-    location_sample_kernel<3><<<grid, 32, 0, st>>>(stats, mask, w, w_last, sigmasq_loc, N, T, fw,
-                                                   v_out, loglik);
+  char* p2 = (char*)fw + kpms_round_up((size_t)N * T * (1 + dk) * sizeof(double), 256);
+  double* llpart = (double*)p2;
+  const int nch = loc_nchunks(T);
+  int* tv = (int*)(p2 + kpms_round_up((size_t)N * nch * sizeof(double), 256));
+  location_tv_kernel<<<N, 128, 0, st>>>(mask, T, tv);
+  rc = kpms_last_launch();
+  if (rc) return rc;
+  const unsigned grid = (unsigned)((N * nch + 63) / 64);
+  if (dk == 2) {
+    location_forward_kernel<2><<<grid, 64, 0, st>>>(stats, mask, w_last, tv, sigmasq_loc, N, T,
+                                                    loglik != nullptr, fw, llpart, v_out);
+    rc = kpms_last_launch();
+    if (rc) return rc;
+    location_backward_kernel<2><<<grid, 64, 0, st>>>(fw, mask, w, sigmasq_loc, N, T, llpart, v_out,
+                                                     loglik);
+  } else {
+    location_forward_kernel<3><<<grid, 64, 0, st>>>(stats, mask, w_last, tv, sigmasq_loc, N, T,
+                                                    loglik != nullptr, fw, llpart, v_out);
+    rc = kpms_last_launch();
+    if (rc) return rc;
+    location_backward_kernel<3><<<grid, 64, 0, st>>>(fw, mask, w, sigmasq_loc, N, T, llpart, v_out,
+                                                     loglik);
+  }
   return kpms_last_launch();
 }

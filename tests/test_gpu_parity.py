@@ -345,3 +345,30 @@ def test_cpu_tensor_is_rejected(G):
     from keypointmoseq_b200._lib import KpmsError
     with pytest.raises(KpmsError):
         G.ar_log_likelihood(x=torch.zeros(1, 10, 10), Ab=torch.zeros(2, 10, 31), Q=torch.eye(10).repeat(2, 1, 1))
+
+
+def test_location_chunked_long_sequence(G):
+    """T > 256 exercises the chunk-parallel location sampler (warm-up 128 steps)."""
+    N, T, k, dk, D, L, K = 3, 900, 8, 2, 10, 3, 4
+    d, s, p, Gm = H.problem(seed=61, N=N, T=T, k=k, dk=dk, D=D, L=L, K=K, ragged=True)
+    rng = np.random.default_rng(3)
+    w = H.f32r(rng.standard_normal((N, T - 1, dk)))
+    wl = H.f32r(rng.standard_normal((N, dk)))
+    oc = dict(Y=d['Y'], mask=d['mask'], v=s['v'], h=s['h'], x=s['x'], s=s['s'], Cd=p['Cd'], sigmasq=p['sigmasq'], Gamma=Gm)
+    vo, llo = O.resample_location(**oc, sigmasq_loc=0.5, w=w, w_last=wl, return_loglik=True)
+    vv, info = G.resample_location(0, **{a: T_(b) for a, b in oc.items()}, sigmasq_loc=0.5,
+                                   draws={'w': T_(w), 'w_last': T_(wl)}, return_info=True)
+    vv = N_(vv).astype(np.float64)
+    assert np.abs(vv - vo).max() < 3e-7 * max(1.0, np.abs(vo).max())
+    assert np.all(np.abs(N_(info['loglik']) - llo) <= 1e-9 * np.abs(llo))
+
+
+def test_hmm_long_sequence_bench_shape(G):
+    """K=100 at a few thousand frames: marginal log-likelihood and state agreement at scale."""
+    ll, mask, pi, u = _hmm_case(7, N=3, T=6000, K=100, ragged=True)
+    zo, lo = O._hmm_batch(ll, mask, pi, u)
+    z, lg = G.sample_hmm_stateseqs(ll=T_(ll), mask=T_(mask), pi=T_(pi), u=T_(u))
+    z, lg = N_(z), N_(lg)
+    assert np.all(np.abs(lg - lo) <= 1e-5 * np.abs(lo))
+    valid = mask > 0
+    assert (z[valid] == zo[valid]).mean() >= 0.999

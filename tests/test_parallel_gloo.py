@@ -1,0 +1,85 @@
+"""Multi-process host logic on CPU (gloo, world_size 2): session sharding, the packed
+sufficient-statistic all-reduce of `parallel.gibbs_sweep`, and replicated parameter draws.
+The per-shard statistics come from the oracle here (no GPU in this test); on the GPU box the
+same pack/all_reduce/unpack code runs on the kernels' outputs over NCCL."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as td
+import torch.multiprocessing as mp
+
+import kpms_helpers as H
+from oracle import kpms_oracle as O
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _local_stats(d, s, p, Gm, L, K, lo, hi):
+    sl = slice(lo, hi)
+    F = O.ar_sufficient_stats(nlags=L, num_states=K, mask=d['mask'][sl], x=s['x'][sl], z=s['z'][sl])
+    S_y, msum = O.obs_variance_stats(Y=d['Y'][sl], mask=d['mask'][sl], Cd=p['Cd'], v=s['v'][sl], h=s['h'][sl],
+                                     x=s['x'][sl], s=s['s'][sl], Gamma=Gm)
+    counts = O.count_transitions(K, d['mask'][sl][:, -s['z'].shape[1]:], s['z'][sl])
+    t = torch.as_tensor
+    return t(F), t(S_y), t(np.array([msum])), t(counts.astype(np.int64))
+
+
+def _worker(rank, world, port, out):
+    from keypointmoseq_b200 import gibbs as G, parallel
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    td.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        N, T, k, D, L, K = 5, 60, 6, 10, 3, 4
+        d, s, p, Gm = H.problem(seed=9, N=N, T=T, k=k, D=D, L=L, K=K, ragged=True)
+        hp = H.hyp(D, L, K)
+        lo, hi = parallel.shard_range(N, rank, world)
+        F, S_y, msum, counts = _local_stats(d, s, p, Gm, L, K, lo, hi)
+        buf = parallel.pack_stats(F, S_y, msum, counts)
+        td.all_reduce(buf, op=td.ReduceOp.SUM)
+        F2, S2, m2, c2 = parallel.unpack_stats(buf, K, F.shape[1], k)
+        Ab, Q = G.sample_ar_params((3, 1), F2, nlags=L, nu_0=hp['nu_0'], S_0=torch.as_tensor(hp['S_0']),
+                                   M_0=torch.as_tensor(hp['M_0']), K_0=torch.as_tensor(hp['K_0']))
+        sig = G.sample_obs_variance((3, 1), S2, m2, nu_sigma=hp['nu_sigma'], sigmasq_0=hp['sigmasq_0'])
+        gathered = [torch.zeros_like(Ab) for _ in range(world)]
+        td.all_gather(gathered, Ab)
+        if rank == 0:
+            Ff, Sf, mf, cf = _local_stats(d, s, p, Gm, L, K, 0, N)
+            out.put(dict(F_err=float((F2 - Ff).abs().max() / Ff.abs().max()), S_err=float((S2 - Sf).abs().max()),
+                         m_ok=bool(torch.equal(m2, mf)), c_ok=bool(torch.equal(c2, cf)),
+                         same_params=bool(all(torch.equal(g, Ab) for g in gathered)),
+                         finite=bool(torch.isfinite(Ab).all() and torch.isfinite(Q).all() and (sig > 0).all())))
+    finally:
+        td.destroy_process_group()
+
+
+def test_shard_range_partitions_sessions():
+    from keypointmoseq_b200 import parallel
+    for n, w in [(1000, 8), (125, 8), (5, 2), (3, 4)]:
+        spans = [parallel.shard_range(n, r, w) for r in range(w)]
+        assert spans[0][0] == 0 and spans[-1][1] == n
+        assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+        sizes = [b - a for a, b in spans]
+        assert max(sizes) - min(sizes) <= 1
+
+
+def test_packed_allreduce_and_replicated_draws_gloo():
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = out.get(timeout=300)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert res["F_err"] < 1e-13 and res["S_err"] < 1e-9
+    assert res["m_ok"] and res["c_ok"] and res["same_params"] and res["finite"]
