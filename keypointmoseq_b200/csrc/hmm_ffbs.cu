@@ -13,6 +13,7 @@
 #include "common.cuh"
 
 #define HMM_RING 8
+#define HMM_STAGE 16   // frames staged ahead by the backward sampler
 
 extern "C" size_t kpms_hmm_ffbs_workspace_bytes(int N, int Tm, int K) {
   if (N <= 0 || Tm <= 0 || K <= 0) return 0;
@@ -48,142 +49,169 @@ __global__ void __launch_bounds__(KP)
   int* z_n = z + (size_t)n * Tm;
 
   // ------------------------------------------------------------------ forward
-  float ring[HMM_RING];
-#pragma unroll
-  for (int i = 0; i < HMM_RING; i++)
-    ring[i] = (j < K && i < Tm) ? ll_n[(size_t)i * K + j] : -INFINITY;
-  {
-    float wm = warp_max_f(ring[0]);
-    if (lane == 0) wmax_s[0][warp] = wm;
+  // ll rows (and the mask) are staged HMM_STAGE frames ahead into shared memory with cp.async:
+  // thread j copies and later reads only its own elements, so the staging needs no barrier, and
+  // unlike a register ring it does not serialise on the six scoreboard slots.
+  float* stage = piT + KP * KP;              // [HMM_STAGE][KP]  ll rows (alphan rows in the backward pass)
+  float* mstage = stage + HMM_STAGE * KP;    // [HMM_STAGE][KP]  per-thread copy of the mask
+  float* um = mstage + HMM_STAGE * KP;       // [HMM_STAGE][2]   backward: u, mask
+  float* lt = um + HMM_STAGE * 2;            // [32]             backward: lane totals
+  const unsigned stage_sa = (unsigned)__cvta_generic_to_shared(stage);
+  const unsigned mstage_sa = (unsigned)__cvta_generic_to_shared(mstage);
+  const unsigned um_sa = (unsigned)__cvta_generic_to_shared(um);
+  auto issue_f = [&](int t) {
+    if (t < Tm) {
+      const int slot = t % HMM_STAGE;
+      if (j < K) {
+        const float* src = ll_n + (size_t)t * K + j;
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(stage_sa + (unsigned)((slot * KP + j) * 4)), "l"(src));
+      }
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(mstage_sa + (unsigned)((slot * KP + j) * 4)), "l"(mk_n + t));
+    }
+    asm volatile("cp.async.commit_group;\n" ::);
+  };
+#pragma unroll 1
+  for (int i = 0; i < HMM_STAGE; i++) issue_f(i);
+  asm volatile("cp.async.wait_group %0;\n" ::"n"(HMM_STAGE - 2));
+  {  // maxima of frames 0 and 1; afterwards frame t+2 is reduced during frame t
+    const float l0 = (j < K) ? stage[j] : -INFINITY;
+    const float l1 = (j < K && Tm > 1) ? stage[KP + j] : -INFINITY;
+    const float wm0 = warp_max_f(l0), wm1 = warp_max_f(l1);
+    if (lane == 0) {
+      wmax_s[0][warp] = wm0;
+      wmax_s[1][warp] = wm1;
+    }
   }
   __syncthreads();
   float in_pot = (j < K) ? 1.0f / (float)K : 0.0f;
   double logtot = 0.0;
-  for (int tb = 0; tb < Tm; tb += HMM_RING) {
+#pragma unroll 1
+  for (int t = 0; t < Tm; t++) {
+    const int buf = t & 1, slot = t % HMM_STAGE;
+    float cmax = wmax_s[buf][0];
 #pragma unroll
-    for (int i = 0; i < HMM_RING; i++) {
-      const int t = tb + i;
-      if (t < Tm) {  // uniform
-        const int buf = t & 1;
-        float cmax = wmax_s[buf][0];
-#pragma unroll
-        for (int w = 1; w < NW; w++) cmax = fmaxf(cmax, wmax_s[buf][w]);
-        const float llv = ring[i];
-        const float a = (j < K) ? in_pot * expf(llv - cmax) : 0.0f;
-        a_s[buf][j] = a;
-        const float m = mk_n[t];
-        // next frame's max, one frame ahead (ring[(i+1)%RING] already holds ll[t+1])
-        {
-          const float nxt = ring[(i + 1) % HMM_RING];
-          float wm = warp_max_f(nxt);
-          if (lane == 0) wmax_s[buf ^ 1][warp] = wm;
-        }
-        // refill this ring slot with ll[t+RING]
-        ring[i] = (j < K && t + HMM_RING < Tm) ? ll_n[(size_t)(t + HMM_RING) * K + j] : -INFINITY;
-        __syncthreads();
-        // normaliser: every warp reduces the KP shared values itself (identical order in
-        // every warp, so all threads agree bit-for-bit); the shuffles overlap the FMA stream
-        float part = 0.0f;
-#pragma unroll
-        for (int q = 0; q < NW; q++) part += a_s[buf][lane + 32 * q];
-        float acc[8];
-#pragma unroll
-        for (int q = 0; q < 8; q++) acc[q] = 0.0f;
-        const float4* av = reinterpret_cast<const float4*>(a_s[buf]);
-#pragma unroll
-        for (int q = 0; q < KP / 4; q++) {
-          const float4 v = av[q];
-          acc[(4 * q + 0) & 7] = fmaf(v.x, pcol[4 * q + 0], acc[(4 * q + 0) & 7]);
-          acc[(4 * q + 1) & 7] = fmaf(v.y, pcol[4 * q + 1], acc[(4 * q + 1) & 7]);
-          acc[(4 * q + 2) & 7] = fmaf(v.z, pcol[4 * q + 2], acc[(4 * q + 2) & 7]);
-          acc[(4 * q + 3) & 7] = fmaf(v.w, pcol[4 * q + 3], acc[(4 * q + 3) & 7]);
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-        const float acc0 = (acc[0] + acc[1]) + (acc[2] + acc[3]);
-        const float acc1 = (acc[4] + acc[5]) + (acc[6] + acc[7]);
-        const float s0 = part, s1 = 0.0f;
-        const float norm = (s0 + s1) + 1e-16f;
-        const float inv = 1.0f / norm;
-        if (j < K) al_n[(size_t)t * K + j] = a * inv;
-        if (m > 0.0f) in_pot = (acc0 + acc1) * inv;
-        if (j == 0 && m > 0.0f) logtot += (double)logf(norm) + (double)cmax;
-      }
+    for (int w = 1; w < NW; w++) cmax = fmaxf(cmax, wmax_s[buf][w]);
+    asm volatile("cp.async.wait_group %0;\n" ::"n"(HMM_STAGE - 3));  // frames <= t+2 have landed
+    const float llv = (j < K) ? stage[slot * KP + j] : -INFINITY;
+    const float m = mstage[slot * KP + j];
+    const float a = (j < K) ? in_pot * expf(llv - cmax) : 0.0f;
+    a_s[buf][j] = a;
+    const float nxt2 = (j < K && t + 2 < Tm) ? stage[((t + 2) % HMM_STAGE) * KP + j] : -INFINITY;
+    issue_f(t + HMM_STAGE);  // refills the slot this thread has just read
+    __syncthreads();
+    // max of frame t+2, written after this frame's barrier into the slot this frame has just
+    // finished reading and read two barriers later: the shuffle chain overlaps the FMA stream
+    {
+      const float wm = warp_max_f(nxt2);
+      if (lane == 0) wmax_s[buf][warp] = wm;
     }
+    // mat-vec and normaliser from the same shared values; 8 + 8 independent chains
+    float acc[8], sm8[8];
+#pragma unroll
+    for (int q = 0; q < 8; q++) acc[q] = 0.0f, sm8[q] = 0.0f;
+    const float4* av = reinterpret_cast<const float4*>(a_s[buf]);
+#pragma unroll
+    for (int q = 0; q < KP / 4; q++) {
+      const float4 v = av[q];
+      acc[(4 * q + 0) & 7] = fmaf(v.x, pcol[4 * q + 0], acc[(4 * q + 0) & 7]);
+      acc[(4 * q + 1) & 7] = fmaf(v.y, pcol[4 * q + 1], acc[(4 * q + 1) & 7]);
+      acc[(4 * q + 2) & 7] = fmaf(v.z, pcol[4 * q + 2], acc[(4 * q + 2) & 7]);
+      acc[(4 * q + 3) & 7] = fmaf(v.w, pcol[4 * q + 3], acc[(4 * q + 3) & 7]);
+      sm8[(4 * q + 0) & 7] += v.x;
+      sm8[(4 * q + 1) & 7] += v.y;
+      sm8[(4 * q + 2) & 7] += v.z;
+      sm8[(4 * q + 3) & 7] += v.w;
+    }
+    const float acc0 = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+    const float acc1 = (acc[4] + acc[5]) + (acc[6] + acc[7]);
+    const float s0 = (sm8[0] + sm8[1]) + (sm8[2] + sm8[3]);
+    const float s1 = (sm8[4] + sm8[5]) + (sm8[6] + sm8[7]);
+    const float norm = (s0 + s1) + 1e-16f;
+    const float inv = 1.0f / norm;
+    if (j < K) al_n[(size_t)t * K + j] = a * inv;
+    if (m > 0.0f) in_pot = (acc0 + acc1) * inv;
+    if (j == 0 && m > 0.0f) logtot += (double)__logf(norm) + (double)cmax;
   }
   if (j == 0 && loglik != nullptr) loglik[n] = logtot;
+  asm volatile("cp.async.wait_group 0;\n" ::);
   __syncthreads();  // alphan (global) written by this CTA is visible to warp 0 below
   if (warp != 0) return;
 
   // ------------------------------------------------------------------ backward (warp 0)
+  // alphan rows, u and mask are staged HMM_STAGE frames ahead into shared memory with
+  // cp.async (a register ring would serialise on the 6 scoreboard slots); the prefix sum over
+  // the 32 lane totals goes through shared memory (one store, 8 broadcast loads) because a
+  // 5-step shuffle scan costs ~400 cycles of dependent latency per frame; the sampled state
+  // is the number of states whose cumulative weight is <= u * total (4 ballots + popc).
   constexpr int PER = KP / 32;  // states per lane: lane owns states lane*PER .. lane*PER+PER-1
-  int s_next = -1;              // -1: next_potential = ones (distributions.py:76)
-  float aring[HMM_RING][PER];
-  float uring[HMM_RING], mring[HMM_RING];
+  static_assert(PER <= 4, "one 16-byte slot per lane");
+  auto issue = [&](int t) {  // copy frame t into its slot (t >= 0), then close the group
+    if (t >= 0) {
+      const int slot = t % HMM_STAGE;
 #pragma unroll
-  for (int i = 0; i < HMM_RING; i++) {
-    const int t = Tm - 1 - i;
-#pragma unroll
-    for (int e = 0; e < PER; e++) {
-      const int st = lane * PER + e;
-      aring[i][e] = (t >= 0 && st < K) ? al_n[(size_t)t * K + st] : 0.0f;
-    }
-    uring[i] = (t >= 0) ? u_n[t] : 0.0f;
-    mring[i] = (t >= 0) ? mk_n[t] : 0.0f;
-  }
-  for (int tb = Tm - 1; tb >= 0; tb -= HMM_RING) {
-#pragma unroll
-    for (int i = 0; i < HMM_RING; i++) {
-      const int t = tb - i;
-      if (t >= 0) {
-        int zt = 0;
-        if (mring[i] > 0.0f) {
-          float w[PER];
-          float run = 0.0f;
-#pragma unroll
-          for (int e = 0; e < PER; e++) {
-            const float np = (s_next < 0) ? 1.0f : piT[s_next * KP + lane * PER + e];
-            run += np * aring[i][e];
-            w[e] = run;  // inclusive prefix within the lane
-          }
-          float incl = run;  // inclusive scan of lane totals
-#pragma unroll
-          for (int o = 1; o < 32; o <<= 1) {
-            float v = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += v;
-          }
-          const float total = __shfl_sync(0xffffffffu, incl, 31);
-          const float thr = uring[i] * total;
-          const float excl = incl - run;
-          const unsigned bal = __ballot_sync(0xffffffffu, incl > thr);
-          int first = K - 1;
-          if (bal != 0u) {
-            const int fl = __ffs(bal) - 1;
-            int cand = K - 1;
-            if (lane == fl) {
-              cand = lane * PER + PER - 1;
-#pragma unroll
-              for (int e = PER - 1; e >= 0; e--)
-                if (excl + w[e] > thr) cand = lane * PER + e;
-            }
-            first = __shfl_sync(0xffffffffu, cand, fl);
-          }
-          zt = min(first, K - 1);
-          s_next = zt;
+      for (int e = 0; e < PER; e++) {
+        const int st = lane * PER + e;
+        if (st < K) {
+          const float* src = al_n + (size_t)t * K + st;
+          const unsigned dst = stage_sa + (unsigned)((slot * KP + st) * 4);
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(src));
         }
-        if (lane == 0) z_n[t] = zt;
-        // refill
-        const int tn = t - HMM_RING;
-#pragma unroll
-        for (int e = 0; e < PER; e++) {
-          const int st = lane * PER + e;
-          aring[i][e] = (tn >= 0 && st < K) ? al_n[(size_t)tn * K + st] : 0.0f;
-        }
-        uring[i] = (tn >= 0) ? u_n[tn] : 0.0f;
-        mring[i] = (tn >= 0) ? mk_n[tn] : 0.0f;
+      }
+      if (lane < 2) {
+        const float* src = (lane == 0) ? (u_n + t) : (mk_n + t);
+        const unsigned dst = um_sa + (unsigned)((slot * 2 + lane) * 4);
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(src));
       }
     }
+    asm volatile("cp.async.commit_group;\n" ::);
+  };
+  for (int e = lane; e < HMM_STAGE * KP; e += 32) stage[e] = 0.0f;  // padded states stay 0
+  __syncwarp();
+#pragma unroll 1
+  for (int i = 0; i < HMM_STAGE; i++) issue(Tm - 1 - i);
+  int s_next = -1;  // -1: next_potential = ones (distributions.py:76)
+#pragma unroll 1
+  for (int t = Tm - 1; t >= 0; t--) {
+    asm volatile("cp.async.wait_group %0;\n" ::"n"(HMM_STAGE - 1));
+    __syncwarp();
+    const int slot = t % HMM_STAGE;
+    const float uu = um[slot * 2 + 0], mm = um[slot * 2 + 1];
+    int zt = 0;
+    if (mm > 0.0f) {
+      float w[PER];
+      float run = 0.0f;
+#pragma unroll
+      for (int e = 0; e < PER; e++) {
+        const float np = (s_next < 0) ? 1.0f : piT[s_next * KP + lane * PER + e];
+        run = fmaf(np, stage[slot * KP + lane * PER + e], run);
+        w[e] = run;  // inclusive prefix within the lane
+      }
+      lt[lane] = run;
+      __syncwarp();
+      // exclusive prefix over lane totals: 8 group sums of 4 lanes, then the part of the own group
+      const int grp = lane >> 2, sub = lane & 3;
+      float excl = 0.0f, total = 0.0f;
+#pragma unroll
+      for (int q = 0; q < 8; q++) {
+        const float4 v = reinterpret_cast<const float4*>(lt)[q];
+        const float g4 = (v.x + v.y) + (v.z + v.w);
+        const float own = ((sub > 0) ? v.x : 0.0f) + ((sub > 1) ? v.y : 0.0f) + ((sub > 2) ? v.z : 0.0f);
+        excl += (q < grp) ? g4 : ((q == grp) ? own : 0.0f);
+        total += g4;
+      }
+      const float thr = uu * total;
+      int cnt = 0;
+#pragma unroll
+      for (int e = 0; e < PER; e++)
+        cnt += __popc(__ballot_sync(0xffffffffu, !(excl + w[e] > thr)));
+      zt = min(cnt, K - 1);
+      s_next = zt;
+    }
+    if (lane == 0) z_n[t] = zt;
+    __syncwarp();  // every lane is done with this slot and with lt
+    issue(t - HMM_STAGE);
   }
+  asm volatile("cp.async.wait_group 0;\n" ::);
 }
 
 // Generic kernel for K > 128 (K <= 1024): thread j owns state j, pi / pi^T in fp32 in global
@@ -286,7 +314,7 @@ static int launch_reg(const float* ll, const float* mask, long long ms, const do
                       const float* u, int N, int Tm, int K, int* z, double* loglik, float* alphan,
                       cudaStream_t st) {
   auto kern = hmm_ffbs_reg_kernel<KP>;
-  const size_t smem = (size_t)KP * KP * sizeof(float);
+  const size_t smem = (size_t)(KP * KP + 2 * HMM_STAGE * KP + HMM_STAGE * 2 + 32) * sizeof(float);
   KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kern<<<N, KP, smem, st>>>(ll, mask, ms, pi, u, Tm, K, z, loglik, alphan);
   return kpms_last_launch();
