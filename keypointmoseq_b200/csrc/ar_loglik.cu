@@ -15,11 +15,14 @@
 
 static inline int ar_pp(int D, int L) { return (D * L + D + 1 + 3) / 4 * 4; }
 
-// workspace: [Wf: K*D*PP f32][cst: K f32]
+size_t kpms_ar_tc_tile_bytes(int K, int D, int L);  // ar_loglik_tc.cu
+
+// workspace: [Wf: K*D*PP f32][cst: K f32][TF32 hi/lo weight tiles of the tensor-core kernel]
 extern "C" size_t kpms_ar_loglik_workspace_bytes(int K, int D, int L) {
   if (K <= 0 || D <= 0 || L <= 0) return 0;
   size_t w = (size_t)K * D * ar_pp(D, L) * sizeof(float);
-  return kpms_round_up(w, 256) + kpms_round_up((size_t)K * sizeof(float), 256);
+  return kpms_round_up(w, 256) + kpms_round_up((size_t)K * sizeof(float), 256) +
+         kpms_ar_tc_tile_bytes(K, D, L);
 }
 
 // One warp per state: lane 0 factors Q_k, then the P columns of W_k are solved in parallel.
@@ -138,7 +141,7 @@ static int launch_simt(const float* x, const float* Wf, const float* cst, int N,
 }
 
 int kpms_ar_loglik_tc(const float* x, const float* Wf, const float* cst, int N, int T, int D, int L,
-                      int K, float* ll, cudaStream_t st);  // ar_loglik_tc.cu
+                      int K, float* ll, void* tiles, size_t tile_bytes, cudaStream_t st);  // ar_loglik_tc.cu
 
 extern "C" int kpms_ar_loglik(const float* x, const double* Ab, const double* Q, int N, int T,
                               int D, int L, int K, float* ll, void* workspace,
@@ -153,11 +156,12 @@ extern "C" int kpms_ar_loglik(const float* x, const double* Ab, const double* Q,
   const int PP = ar_pp(D, L);
   float* Wf = (float*)workspace;
   float* cst = (float*)((char*)workspace + kpms_round_up((size_t)K * D * PP * sizeof(float), 256));
+  void* tiles = (char*)cst + kpms_round_up((size_t)K * sizeof(float), 256);
   ar_prepare_kernel<<<K, 32, 0, st>>>(Ab, Q, D, L, PP, Wf, cst);
   int rc = kpms_last_launch();
   if (rc) return rc;
   if (impl == 0) {
-    rc = kpms_ar_loglik_tc(x, Wf, cst, N, T, D, L, K, ll, st);
+    rc = kpms_ar_loglik_tc(x, Wf, cst, N, T, D, L, K, ll, tiles, kpms_ar_tc_tile_bytes(K, D, L), st);
     if (rc != KPMS_ERR_UNSUPPORTED) return rc;
   }
 #define KPMS_X(d, l) \
@@ -241,7 +245,13 @@ extern "C" int kpms_ar_loglik_static(const float* x, const double* Ab, const dou
   rc = kpms_last_launch();
   if (rc) return rc;
   if (impl == 0) {
-    rc = kpms_ar_loglik_tc(x, Wf, cst, N, T, D, L, K, ll, st);
+    // the tensor-core kernel wants room for its packed TF32 tiles; what is left of the fixed
+    // array after the fp32 weights is offered, and when that is too small (more than a few
+    // dozen states) the CUDA-core kernel computes the same result
+    float* tiles = cst + kpms_round_up((size_t)K, 64);
+    const size_t used = (size_t)(tiles - base);
+    const size_t left = used < (size_t)KPMS_AR_STATIC_FLOATS ? ((size_t)KPMS_AR_STATIC_FLOATS - used) * sizeof(float) : 0;
+    rc = kpms_ar_loglik_tc(x, Wf, cst, N, T, D, L, K, ll, tiles, left, st);
     if (rc != KPMS_ERR_UNSUPPORTED) return rc;
   }
 #define KPMS_X(d, l) \

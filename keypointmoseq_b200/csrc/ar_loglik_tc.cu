@@ -1,6 +1,270 @@
-// tcgen05 3xTF32 emission kernel (placeholder until the tensor-core path lands).
+// a1 on the 5th-generation tensor cores: tcgen05.mma kind::tf32, 3xTF32 split, FP32 accumulators
+// in TMEM.  Reference: gibbs.py:100-104,110 (the (frames x (D*L+1)) . ((D*L+1) x D) contraction per
+// state) + tfd.MultivariateNormalFullCovariance.log_prob.
+//
+//   D[frame, k*DD+d] = sum_p  f[frame, p] * W[k, d, p]        (M = 128 frames, N = 16 states * DD,
+//   ll[frame, k]     = cst[k] - 1/2 sum_d D[frame, k*DD+d]^2    contraction KD = round_up(P, 8))
+//
+// Work split: CTA (tile, stripe) keeps ONE weight tile (16 states; hi and lo TF32 parts, packed by
+// ar_tc_pack_kernel in the UMMA K-major no-swizzle layout) resident in shared memory for the whole
+// launch and walks its stripe of 128-frame blocks: build the A tile (lag window of x read in place,
+// hi/lo split) -> 3 x KD/8 tcgen05.mma into TMEM -> tcgen05.ld epilogue: each thread owns one
+// frame row, squares and group-sums DD consecutive columns per state, adds the constant, stores.
+// The weights are never re-read from L2/HBM and x is read once per weight tile.
+//
+// UMMA K-major no-swizzle layout (16-byte units): element (row r, k) lives at
+//   (r / 8) * SBO + (k / 4) * LBO + (r % 8) * 16 + (k % 4) * 4   bytes,  LBO = 128, SBO = (KD/4)*128.
 #include "common.cuh"
-int kpms_ar_loglik_tc(const float*, const float*, const float*, int, int, int, int, int, float*,
-                      cudaStream_t) {
+#include "dispatch.cuh"
+
+#define TC_STATES 16   // states per weight tile
+#define TC_M 128       // frames per block (UMMA M)
+
+template <int DD, int LL>
+struct TC {
+  static constexpr int P = DD * LL + DD + 1;
+  static constexpr int PP = (P + 3) / 4 * 4;       // row length of the fp32 weights (ar_prepare_kernel)
+  static constexpr int KD = (P + 7) / 8 * 8;       // contraction length, multiple of the UMMA K (8 for tf32)
+  static constexpr int KC = KD / 4;                // 16-byte chunks along K
+  static constexpr int LBO = 128;
+  static constexpr int SBO = KC * 128;
+  static constexpr int N = TC_STATES * DD;         // UMMA N (multiple of 16, <= 256 for DD <= 16)
+  static constexpr int A_BYTES = (TC_M / 8) * SBO;
+  static constexpr int B_BYTES = (N / 8) * SBO;
+  static constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) |
+                                    ((uint32_t)(TC_M >> 4) << 24);  // F32 accum, TF32 x TF32, K-major both
+  static_assert(N % 16 == 0 && N <= 256, "invalid UMMA N");
+};
+
+__device__ __forceinline__ uint32_t tf32_rna(float v) {
+  uint32_t u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v));
+  return u;
+}
+
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;  // descriptor version (Blackwell)
+  return d;                 // base offset 0, layout type 0 = no swizzle
+}
+
+// Pack the fp32 whitened weights into per-tile hi / lo TF32 operands in the UMMA layout.
+template <int DD, int LL>
+__global__ void ar_tc_pack_kernel(const float* __restrict__ Wf, int K, unsigned char* __restrict__ tiles) {
+  using C = TC<DD, LL>;
+  const int tile = blockIdx.x;
+  unsigned char* base = tiles + (size_t)tile * 2 * C::B_BYTES;
+  for (int e = threadIdx.x; e < C::N * C::KD; e += blockDim.x) {
+    const int n = e / C::KD, p = e % C::KD;
+    const int k = tile * TC_STATES + n / DD, d = n % DD;
+    const float v = (k < K && p < C::PP) ? Wf[((size_t)k * DD + d) * C::PP + p] : 0.0f;
+    const uint32_t hi = tf32_rna(v);
+    const uint32_t lo = tf32_rna(v - __uint_as_float(hi));
+    const size_t off = (size_t)(n / 8) * C::SBO + (size_t)(p / 4) * C::LBO + (n % 8) * 16 + (p % 4) * 4;
+    *reinterpret_cast<uint32_t*>(base + off) = hi;
+    *reinterpret_cast<uint32_t*>(base + C::B_BYTES + off) = lo;
+  }
+}
+
+template <int DD, int LL>
+__global__ void __launch_bounds__(TC_M, 1)
+    ar_loglik_tc_kernel(const float* __restrict__ x, const unsigned char* __restrict__ tiles,
+                        const float* __restrict__ cst, int N, int T, int K, int nstripes,
+                        float* __restrict__ ll) {
+  using C = TC<DD, LL>;
+  extern __shared__ __align__(1024) unsigned char smem[];
+  unsigned char* sA_hi = smem;
+  unsigned char* sA_lo = sA_hi + C::A_BYTES;
+  unsigned char* sB_hi = sA_lo + C::A_BYTES;
+  unsigned char* sB_lo = sB_hi + C::B_BYTES;
+  float* s_cst = reinterpret_cast<float*>(sB_lo + C::B_BYTES);                    // TC_STATES
+  uint64_t* mbar = reinterpret_cast<uint64_t*>(s_cst + TC_STATES);                // 8-byte aligned
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mbar + 1);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tile = blockIdx.x, stripe = blockIdx.y;
+  const int k0 = tile * TC_STATES;
+  const int Tm = T - LL;
+  const long long frames = (long long)N * Tm;
+  const long long nblk = (frames + TC_M - 1) / TC_M;
+
+  // ---- one-time setup: weight tile, constants, barrier, tensor memory
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(tiles + (size_t)tile * 2 * C::B_BYTES);
+    uint4* dst = reinterpret_cast<uint4*>(sB_hi);
+    for (int i = tid; i < 2 * C::B_BYTES / 16; i += TC_M) dst[i] = src[i];
+    if (tid < TC_STATES) s_cst[tid] = (k0 + tid < K) ? cst[k0 + tid] : 0.0f;
+  }
+  const uint32_t mbar_sa = (uint32_t)__cvta_generic_to_shared(mbar);
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(mbar_sa));
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::);
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;\n" ::"r"(
+        (uint32_t)__cvta_generic_to_shared(tmem_slot)));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::);
+  }
+  asm volatile("fence.proxy.async.shared::cta;\n" ::);  // weight tile written with generic stores
+  asm volatile("tcgen05.fence::before_thread_sync;\n" ::);
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;\n" ::);
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t a_hi_sa = (uint32_t)__cvta_generic_to_shared(sA_hi);
+  const uint32_t a_lo_sa = (uint32_t)__cvta_generic_to_shared(sA_lo);
+  const uint32_t b_hi_sa = (uint32_t)__cvta_generic_to_shared(sB_hi);
+  const uint32_t b_lo_sa = (uint32_t)__cvta_generic_to_shared(sB_lo);
+  uint32_t parity = 0;
+
+  for (long long blk = stripe; blk < nblk; blk += nstripes) {
+    // ---- A tile: thread r builds row r = frame blk*128 + r (hi and lo parts)
+    const long long g = blk * TC_M + tid;
+    const bool live = g < frames;
+    {
+      const float* xp = x;
+      if (live) {
+        const int n = (int)(g / Tm), tp = (int)(g % Tm);
+        xp = x + ((size_t)n * T + tp) * DD;  // lag window x[tp .. tp+L]: DL+DD contiguous floats
+      }
+      const size_t rowoff = (size_t)(tid / 8) * C::SBO + (tid % 8) * 16;
+#pragma unroll
+      for (int kc = 0; kc < C::KC; kc++) {
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+          const int p = kc * 4 + q;
+          float v = 0.0f;
+          if (live) {
+            if (p < DD * LL + DD) v = xp[p];
+            else if (p == C::P - 1) v = 1.0f;
+          }
+          hi[q] = tf32_rna(v);
+          lo[q] = tf32_rna(v - __uint_as_float(hi[q]));
+        }
+        *reinterpret_cast<uint4*>(sA_hi + rowoff + kc * C::LBO) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(sA_lo + rowoff + kc * C::LBO) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+      }
+    }
+    asm volatile("fence.proxy.async.shared::cta;\n" ::);
+    asm volatile("tcgen05.fence::before_thread_sync;\n" ::);
+    __syncthreads();
+    // ---- 3xTF32: hi*hi + hi*lo + lo*hi, KD/8 k-steps each, one elected thread issues
+    if (tid == 0) {
+      asm volatile("tcgen05.fence::after_thread_sync;\n" ::);
+      uint32_t acc = 0;
+#pragma unroll
+      for (int ks = 0; ks < C::KD / 8; ks++) {
+        const uint32_t koff = ks * 2 * C::LBO;
+        const uint64_t dah = umma_desc(a_hi_sa + koff, C::LBO, C::SBO), dal = umma_desc(a_lo_sa + koff, C::LBO, C::SBO);
+        const uint64_t dbh = umma_desc(b_hi_sa + koff, C::LBO, C::SBO), dbl = umma_desc(b_lo_sa + koff, C::LBO, C::SBO);
+#pragma unroll
+        for (int term = 0; term < 3; term++) {
+          const uint64_t da = (term == 2) ? dal : dah;
+          const uint64_t db = (term == 1) ? dbl : dbh;
+          asm volatile(
+              "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+              "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem_base),
+              "l"(da), "l"(db), "r"(C::IDESC), "r"(acc));
+          acc = 1;
+        }
+      }
+      asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(mbar_sa));
+    }
+    // ---- wait for the accumulator
+    {
+      uint32_t done = 0;
+      while (!done) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}\n"
+            : "=r"(done)
+            : "r"(mbar_sa), "r"(parity));
+      }
+      parity ^= 1u;
+    }
+    asm volatile("tcgen05.fence::after_thread_sync;\n" ::);
+    // ---- epilogue: thread = frame row; warp w reads TMEM lanes 32w..32w+31
+    {
+      float q[TC_STATES];
+#pragma unroll
+      for (int sidx = 0; sidx < TC_STATES; sidx++) q[sidx] = 0.0f;
+      const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16);
+#pragma unroll
+      for (int c0 = 0; c0 < C::N; c0 += 16) {
+        uint32_t r[16];
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, "
+            "%13, %14, %15}, [%16];\n"
+            : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+              "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+            : "r"(taddr + (uint32_t)c0));
+        asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::);
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+          const float v = __uint_as_float(r[i]);
+          q[(c0 + i) / DD] = fmaf(v, v, q[(c0 + i) / DD]);
+        }
+      }
+      if (live) {
+        float* out = ll + g * K + k0;
+        if ((K & 3) == 0 && k0 + TC_STATES <= K) {
+#pragma unroll
+          for (int s4 = 0; s4 < TC_STATES; s4 += 4)
+            *reinterpret_cast<float4*>(out + s4) =
+                make_float4(s_cst[s4] - 0.5f * q[s4], s_cst[s4 + 1] - 0.5f * q[s4 + 1],
+                            s_cst[s4 + 2] - 0.5f * q[s4 + 2], s_cst[s4 + 3] - 0.5f * q[s4 + 3]);
+        } else {
+#pragma unroll
+          for (int sidx = 0; sidx < TC_STATES; sidx++)
+            if (k0 + sidx < K) out[sidx] = s_cst[sidx] - 0.5f * q[sidx];
+        }
+      }
+    }
+    // the next block overwrites the A tile and the accumulator
+    asm volatile("tcgen05.fence::before_thread_sync;\n" ::);
+    __syncthreads();
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;\n" ::"r"(tmem_base));
+  }
+}
+
+size_t kpms_ar_tc_tile_bytes(int K, int D, int L) {
+  const int P = D * L + D + 1, KD = (P + 7) / 8 * 8, SBO = (KD / 4) * 128;
+  const int ntiles = (K + TC_STATES - 1) / TC_STATES;
+  return kpms_round_up((size_t)ntiles * 2 * ((TC_STATES * D) / 8) * SBO, 256);
+}
+
+template <int DD, int LL>
+static int launch_tc(const float* x, const float* Wf, const float* cst, int N, int T, int K, float* ll,
+                     unsigned char* tiles, cudaStream_t st) {
+  using C = TC<DD, LL>;
+  const int ntiles = (K + TC_STATES - 1) / TC_STATES;
+  ar_tc_pack_kernel<DD, LL><<<ntiles, 256, 0, st>>>(Wf, K, tiles);
+  int rc = kpms_last_launch();
+  if (rc) return rc;
+  const size_t smem = 1024 + 2 * C::A_BYTES + 2 * C::B_BYTES + TC_STATES * sizeof(float) + 16;
+  auto kern = ar_loglik_tc_kernel<DD, LL>;
+  KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const long long nblk = ((long long)N * (T - LL) + TC_M - 1) / TC_M;
+  long long stripes = 148 / ntiles;
+  if (stripes < 1) stripes = 1;
+  if (stripes > nblk) stripes = nblk;
+  if (ntiles > 65535) return KPMS_ERR_UNSUPPORTED;
+  kern<<<dim3(ntiles, (unsigned)stripes), TC_M, smem, st>>>(x, tiles, cst, N, T, K, (int)stripes, ll);
+  return kpms_last_launch();
+}
+
+// tiles == nullptr or too small -> KPMS_ERR_UNSUPPORTED (caller falls back to the CUDA-core kernel)
+int kpms_ar_loglik_tc(const float* x, const float* Wf, const float* cst, int N, int T, int D, int L,
+                      int K, float* ll, void* tiles, size_t tile_bytes, cudaStream_t st) {
+  if (tiles == nullptr || tile_bytes < kpms_ar_tc_tile_bytes(K, D, L) || !kpms_aligned(tiles, 256))
+    return KPMS_ERR_UNSUPPORTED;
+#define KPMS_X(d, l) \
+  if (D == d && L == l) return launch_tc<d, l>(x, Wf, cst, N, T, K, ll, (unsigned char*)tiles, st);
+  KPMS_FOR_EACH_DL(KPMS_X)
+#undef KPMS_X
   return KPMS_ERR_UNSUPPORTED;
 }
