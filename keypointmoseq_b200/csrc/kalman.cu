@@ -120,10 +120,10 @@ struct KW {  // packed per-state table + per-warp shared-memory layout of the wa
   static constexpr int QB = F + NN;            // DD
   static constexpr int SC = QB + DD;           // c_z, logdet Q_
   static constexpr int SIZE = (SC + 2 + 1) / 2 * 2;
-  static constexpr int RS = 32;                // row stride (doubles) of the M / L / T row buffers
+  static constexpr int RS = 36;                // row stride (doubles) of the 32-row M / L / T / Z buffers
   static constexpr int SM_MS = 0;
-  static constexpr int SM_LS = SM_MS + NN * RS;
-  static constexpr int SM_TAB = SM_LS + NN * RS;
+  static constexpr int SM_LS = SM_MS + 32 * RS;
+  static constexpr int SM_TAB = SM_LS + 32 * RS;
   static constexpr int SM_DV = SM_TAB + SIZE;
   static constexpr int SM_HV = SM_DV + 32;
   static constexpr int SM_TOTAL = SM_HV + 32;
@@ -597,6 +597,8 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 2)
   const int c = lane;
   const bool col = c < NN;
   const int ca = min(max(c - OFF, 0), DD - 1);  // clamped index into the D-blocks
+  for (int e = lane; e < 64 * RS; e += 32) S[e] = 0.0;  // zero padding of the 32 x 32 operands
+  __syncwarp();
 
   double Lp[NN];
 #pragma unroll
@@ -698,62 +700,109 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 2)
       if (col) fwp[Y::FW_ETA + c] = eta_c;
     }
     __syncwarp();
-    // ---- T = L^T Fcol : lane c < OFF: 100 e_{D+c}; OFF <= c < NN: column of F_D; lane NN: eta_c - f
-    double Tc[NN];
+    // ---- T = L^T [F | eta_c - f] and Lam_p' = Qinv_ - T^T T on the FP64 tensor cores
+    // (mma.sync m8n8k4.f64): operands are register fragments fetched once from the row buffers,
+    // so the n^3-type work no longer pays one broadcast load per FMA.
+    //   "K-fragment" of a row-major X: lane (g, qd) holds X[4*kq + qd][8*b + g]; it is both the
+    //   A operand (X^T tile) and the B operand (X tile) of a product X^T Y.
+    {
+      constexpr int NB = (NN + 1 + 7) / 8;   // 8-column blocks of T (NN columns of V and u)
+      constexpr int KQ = (NN + 3) / 4;       // 4-row chunks of the contraction
+      constexpr int RB = (NN + 7) / 8;       // 8-row blocks of T
+      constexpr int CB0 = OFF / 8;           // first column block that holds a dense column
+      const int g = lane >> 2, qd = lane & 3;
+      // dense column blocks of T by DMMA: T[:, 8cb..8cb+7] = L^T F[:, 8cb..]
+      double Tacc[RB][NB - CB0][2];
 #pragma unroll
-    for (int r = 0; r < NN; r++) Tc[r] = 0.0;
+      for (int rb = 0; rb < RB; rb++)
 #pragma unroll
-    for (int q = 0; q < NN; q++) {
-      const double fdv = Tb[Wt::FD + q * DD + ca];
-      const double hq = hv[q];
-      const double fq = (c < OFF) ? ((q == DD + c) ? 100.0 : 0.0) : (col ? fdv : hq);
+        for (int cb = 0; cb < NB - CB0; cb++) Tacc[rb][cb][0] = Tacc[rb][cb][1] = 0.0;
 #pragma unroll
-      for (int r = 0; r + 1 <= q; r += 2) {
-        const double2 ll2 = *reinterpret_cast<const double2*>(Ls + q * RS + r);
-        Tc[r] = fma(ll2.x, fq, Tc[r]);
-        Tc[r + 1] = fma(ll2.y, fq, Tc[r + 1]);
-      }
-      if (!(q & 1)) Tc[q] = fma(Ls[q * RS + q], fq, Tc[q]);
-    }
-    // rows of T (31 columns: NN of V and u) into the M buffer
+      for (int kq = 0; kq < KQ; kq++) {
+        const int q = 4 * kq + qd;
+        double bF[NB - CB0];
 #pragma unroll
-    for (int r = 0; r < NN; r++)
-      if (c <= NN) Ms[r * RS + c] = Tc[r];
-    __syncwarp();
-    // ---- S4: Lam_p' = Qinv_ - T^T T, eta_p' = qb_ + T^T u
+        for (int cb = 0; cb < NB - CB0; cb++) {
+          const int cf = 8 * (cb + CB0) + g;   // column of F held by this lane
+          double v = 0.0;
+          if (q < NN) {
+            if (cf < OFF) v = (q == DD + cf) ? 100.0 : 0.0;
+            else if (cf < NN) v = Tb[Wt::FD + q * DD + (cf - OFF)];
+            else if (cf == NN) v = hv[q];
+          }
+          bF[cb] = v;
+        }
 #pragma unroll
-    for (int i = 0; i < NN; i++) Lp[i] = 0.0;
-    double ea = 0.0;
+        for (int rb = 0; rb < RB; rb++) {
+          const double av = Ls[q * RS + 8 * rb + g];   // L[q][r]: rows >= NN and columns >= NN are zero
 #pragma unroll
-    for (int r = 0; r < NN; r++) {
-      const double tr = Tc[r];
-      constexpr int dummy = 0;
-      (void)dummy;
-      const int i0 = (r > DD) ? ((r - DD) & ~1) : 0;  // row r of T is zero in columns < r - D
-#pragma unroll
-      for (int i = 0; i + 1 < NN + 1; i += 2) {
-        if (i >= i0 && i < NN) {
-          const double2 tt = *reinterpret_cast<const double2*>(Ms + r * RS + i);
-          Lp[i] = fma(tt.x, tr, Lp[i]);
-          if (i + 1 < NN) Lp[i + 1] = fma(tt.y, tr, Lp[i + 1]);
+          for (int cb = 0; cb < NB - CB0; cb++)
+            asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                         : "+d"(Tacc[rb][cb][0]), "+d"(Tacc[rb][cb][1])
+                         : "d"(av), "d"(bF[cb]));
         }
       }
-      ea = fma(Ms[r * RS + NN], tr, ea);
+      // dense blocks of T to the row buffer (accumulator layout: row 8rb+g, columns 8cb+2qd, +1)
+#pragma unroll
+      for (int rb = 0; rb < RB; rb++)
+#pragma unroll
+        for (int cb = 0; cb < NB - CB0; cb++)
+          *reinterpret_cast<double2*>(Ms + (8 * rb + g) * RS + 8 * (cb + CB0) + 2 * qd) =
+              make_double2(Tacc[rb][cb][0], Tacc[rb][cb][1]);
+      __syncwarp();
+      // K-fragments of T: unit-column blocks straight from L (T[r][c] = 100 L[D+c][r]), the rest
+      // from the buffer just written
+      double Tk[KQ][NB];
+#pragma unroll
+      for (int kq = 0; kq < KQ; kq++) {
+        const int r = 4 * kq + qd;
+#pragma unroll
+        for (int b = 0; b < NB; b++) {
+          const int cf = 8 * b + g;
+          if (b < CB0) Tk[kq][b] = 100.0 * Ls[(DD + cf) * RS + r];
+          else Tk[kq][b] = Ms[r * RS + cf];
+        }
+      }
+      __syncwarp();
+      // Z = T^T T, lower block triangle; row NN of Z is T^T u, Z[NN][NN] = u^T u
+      double Zacc[NB * (NB + 1) / 2][2];
+#pragma unroll
+      for (int e = 0; e < NB * (NB + 1) / 2; e++) Zacc[e][0] = Zacc[e][1] = 0.0;
+#pragma unroll
+      for (int kq = 0; kq < KQ; kq++) {
+#pragma unroll
+        for (int ib = 0; ib < NB; ib++)
+#pragma unroll
+          for (int jb = 0; jb <= ib; jb++)
+            asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                         : "+d"(Zacc[ib * (ib + 1) / 2 + jb][0]), "+d"(Zacc[ib * (ib + 1) / 2 + jb][1])
+                         : "d"(Tk[kq][ib]), "d"(Tk[kq][jb]));
+      }
+#pragma unroll
+      for (int ib = 0; ib < NB; ib++)
+#pragma unroll
+        for (int jb = 0; jb <= ib; jb++)
+          *reinterpret_cast<double2*>(Ls + (8 * ib + g) * RS + 8 * jb + 2 * qd) =
+              make_double2(Zacc[ib * (ib + 1) / 2 + jb][0], Zacc[ib * (ib + 1) / 2 + jb][1]);
+      __syncwarp();
     }
+    // back to one column per lane: Lam_p'[i][c] = Qinv_[i][c] - Z[i][c] (i >= c), eta_p' = qb_ + Z[NN][c]
 #pragma unroll
     for (int i = 0; i < NN; i++) {
       double qv;
       if (c < OFF) qv = (i == c) ? 100.0 : 0.0;
       else qv = (i >= OFF) ? Tb[Wt::QI + (i - OFF) * DD + ca] : 0.0;
-      Lp[i] = qv - Lp[i];
+      Lp[i] = qv - ((i >= c && col) ? Ls[i * RS + c] : 0.0);
     }
-    eta_p = ((c >= OFF) ? Tb[Wt::QB + ca] : 0.0) + ea;
-    if (want_ll && store) {
-      double uu = 0.0;  // meaningful in lane NN (its column of T is u)
-#pragma unroll
-      for (int r = 0; r < NN; r++) uu = fma(Tc[r], Tc[r], uu);
-      llacc += ct - 0.5 * Tb[Wt::SC + 1] + log(pd) + 0.5 * (uu - Tb[Wt::SC + 0]);
-    }
+    eta_p = ((c >= OFF) ? Tb[Wt::QB + ca] : 0.0) + (col ? Ls[NN * RS + c] : 0.0);
+    const double uu_z = Ls[NN * RS + NN];
+    __syncwarp();
+    // the buffer held Z: restore the zero padding the next step's operands rely on (row NN and
+    // column NN; rows / columns beyond are zero in Z already, and the rest is rewritten when L is
+    // published)
+    Ls[NN * RS + lane] = 0.0;
+    Ls[lane * RS + NN] = 0.0;
+    if (want_ll && store) llacc += ct - 0.5 * Tb[Wt::SC + 1] + log(pd) + 0.5 * (uu_z - Tb[Wt::SC + 0]);
     __syncwarp();
   }
   if (nch > 1) {
