@@ -46,7 +46,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--sessions-per-gpu", type=int, default=125)
     ap.add_argument("--frames", type=int, default=36000)
-    ap.add_argument("--chunk-len", type=int, default=1024, help="Kalman chunk length (0 = one CTA per session)")
+    ap.add_argument("--chunk-len", default="auto", help="Kalman chunk length: auto, 0 (= one warp per session) or steps")
     ap.add_argument("--burn-in", type=int, default=256, help="Kalman chunk warm-up steps")
     ap.add_argument("--cpu-sessions", type=int, default=0, help="0 = one per host core (max 16)")
     ap.add_argument("--cpu-frames", type=int, default=6000)
@@ -195,7 +195,7 @@ def main():
         td.init_process_group("nccl", device_id=dev)
     lib = _lib.load()
     if args.chunk_len is not None:
-        G.LATENTS_CHUNKING["chunk_len"] = args.chunk_len
+        G.LATENTS_CHUNKING["chunk_len"] = args.chunk_len if args.chunk_len == "auto" else int(args.chunk_len)
     if args.burn_in is not None:
         G.LATENTS_CHUNKING["burn_in"] = args.burn_in
 
@@ -345,7 +345,8 @@ def main():
                 "vs_baseline": None, "dtype": "f64 (Kalman, statistics) / f32 (HMM messages, emission GEMM)",
                 "data": "synthetic",
                 "config": {"workload": "cfg4-shard", "sessions_per_gpu": N, "frames": T, **sh,
-                           "total_sessions": N * world, "kalman_chunk_len": G.LATENTS_CHUNKING["chunk_len"],
+                           "total_sessions": N * world, "kalman_chunk_len": (G.auto_chunk_len(N, T, sh["L"], G.LATENTS_CHUNKING["burn_in"], dev)
+                                                if G.LATENTS_CHUNKING["chunk_len"] == "auto" else G.LATENTS_CHUNKING["chunk_len"]),
                            "kalman_burn_in": G.LATENTS_CHUNKING["burn_in"],
                            "kalman_boundary_err": boundary_err,
                            "l2": "per-step working set (>= 20 GB of filter workspace + ll/alphan) far exceeds the 126 MB L2"},

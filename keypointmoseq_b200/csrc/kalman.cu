@@ -120,11 +120,23 @@ struct KW {  // packed per-state table + per-warp shared-memory layout of the wa
   static constexpr int QB = F + NN;            // DD
   static constexpr int SC = QB + DD;           // c_z, logdet Q_
   static constexpr int SIZE = (SC + 2 + 1) / 2 * 2;
-  static constexpr int RS = 36;                // row stride (doubles) of the 32-row M / L / T / Z buffers
-  static constexpr int SM_MS = 0;
-  static constexpr int SM_LS = SM_MS + 32 * RS;
+  static constexpr int RS = 36;                // row stride (doubles) of the 32-row L / Z buffer
+  static constexpr int OFF_ = NN - DD;
+  static constexpr int NB = (NN + 1 + 7) / 8;  // 8-column blocks of T (NN columns of V and u)
+  static constexpr int CB0 = OFF_ / 8;         // first column block holding a dense column of F
+  static constexpr int TS = 8 * (NB - CB0) + 4;  // row stride of the dense blocks of T
+  // rows of M packed back to back, each padded to an even length (16-byte aligned row starts)
+  __host__ __device__ static constexpr int moff(int k) {
+    int o = 0;
+    for (int r = 0; r < k; r++) o += (r + 2) & ~1;
+    return o;
+  }
+  static constexpr int MSZ = ((moff(NN) > 32 * TS ? moff(NN) : 32 * TS) + 1) & ~1;
+  static constexpr int TABS = (SIZE - FD + 1) & ~1;  // shared-memory part of the table (all but G)
+  static constexpr int SM_MS = 0;              // M rows (S2/S3), then the dense blocks of T
+  static constexpr int SM_LS = SM_MS + MSZ;    // rows of L, then Z
   static constexpr int SM_TAB = SM_LS + 32 * RS;
-  static constexpr int SM_DV = SM_TAB + SIZE;
+  static constexpr int SM_DV = SM_TAB + TABS;
   static constexpr int SM_HV = SM_DV + 32;
   static constexpr int SM_TOTAL = SM_HV + 32;
 };
@@ -568,7 +580,7 @@ __global__ void __launch_bounds__(KAL_NT, 1)
 #define KW_WARPS 4
 
 template <int NN, int DD>
-__global__ void __launch_bounds__(KW_WARPS * 32, 2)
+__global__ void __launch_bounds__(KW_WARPS * 32, 3)
     kalman_forward_warp_kernel(const float* __restrict__ mask, const int* __restrict__ z,
                                const float* __restrict__ w_last, KalWs ws, int N, int T, int Lg,
                                int chunk_len, int burn_in, int want_ll) {
@@ -582,7 +594,8 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 2)
   double* S = sm + (size_t)wib * Wt::SM_TOTAL;
   double* Ms = S + Wt::SM_MS;   // rows of M, later rows of T
   double* Ls = S + Wt::SM_LS;   // rows of L
-  double* Tb = S + Wt::SM_TAB;  // packed tables of the current state
+  double* Tb = S + Wt::SM_TAB - Wt::FD;  // tables of the current state except G (indexed with the KW offsets)
+  const double* Gg = ws.tabw;   // G of the current state is read from global memory (L1/L2 resident)
   double* dv = S + Wt::SM_DV;   // 1 / M[i][i]
   double* hv = S + Wt::SM_HV;   // eta_c - f  (then scratch)
   const int Tp = T - Lg + 1, Tt = Tp - 1;
@@ -597,7 +610,7 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 2)
   const int c = lane;
   const bool col = c < NN;
   const int ca = min(max(c - OFF, 0), DD - 1);  // clamped index into the D-blocks
-  for (int e = lane; e < 64 * RS; e += 32) S[e] = 0.0;  // zero padding of the 32 x 32 operands
+  for (int e = lane; e < Wt::SM_TOTAL; e += 32) S[e] = 0.0;  // zero padding of the 32 x 32 operands
   __syncwarp();
 
   double Lp[NN];
@@ -621,6 +634,8 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 2)
     ctn = o[Y::OBS_C];
   };
   load_obs(tb);
+  float mk_next = mk[tb];
+  int z_next = (tb < Tt) ? zn[tb] : 0;
 
   for (int tau = tb; tau < t1; tau++) {
     if (tau == t0 && cc > 0) {
@@ -630,7 +645,10 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 2)
         if (c <= i) bd[i * (i + 1) / 2 + c] = Lp[i];
       if (col) bd[NTRI + c] = eta_p;
     }
-    const bool live = mk[tau] > 0.0f;
+    const bool live = mk_next > 0.0f;
+    const int zt = z_next;
+    mk_next = mk[tau + 1];                 // tau + 1 <= Tt: in range (mask row has T - L + 1 usable entries)
+    z_next = (tau + 1 < Tt) ? zn[tau + 1] : 0;
     double Jc[DD];
 #pragma unroll
     for (int a = 0; a < DD; a++) Jc[a] = Jn[a];
@@ -638,40 +656,44 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 2)
     load_obs(tau + 1);  // tau + 1 <= Tp - 1
     if (!live) continue;  // kalman.py:109-111
     const bool store = tau >= t0;
-    const int zt = zn[tau];
     if (zt != cur_z) {
       __syncwarp();
-      const double2* src = reinterpret_cast<const double2*>(ws.tabw + (size_t)zt * Wt::SIZE);
-      double2* dst = reinterpret_cast<double2*>(Tb);
-      for (int e = lane; e < Wt::SIZE / 2; e += 32) dst[e] = src[e];
+      const double* src = ws.tabw + (size_t)zt * Wt::SIZE;
+      for (int e = Wt::FD + lane; e < Wt::SIZE; e += 32) Tb[e] = src[e];
+      Gg = src;
       cur_z = zt;
       __syncwarp();
     }
     // ---- S1: column c of Lam_s = Lam_p + A^T Qinv A + C^T R^-1 C
     double Wc[NN];
 #pragma unroll
-    for (int i = 0; i < NN; i++) Wc[i] = Lp[i] + ((i >= c) ? Tb[Wt::G + i * (i + 1) / 2 + c] : 0.0);
+    for (int i = 0; i < NN; i++) Wc[i] = Lp[i] + ((i >= c) ? __ldg(Gg + Wt::G + i * (i + 1) / 2 + c) : 0.0);
 #pragma unroll
     for (int a = 0; a < DD; a++) Wc[OFF + a] += Jc[a];
     const double eta_c = eta_p + ec;
     // ---- S2: bottom-up Cholesky, rows of M published to Ms
     double pd = 1.0;
+    double piv = __shfl_sync(FULL, Wc[NN - 1], NN - 1);
 #pragma unroll
     for (int k = NN - 1; k >= 0; k--) {
-      const double piv = __shfl_sync(FULL, Wc[k], k);
       const double rs = rsqrt(piv);
       const double m = Wc[k] * rs;
-      if (c <= k) Ms[k * RS + c] = m;
+      if (k > 0) {
+        // next pivot W[k-1][k-1] - M[k][k-1]^2 is known to lane k-1 from its own registers:
+        // broadcast it now, so the shared-memory round trip below is off the pivot chain
+        piv = __shfl_sync(FULL, fma(-m, m, Wc[k - 1]), k - 1);
+      }
+      if (c <= k) Ms[Wt::moff(k) + c] = m;
       if (c == 0) dv[k] = rs;
       pd *= rs;
       __syncwarp();
 #pragma unroll
       for (int i = 0; i + 1 < k; i += 2) {
-        const double2 mm = *reinterpret_cast<const double2*>(Ms + k * RS + i);
+        const double2 mm = *reinterpret_cast<const double2*>(Ms + Wt::moff(k) + i);
         Wc[i] = fma(-mm.x, m, Wc[i]);
         Wc[i + 1] = fma(-mm.y, m, Wc[i + 1]);
       }
-      if (k & 1) Wc[k - 1] = fma(-Ms[k * RS + k - 1], m, Wc[k - 1]);
+      if (k & 1) Wc[k - 1] = fma(-Ms[Wt::moff(k) + k - 1], m, Wc[k - 1]);
     }
     // ---- S3: L = M^-1, column c (zero above the diagonal by construction)
     double Lc[NN];
@@ -680,11 +702,11 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 2)
       double a0 = (i == c) ? 1.0 : 0.0, a1 = 0.0;
 #pragma unroll
       for (int q = 0; q + 1 < i; q += 2) {
-        const double2 mm = *reinterpret_cast<const double2*>(Ms + i * RS + q);
+        const double2 mm = *reinterpret_cast<const double2*>(Ms + Wt::moff(i) + q);
         a0 = fma(-mm.x, Lc[q], a0);
         a1 = fma(-mm.y, Lc[q + 1], a1);
       }
-      if (i & 1) a0 = fma(-Ms[i * RS + i - 1], Lc[i - 1], a0);
+      if (i & 1) a0 = fma(-Ms[Wt::moff(i) + i - 1], Lc[i - 1], a0);
       Lc[i] = (a0 + a1) * dv[i];
     }
     // rows of L to shared memory, eta_c - f for the mean column, L and eta_c to the workspace
@@ -724,12 +746,11 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 2)
 #pragma unroll
         for (int cb = 0; cb < NB - CB0; cb++) {
           const int cf = 8 * (cb + CB0) + g;   // column of F held by this lane
-          double v = 0.0;
-          if (q < NN) {
-            if (cf < OFF) v = (q == DD + cf) ? 100.0 : 0.0;
-            else if (cf < NN) v = Tb[Wt::FD + q * DD + (cf - OFF)];
-            else if (cf == NN) v = hv[q];
-          }
+          const int qq = min(q, NN - 1);
+          const double fd = Tb[Wt::FD + qq * DD + min(max(cf - OFF, 0), DD - 1)];
+          const double hq = hv[qq];
+          double v = (cf < OFF) ? ((q == DD + cf) ? 100.0 : 0.0) : ((cf < NN) ? fd : ((cf == NN) ? hq : 0.0));
+          v = (q < NN) ? v : 0.0;
           bF[cb] = v;
         }
 #pragma unroll
@@ -747,7 +768,7 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 2)
       for (int rb = 0; rb < RB; rb++)
 #pragma unroll
         for (int cb = 0; cb < NB - CB0; cb++)
-          *reinterpret_cast<double2*>(Ms + (8 * rb + g) * RS + 8 * (cb + CB0) + 2 * qd) =
+          *reinterpret_cast<double2*>(Ms + (8 * rb + g) * Wt::TS + 8 * cb + 2 * qd) =
               make_double2(Tacc[rb][cb][0], Tacc[rb][cb][1]);
       __syncwarp();
       // K-fragments of T: unit-column blocks straight from L (T[r][c] = 100 L[D+c][r]), the rest
@@ -760,7 +781,7 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 2)
         for (int b = 0; b < NB; b++) {
           const int cf = 8 * b + g;
           if (b < CB0) Tk[kq][b] = 100.0 * Ls[(DD + cf) * RS + r];
-          else Tk[kq][b] = Ms[r * RS + cf];
+          else Tk[kq][b] = Ms[r * Wt::TS + (cf - 8 * CB0)];
         }
       }
       __syncwarp();
@@ -827,19 +848,19 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 2)
       const double piv = __shfl_sync(FULL, Wc[k], k);
       const double rs = rsqrt(piv);
       const double m = Wc[k] * rs;
-      if (c <= k) Ms[k * RS + c] = m;
+      if (c <= k) Ls[k * RS + c] = m;
       if (c == 0) dv[k] = rs;
       pd *= rs;
       __syncwarp();
 #pragma unroll
-      for (int i = 0; i < k; i++) Wc[i] = fma(-Ms[k * RS + i], m, Wc[i]);
+      for (int i = 0; i < k; i++) Wc[i] = fma(-Ls[k * RS + i], m, Wc[i]);
     }
     double Lc[NN];
 #pragma unroll
     for (int i = 0; i < NN; i++) {
       double a0 = (i == c) ? 1.0 : 0.0;
 #pragma unroll
-      for (int q = 0; q < i; q++) a0 = fma(-Ms[i * RS + q], Lc[q], a0);
+      for (int q = 0; q < i; q++) a0 = fma(-Ls[i * RS + q], Lc[q], a0);
       Lc[i] = a0 * dv[i];
     }
     if (col) hv[c] = eta_c;

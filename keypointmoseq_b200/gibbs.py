@@ -20,7 +20,24 @@ from .util import center_embedding, expand_Cd, f32, f64, i32
 
 VONMISES_ROUNDS = 8          # Best-Fisher rejection rounds pre-drawn per frame
 THIN_CAP = 16384             # max tables per state handled by the sticky thinning
-LATENTS_CHUNKING = {"chunk_len": 0, "burn_in": 0}   # module default: exact, one CTA per session
+# Kalman time-chunking: "auto" cuts every session into chunks sized so that one wave of warps
+# covers the shard; each chunk is warmed up over `burn_in` earlier steps.  With strict=True the
+# reported chunk-boundary mismatch is read back and the call is repeated in the exact sequential
+# mode (chunk_len = 0) if it exceeds `tol` (never observed at burn_in >= 128).
+LATENTS_CHUNKING = {"chunk_len": "auto", "burn_in": 256, "strict": True, "tol": 1e-10}
+KALMAN_WARPS_PER_SM = 12
+last_latents_boundary_err = None
+
+
+def auto_chunk_len(N, T, L, burn_in, device):
+    """Chunk length such that N * n_chunks is just under one wave of resident warps."""
+    Tt = T - L
+    slots = torch.cuda.get_device_properties(device).multi_processor_count * KALMAN_WARPS_PER_SM
+    nch = max(1, slots // max(N, 1))
+    cl = -(-Tt // nch)
+    if nch == 1 or cl < 4 * max(burn_in, 1):
+        cl = max(4 * max(burn_in, 1), 256)
+    return 0 if cl >= Tt else cl
 
 
 def _dims(Ab):
@@ -91,7 +108,7 @@ def resample_stateseqs(key, *, x, mask, Ab, Q, pi, draws=None, impl=0, **kwargs)
 
 # ------------------------------------------------------------------------ a5-a7
 def resample_latents(key, *, Y, mask, v, h, z, s, Cd, sigmasq, Ab, Q, Gamma=None, draws=None,
-                     chunk_len=None, burn_in=None, return_info=False, **kwargs):
+                     chunk_len=None, burn_in=None, strict=None, return_info=False, **kwargs):
     """gibbs.py:10-23 -> x (N,T,D) float32.  With `return_info=True` also returns a dict with
     the innovation-form marginal log-likelihood (N,) and the chunk-boundary mismatch (2,)."""
     lib = _lib.load()
@@ -110,18 +127,29 @@ def resample_latents(key, *, Y, mask, v, h, z, s, Cd, sigmasq, Ab, Q, Gamma=None
         seed = dist.seed_of(key)
         w = dist.fill_normal((N, T - L, n), seed, dist.STREAM_X, dev)
         w_last = dist.fill_normal((N, n), seed, dist.STREAM_X_LAST, dev)
+    global last_latents_boundary_err
     chunk_len = LATENTS_CHUNKING["chunk_len"] if chunk_len is None else chunk_len
     burn_in = LATENTS_CHUNKING["burn_in"] if burn_in is None else burn_in
+    strict = LATENTS_CHUNKING["strict"] if strict is None else strict
+    if chunk_len == "auto":
+        chunk_len = auto_chunk_len(N, T, L, int(burn_in), dev)
     x = torch.empty((N, T, D), dtype=torch.float32, device=dev)
     loglik = torch.empty((N,), dtype=torch.float64, device=dev) if return_info else None
-    berr = torch.zeros((2,), dtype=torch.float64, device=dev) if return_info else None
-    nbytes = lib.kpms_resample_latents_workspace_bytes(N, T, k, dk, D, L, K, int(chunk_len))
-    ws = _lib.WORKSPACE.get("latents", nbytes, dev)
-    _lib.check(lib.kpms_resample_latents(
-        _lib.ptr(Y), _lib.ptr(mask), _lib.ptr(v), _lib.ptr(h), _lib.ptr(z), _lib.ptr(s), _lib.ptr(Cdfull),
-        _lib.ptr(sigmasq), _lib.ptr(Ab), _lib.ptr(Q), _lib.ptr(w), _lib.ptr(w_last), N, T, k, dk, D, L, K,
-        int(chunk_len), int(burn_in), _lib.ptr(x), _lib.ptr(loglik), _lib.ptr(berr), _lib.ptr(ws),
-        ws.numel(), _lib.stream_ptr(dev)), "kpms_resample_latents")
+    berr = torch.zeros((2,), dtype=torch.float64, device=dev)
+
+    def run(cl):
+        nbytes = lib.kpms_resample_latents_workspace_bytes(N, T, k, dk, D, L, K, int(cl))
+        ws = _lib.WORKSPACE.get("latents", nbytes, dev)
+        _lib.check(lib.kpms_resample_latents(
+            _lib.ptr(Y), _lib.ptr(mask), _lib.ptr(v), _lib.ptr(h), _lib.ptr(z), _lib.ptr(s), _lib.ptr(Cdfull),
+            _lib.ptr(sigmasq), _lib.ptr(Ab), _lib.ptr(Q), _lib.ptr(w), _lib.ptr(w_last), N, T, k, dk, D, L, K,
+            int(cl), int(burn_in), _lib.ptr(x), _lib.ptr(loglik), _lib.ptr(berr), _lib.ptr(ws),
+            ws.numel(), _lib.stream_ptr(dev)), "kpms_resample_latents")
+
+    run(chunk_len)
+    if chunk_len > 0 and strict and float(berr.max()) > LATENTS_CHUNKING["tol"]:
+        run(0)   # warm-up too short for this model: redo exactly (one warp per session)
+    last_latents_boundary_err = berr
     if return_info:
         return x, {"loglik": loglik, "boundary_err": berr}
     return x

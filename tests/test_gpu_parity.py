@@ -167,16 +167,19 @@ def test_resample_latents_chunked_matches_exact(G):
     kw = dict(Y=T_(d['Y']), mask=T_(d['mask']), v=T_(s['v']), h=T_(s['h']), z=T_(s['z']), s=T_(s['s']),
               Cd=T_(p['Cd']), sigmasq=T_(p['sigmasq']), Ab=T_(p['Ab']), Q=T_(p['Q']), Gamma=T_(Gm),
               draws={'w': T_(dr['x_w']), 'w_last': T_(dr['x_w_last'])}, return_info=True)
-    x0, i0 = G.resample_latents(0, **kw)
-    x1, i1 = G.resample_latents(0, chunk_len=128, burn_in=160, **kw)
+    x0, i0 = G.resample_latents(0, chunk_len=0, **kw)
+    x1, i1 = G.resample_latents(0, chunk_len=128, burn_in=160, strict=False, **kw)
     berr = N_(i1['boundary_err'])
     assert berr.max() < 1e-9, berr
     assert float((x0 - x1).abs().max()) < 1e-6
     l0, l1 = N_(i0['loglik']), N_(i1['loglik'])
     assert np.all(np.abs(l0 - l1) <= 1e-9 * np.abs(l0))
     # too short a warm-up must be visible in the reported mismatch
-    _, i2 = G.resample_latents(0, chunk_len=128, burn_in=2, **kw)
+    _, i2 = G.resample_latents(0, chunk_len=128, burn_in=2, strict=False, **kw)
     assert N_(i2['boundary_err']).max() > 1e-6
+    # strict mode notices the mismatch and silently redoes the call exactly
+    x3, i3 = G.resample_latents(0, chunk_len=128, burn_in=2, strict=True, **kw)
+    assert float((x0 - x3).abs().max()) == 0.0 and N_(i3['boundary_err']).max() == 0.0
 
 
 # ------------------------------------------------------------------ a8-a11

@@ -31,7 +31,10 @@ def run(cl, bi, reps=2):
 
 x0, i0, t0 = run(0, 0, reps=1)
 print(json.dumps(dict(mode="exact", ms=t0, frames=N * T)), flush=True)
-for cl, bi in [(2048, 256), (1024, 256), (512, 256), (512, 128), (256, 128), (256, 64), (128, 64)]:
+pairs = [(2048, 256), (1024, 256), (512, 256), (512, 128), (256, 128), (256, 64), (128, 64)]
+if len(sys.argv) > 4:
+    pairs = [tuple(int(v) for v in a.split(':')) for a in sys.argv[4].split(',')]
+for cl, bi in pairs:
     x, info, t = run(cl, bi)
     be = info['boundary_err'].cpu().numpy()
     dx = float((x - x0).abs().max())
