@@ -27,11 +27,10 @@ SIGNATURES = {
     "kpms_ar_loglik_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "kpms_ar_loglik": (c_int, [P, P, P, c_int, c_int, c_int, c_int, c_int, P, P, c_size_t, c_int, P]),
     "kpms_ar_loglik_static": (c_int, [P, P, P, c_int, c_int, c_int, c_int, c_int, P, c_int, P]),
-    "kpms_hmm_ffbs_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
-    "kpms_hmm_ffbs": (c_int, [P, P, c_int64, P, P, c_int, c_int, c_int, P, P, P, c_size_t, P]),
-    "kpms_resample_stateseqs_workspace_bytes": (c_size_t, [c_int] * 5),
-    "kpms_resample_stateseqs": (c_int, [P, P, P, P, P, P, c_int, c_int, c_int, c_int, c_int, P, P, P,
-                                        c_size_t, c_int, P]),
+    "kpms_hmm_ffbs_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "kpms_hmm_ffbs": (c_int, [P, P, c_int64, P, P, c_int, c_int, c_int, c_int, c_int, P, P, P, P, c_size_t, P]),
+    "kpms_resample_stateseqs_workspace_bytes": (c_size_t, [c_int] * 6),
+    "kpms_resample_stateseqs": (c_int, [P, P, P, P, P, P] + [c_int] * 7 + [P, P, P, P, c_size_t, c_int, P]),
     "kpms_resample_latents_workspace_bytes": (c_size_t, [c_int] * 8),
     "kpms_resample_latents": (c_int, [P] * 12 + [c_int] * 9 + [P, P, P, P, c_size_t, P]),
     "kpms_ar_stats_workspace_bytes": (c_size_t, [c_int] * 5),

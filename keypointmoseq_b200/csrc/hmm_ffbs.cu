@@ -1,102 +1,159 @@
-// a2+a3: HMM forward filter / backward sampler, one CTA per session.
+// a2+a3: HMM forward filter / backward sampler.
 // Reference: distributions.py:46-79 (sample_hmm_stateseq), vmapped at gibbs.py:111-114.
 //
-// Forward (distributions.py:51-60): scaled linear-space filter, uniform initial
-// distribution, mask-blended carry, +1e-16 guard, marginal log-likelihood.
-//   K <= 128: thread j owns state j and keeps column j of pi in REGISTERS; one
-//   __syncthreads per frame (the unnormalised message is double-buffered in shared memory,
-//   every thread re-derives the normaliser from the same shared values, and max_j ll[t+1]
-//   is reduced one frame ahead, off the critical path).  ll is prefetched 8 frames ahead.
-//   K  > 128: generic kernel, pi streamed from L2.
-// Backward (distributions.py:62-72): z_t ~ alphan_t * pi[:, z_{t+1}], inverse CDF on one
-// uniform per frame; done by a single warp (K<=128) with shuffle scans, no block barrier.
+// Forward (distributions.py:51-60): scaled linear-space filter, uniform initial distribution,
+// mask-blended carry, +1e-16 guard, marginal log-likelihood.
+//   K <= 128, kernel F: one CTA per session (or per session chunk); thread j owns state j and keeps
+//   column j of pi in REGISTERS; one __syncthreads per frame (the unnormalised message is
+//   double-buffered in shared memory, every thread re-derives the normaliser from the same shared
+//   values, max_j ll[t+2] is reduced two frames ahead); ll / mask / u are staged 16 frames ahead
+//   with cp.async.  While running the dot product the thread also learns
+//     T_j = sum_i a_i pi[i][j],  P_j = sum_{i<j} a_i pi[i][j]  and  a_j pi[j][j]:
+//   IF the next state is j, the backward sampler keeps state j at this frame exactly when
+//     P_j <= u_t T_j < P_j + a_j pi[j][j]          (inverse CDF, distributions.py:65).
+//   One such "stay" bit per (frame, state) is written out.
+//   Chunks: with chunk_len > 0 a session is cut into chunks run by independent CTAs (3 per SM),
+//   each warmed up over `burn_in` earlier frames from the uniform distribution; the mismatch
+//   between a warmed-up start and its predecessor's end is reported for verification.
+// Backward (distributions.py:62-72), kernel B: one warp per session settles whole runs of frames
+//   (masked, or stay bit set for the current next state) with one ballot and evaluates the full
+//   inverse CDF z = min{ j : cumsum_j > u * total } only where the state changes.
+//   K > 128: generic kernel, pi streamed from L2.
 #include "common.cuh"
+#include <stdlib.h>
 
-#define HMM_RING 8
-#define HMM_STAGE 16   // frames staged ahead by the backward sampler
+#define HMM_STAGE 16    // frames of ll / mask / u staged ahead by the forward pass
+#define HMM_BRING 128   // frames of stay bits / u / mask staged ahead by the backward sampler
 
-extern "C" size_t kpms_hmm_ffbs_workspace_bytes(int N, int Tm, int K) {
-  if (N <= 0 || Tm <= 0 || K <= 0) return 0;
-  size_t al = kpms_round_up((size_t)N * Tm * K * sizeof(float), 256);   // alphan
-  size_t pf = kpms_round_up((size_t)K * K * sizeof(float), 256) * 2;    // pi, pi^T in f32 (K>128)
-  return al + pf;
+__host__ __device__ static inline int hmm_nchunks(int Tm, int chunk_len) {
+  if (chunk_len <= 0 || chunk_len >= Tm) return 1;
+  return (Tm + chunk_len - 1) / chunk_len;
 }
 
+struct HmmWs {
+  float* alphan;
+  float* pf;
+  float* pT;
+  unsigned* stay;
+  double* llpart;
+  float* bnd;   // [N][nch][2][K]
+  int* tv;
+};
+
+static size_t hmm_layout(int N, int Tm, int K, int chunk_len, void* base, HmmWs* ws) {
+  const int nch = hmm_nchunks(Tm, chunk_len);
+  size_t off = 0;
+  char* b = (char*)base;
+  auto take = [&](size_t bytes) {
+    size_t o = off;
+    off += kpms_round_up(bytes, 256);
+    return b ? (void*)(b + o) : nullptr;
+  };
+  void* p;
+  p = take((size_t)N * Tm * K * sizeof(float)); if (ws) ws->alphan = (float*)p;
+  p = take((size_t)K * K * sizeof(float)); if (ws) ws->pf = (float*)p;
+  p = take((size_t)K * K * sizeof(float)); if (ws) ws->pT = (float*)p;
+  p = take((size_t)N * Tm * 4 * sizeof(unsigned)); if (ws) ws->stay = (unsigned*)p;
+  p = take((size_t)N * nch * sizeof(double)); if (ws) ws->llpart = (double*)p;
+  p = take((size_t)N * nch * 2 * K * sizeof(float)); if (ws) ws->bnd = (float*)p;
+  p = take((size_t)N * sizeof(int)); if (ws) ws->tv = (int*)p;
+  return off;
+}
+
+extern "C" size_t kpms_hmm_ffbs_workspace_bytes(int N, int Tm, int K, int chunk_len) {
+  if (N <= 0 || Tm <= 0 || K <= 0) return 0;
+  return hmm_layout(N, Tm, K, chunk_len, nullptr, nullptr);
+}
+
+// number of unmasked frames per session (trailing padding assumed for the warm-up start)
+__global__ void hmm_tv_kernel(const float* __restrict__ mask, long long mask_stride, int Tm,
+                              int* __restrict__ tv) {
+  const int n = blockIdx.x;
+  __shared__ int cnt;
+  if (threadIdx.x == 0) cnt = 0;
+  __syncthreads();
+  int c = 0;
+  for (int t = threadIdx.x; t < Tm; t += blockDim.x) c += mask[(size_t)n * mask_stride + t] > 0.0f;
+  atomicAdd(&cnt, c);
+  __syncthreads();
+  if (threadIdx.x == 0) tv[n] = cnt;
+}
+
+// ------------------------------------------------------------------ kernel F: forward filter
 template <int KP>
-__global__ void __launch_bounds__(KP)
-    hmm_ffbs_reg_kernel(const float* __restrict__ ll, const float* __restrict__ mask,
-                        long long mask_stride, const double* __restrict__ pi,
-                        const float* __restrict__ u, int Tm, int K, int* __restrict__ z,
-                        double* __restrict__ loglik, float* __restrict__ alphan) {
+__global__ void __launch_bounds__(KP, 3)
+    hmm_forward_kernel(const float* __restrict__ ll, const float* __restrict__ mask,
+                       long long mask_stride, const double* __restrict__ pi,
+                       const float* __restrict__ u, int Tm, int K, int chunk_len, int burn_in,
+                       double* __restrict__ loglik, HmmWs ws) {
   constexpr int NW = KP / 32;
-  const int n = blockIdx.x, j = threadIdx.x, lane = j & 31, warp = j >> 5;
-  extern __shared__ __align__(16) float piT[];  // [KP][KP]: piT[s*KP+i] = pi[i][s]
+  const int nch = hmm_nchunks(Tm, chunk_len);
+  const int n = blockIdx.x / nch, cc = blockIdx.x % nch;
+  const int j = threadIdx.x, lane = j & 31, warp = j >> 5;
+  const int t0 = (nch == 1) ? 0 : cc * chunk_len;
+  const int t1 = (nch == 1) ? Tm : min(Tm, t0 + chunk_len);
+  const int tb = (cc > 0) ? max(0, min(t0, ws.tv[n]) - burn_in) : 0;
   __shared__ __align__(16) float a_s[2][KP];
   __shared__ float wmax_s[2][NW];
+  __shared__ __align__(16) float stage[HMM_STAGE][KP];    // ll rows
+  __shared__ float mstage[HMM_STAGE][KP];                 // per-thread copies of the mask
+  __shared__ float ustage[HMM_STAGE][KP];                 // per-thread copies of u
 
   float pcol[KP];
 #pragma unroll
   for (int i = 0; i < KP; i++) pcol[i] = (i < K && j < K) ? (float)pi[(size_t)i * K + j] : 0.0f;
-  for (int idx = j; idx < KP * KP; idx += KP) {
-    int s = idx / KP, i = idx % KP;
-    piT[idx] = (s < K && i < K) ? (float)pi[(size_t)i * K + s] : 0.0f;
-  }
+  const float pjj = (j < K) ? (float)pi[(size_t)j * K + j] : 0.0f;
 
   const float* ll_n = ll + (size_t)n * Tm * K;
-  float* al_n = alphan + (size_t)n * Tm * K;
+  float* al_n = ws.alphan + (size_t)n * Tm * K;
   const float* mk_n = mask + (size_t)n * mask_stride;
   const float* u_n = u + (size_t)n * Tm;
-  int* z_n = z + (size_t)n * Tm;
+  unsigned* stay_n = ws.stay + (size_t)n * Tm * 4;
 
-  // ------------------------------------------------------------------ forward
-  // ll rows (and the mask) are staged HMM_STAGE frames ahead into shared memory with cp.async:
-  // thread j copies and later reads only its own elements, so the staging needs no barrier, and
-  // unlike a register ring it does not serialise on the six scoreboard slots.
-  float* stage = piT + KP * KP;              // [HMM_STAGE][KP]  ll rows (alphan rows in the backward pass)
-  float* mstage = stage + HMM_STAGE * KP;    // [HMM_STAGE][KP]  per-thread copy of the mask
-  float* um = mstage + HMM_STAGE * KP;       // [HMM_STAGE][2]   backward: u, mask
-  float* lt = um + HMM_STAGE * 2;            // [32]             backward: lane totals
-  const unsigned stage_sa = (unsigned)__cvta_generic_to_shared(stage);
-  const unsigned mstage_sa = (unsigned)__cvta_generic_to_shared(mstage);
-  const unsigned um_sa = (unsigned)__cvta_generic_to_shared(um);
+  const unsigned stage_sa = (unsigned)__cvta_generic_to_shared(&stage[0][0]);
+  const unsigned mstage_sa = (unsigned)__cvta_generic_to_shared(&mstage[0][0]);
+  const unsigned ustage_sa = (unsigned)__cvta_generic_to_shared(&ustage[0][0]);
   auto issue_f = [&](int t) {
-    if (t < Tm) {
+    if (t < t1) {
       const int slot = t % HMM_STAGE;
       if (j < K) {
         const float* src = ll_n + (size_t)t * K + j;
         asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(stage_sa + (unsigned)((slot * KP + j) * 4)), "l"(src));
       }
       asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(mstage_sa + (unsigned)((slot * KP + j) * 4)), "l"(mk_n + t));
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(ustage_sa + (unsigned)((slot * KP + j) * 4)), "l"(u_n + t));
     }
     asm volatile("cp.async.commit_group;\n" ::);
   };
 #pragma unroll 1
-  for (int i = 0; i < HMM_STAGE; i++) issue_f(i);
+  for (int i = 0; i < HMM_STAGE; i++) issue_f(tb + i);
   asm volatile("cp.async.wait_group %0;\n" ::"n"(HMM_STAGE - 2));
-  {  // maxima of frames 0 and 1; afterwards frame t+2 is reduced during frame t
-    const float l0 = (j < K) ? stage[j] : -INFINITY;
-    const float l1 = (j < K && Tm > 1) ? stage[KP + j] : -INFINITY;
+  {  // maxima of frames tb and tb+1; afterwards frame t+2 is reduced during frame t
+    const float l0 = (j < K) ? stage[tb % HMM_STAGE][j] : -INFINITY;
+    const float l1 = (j < K && tb + 1 < t1) ? stage[(tb + 1) % HMM_STAGE][j] : -INFINITY;
     const float wm0 = warp_max_f(l0), wm1 = warp_max_f(l1);
     if (lane == 0) {
-      wmax_s[0][warp] = wm0;
-      wmax_s[1][warp] = wm1;
+      wmax_s[tb & 1][warp] = wm0;
+      wmax_s[(tb + 1) & 1][warp] = wm1;
     }
   }
   __syncthreads();
   float in_pot = (j < K) ? 1.0f / (float)K : 0.0f;
   double logtot = 0.0;
 #pragma unroll 1
-  for (int t = 0; t < Tm; t++) {
+  for (int t = tb; t < t1; t++) {
+    if (t == t0 && cc > 0 && j < K) ws.bnd[((size_t)(n * nch + cc) * 2 + 0) * K + j] = in_pot;
     const int buf = t & 1, slot = t % HMM_STAGE;
     float cmax = wmax_s[buf][0];
 #pragma unroll
     for (int w = 1; w < NW; w++) cmax = fmaxf(cmax, wmax_s[buf][w]);
     asm volatile("cp.async.wait_group %0;\n" ::"n"(HMM_STAGE - 3));  // frames <= t+2 have landed
-    const float llv = (j < K) ? stage[slot * KP + j] : -INFINITY;
-    const float m = mstage[slot * KP + j];
-    const float a = (j < K) ? in_pot * expf(llv - cmax) : 0.0f;
+    const float llv = (j < K) ? stage[slot][j] : -INFINITY;
+    const float m = mstage[slot][j];
+    const float uu = ustage[slot][j];
+    const float a = (j < K) ? in_pot * __expf(llv - cmax) : 0.0f;
     a_s[buf][j] = a;
-    const float nxt2 = (j < K && t + 2 < Tm) ? stage[((t + 2) % HMM_STAGE) * KP + j] : -INFINITY;
+    const float nxt2 = (j < K && t + 2 < t1) ? stage[(t + 2) % HMM_STAGE][j] : -INFINITY;
     issue_f(t + HMM_STAGE);  // refills the slot this thread has just read
     __syncthreads();
     // max of frame t+2, written after this frame's barrier into the slot this frame has just
@@ -105,86 +162,157 @@ __global__ void __launch_bounds__(KP)
       const float wm = warp_max_f(nxt2);
       if (lane == 0) wmax_s[buf][warp] = wm;
     }
-    // mat-vec and normaliser from the same shared values; 8 + 8 independent chains
-    float acc[8], sm8[8];
-#pragma unroll
-    for (int q = 0; q < 8; q++) acc[q] = 0.0f, sm8[q] = 0.0f;
+    // One pass over the shared message: total T_j, strictly-lower-index part P_j, normaliser.
+    // Rows are split into 32-row segments; for warp w, segments below w lie entirely under the
+    // diagonal (i < j), segments above entirely over it, and only segment w needs the i < j mask.
+    float lo[4] = {0.f, 0.f, 0.f, 0.f}, hi[4] = {0.f, 0.f, 0.f, 0.f}, md[4] = {0.f, 0.f, 0.f, 0.f};
+    float sm8[4] = {0.f, 0.f, 0.f, 0.f};
     const float4* av = reinterpret_cast<const float4*>(a_s[buf]);
 #pragma unroll
-    for (int q = 0; q < KP / 4; q++) {
-      const float4 v = av[q];
-      acc[(4 * q + 0) & 7] = fmaf(v.x, pcol[4 * q + 0], acc[(4 * q + 0) & 7]);
-      acc[(4 * q + 1) & 7] = fmaf(v.y, pcol[4 * q + 1], acc[(4 * q + 1) & 7]);
-      acc[(4 * q + 2) & 7] = fmaf(v.z, pcol[4 * q + 2], acc[(4 * q + 2) & 7]);
-      acc[(4 * q + 3) & 7] = fmaf(v.w, pcol[4 * q + 3], acc[(4 * q + 3) & 7]);
-      sm8[(4 * q + 0) & 7] += v.x;
-      sm8[(4 * q + 1) & 7] += v.y;
-      sm8[(4 * q + 2) & 7] += v.z;
-      sm8[(4 * q + 3) & 7] += v.w;
-    }
-    const float acc0 = (acc[0] + acc[1]) + (acc[2] + acc[3]);
-    const float acc1 = (acc[4] + acc[5]) + (acc[6] + acc[7]);
-    const float s0 = (sm8[0] + sm8[1]) + (sm8[2] + sm8[3]);
-    const float s1 = (sm8[4] + sm8[5]) + (sm8[6] + sm8[7]);
-    const float norm = (s0 + s1) + 1e-16f;
-    const float inv = 1.0f / norm;
-    if (j < K) al_n[(size_t)t * K + j] = a * inv;
-    if (m > 0.0f) in_pot = (acc0 + acc1) * inv;
-    if (j == 0 && m > 0.0f) logtot += (double)__logf(norm) + (double)cmax;
-  }
-  if (j == 0 && loglik != nullptr) loglik[n] = logtot;
-  asm volatile("cp.async.wait_group 0;\n" ::);
-  __syncthreads();  // alphan (global) written by this CTA is visible to warp 0 below
-  if (warp != 0) return;
-
-  // ------------------------------------------------------------------ backward (warp 0)
-  // alphan rows, u and mask are staged HMM_STAGE frames ahead into shared memory with
-  // cp.async (a register ring would serialise on the 6 scoreboard slots); the prefix sum over
-  // the 32 lane totals goes through shared memory (one store, 8 broadcast loads) because a
-  // 5-step shuffle scan costs ~400 cycles of dependent latency per frame; the sampled state
-  // is the number of states whose cumulative weight is <= u * total (4 ballots + popc).
-  constexpr int PER = KP / 32;  // states per lane: lane owns states lane*PER .. lane*PER+PER-1
-  static_assert(PER <= 4, "one 16-byte slot per lane");
-  auto issue = [&](int t) {  // copy frame t into its slot (t >= 0), then close the group
-    if (t >= 0) {
-      const int slot = t % HMM_STAGE;
+    for (int sg = 0; sg < NW; sg++) {
+      if (sg < warp) {
 #pragma unroll
-      for (int e = 0; e < PER; e++) {
-        const int st = lane * PER + e;
-        if (st < K) {
-          const float* src = al_n + (size_t)t * K + st;
-          const unsigned dst = stage_sa + (unsigned)((slot * KP + st) * 4);
-          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(src));
+        for (int q = 8 * sg; q < 8 * sg + 8; q++) {
+          const float4 v = av[q];
+          lo[0] = fmaf(v.x, pcol[4 * q + 0], lo[0]);
+          lo[1] = fmaf(v.y, pcol[4 * q + 1], lo[1]);
+          lo[2] = fmaf(v.z, pcol[4 * q + 2], lo[2]);
+          lo[3] = fmaf(v.w, pcol[4 * q + 3], lo[3]);
+          sm8[0] += v.x; sm8[1] += v.y; sm8[2] += v.z; sm8[3] += v.w;
+        }
+      } else if (sg > warp) {
+#pragma unroll
+        for (int q = 8 * sg; q < 8 * sg + 8; q++) {
+          const float4 v = av[q];
+          hi[0] = fmaf(v.x, pcol[4 * q + 0], hi[0]);
+          hi[1] = fmaf(v.y, pcol[4 * q + 1], hi[1]);
+          hi[2] = fmaf(v.z, pcol[4 * q + 2], hi[2]);
+          hi[3] = fmaf(v.w, pcol[4 * q + 3], hi[3]);
+          sm8[0] += v.x; sm8[1] += v.y; sm8[2] += v.z; sm8[3] += v.w;
+        }
+      } else {
+#pragma unroll
+        for (int q = 8 * sg; q < 8 * sg + 8; q++) {
+          const float4 v = av[q];
+          const float p0 = v.x * pcol[4 * q + 0], p1 = v.y * pcol[4 * q + 1];
+          const float p2 = v.z * pcol[4 * q + 2], p3 = v.w * pcol[4 * q + 3];
+          hi[0] += p0; hi[1] += p1; hi[2] += p2; hi[3] += p3;     // full segment into the total
+          md[0] += (4 * q + 0 < j) ? p0 : 0.0f;                   // masked part into P
+          md[1] += (4 * q + 1 < j) ? p1 : 0.0f;
+          md[2] += (4 * q + 2 < j) ? p2 : 0.0f;
+          md[3] += (4 * q + 3 < j) ? p3 : 0.0f;
+          sm8[0] += v.x; sm8[1] += v.y; sm8[2] += v.z; sm8[3] += v.w;
         }
       }
-      if (lane < 2) {
-        const float* src = (lane == 0) ? (u_n + t) : (mk_n + t);
-        const unsigned dst = um_sa + (unsigned)((slot * 2 + lane) * 4);
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst), "l"(src));
-      }
+    }
+    const float plo = (lo[0] + lo[1]) + (lo[2] + lo[3]);
+    const float P = plo + ((md[0] + md[1]) + (md[2] + md[3]));
+    const float tot = plo + ((hi[0] + hi[1]) + (hi[2] + hi[3]));
+    const float norm = ((sm8[0] + sm8[1]) + (sm8[2] + sm8[3])) + 1e-16f;
+    const float inv = __frcp_rn(norm);
+    const bool store = t >= t0;
+    {  // stay bit (unnormalised units throughout: only ratios matter)
+      const float thr = uu * tot;
+      const bool st = (j < K) && (P <= thr) && (P + a * pjj > thr);
+      const unsigned word = __ballot_sync(0xffffffffu, st);
+      if (store && lane == 0) stay_n[(size_t)t * 4 + warp] = word;
+    }
+    if (store && j < K) al_n[(size_t)t * K + j] = a * inv;
+    if (m > 0.0f) in_pot = tot * inv;
+    if (store && j == 0 && m > 0.0f) logtot += (double)__logf(norm) + (double)cmax;
+  }
+  if (nch > 1 && j < K) ws.bnd[((size_t)(n * nch + cc) * 2 + 1) * K + j] = in_pot;
+  if (j == 0) ws.llpart[(size_t)n * nch + cc] = logtot;
+  asm volatile("cp.async.wait_group 0;\n" ::);
+  (void)loglik;
+}
+
+// loglik[n] = sum of chunk partials (fixed order); largest mismatch between a warmed-up chunk
+// start and its predecessor's end (max abs difference of the normalised potentials)
+__global__ void hmm_finish_kernel(HmmWs ws, int nch, int K, double* __restrict__ loglik,
+                                  unsigned* __restrict__ err_bits) {
+  const int n = blockIdx.x;
+  if (threadIdx.x == 0 && loglik) {
+    double s = 0.0;
+    for (int c = 0; c < nch; c++) s += ws.llpart[(size_t)n * nch + c];
+    loglik[n] = s;
+  }
+  if (!err_bits || nch < 2) return;
+  float worst = 0.0f;
+  for (int c = 0; c + 1 < nch; c++) {
+    const float* a = ws.bnd + ((size_t)(n * nch + c) * 2 + 1) * K;
+    const float* b = ws.bnd + ((size_t)(n * nch + c + 1) * 2 + 0) * K;
+    for (int e = threadIdx.x; e < K; e += blockDim.x) worst = fmaxf(worst, fabsf(a[e] - b[e]));
+  }
+  for (int o = 16; o > 0; o >>= 1) worst = fmaxf(worst, __shfl_xor_sync(0xffffffffu, worst, o));
+  if ((threadIdx.x & 31) == 0) atomicMax(err_bits, __float_as_uint(worst));
+}
+
+// ------------------------------------------------------------------ kernel B: backward sampler
+template <int KP>
+__global__ void __launch_bounds__(32)
+    hmm_backward_kernel(const float* __restrict__ mask, long long mask_stride,
+                        const double* __restrict__ pi, const float* __restrict__ u, int Tm, int K,
+                        int* __restrict__ z, HmmWs ws) {
+  const int n = blockIdx.x, lane = threadIdx.x;
+  extern __shared__ __align__(16) float piT[];  // [KP][KP]: piT[s*KP+i] = pi[i][s]
+  unsigned* bring = reinterpret_cast<unsigned*>(piT + KP * KP);   // [HMM_BRING][8] stay words, u, mask
+  float* lt = reinterpret_cast<float*>(bring + HMM_BRING * 8);    // [32] lane totals (slow path)
+  for (int idx = lane; idx < KP * KP; idx += 32) {
+    int s = idx / KP, i = idx % KP;
+    piT[idx] = (s < K && i < K) ? (float)pi[(size_t)i * K + s] : 0.0f;
+  }
+  const float* al_n = ws.alphan + (size_t)n * Tm * K;
+  const float* mk_n = mask + (size_t)n * mask_stride;
+  const float* u_n = u + (size_t)n * Tm;
+  int* z_n = z + (size_t)n * Tm;
+  const unsigned* stay_n = ws.stay + (size_t)n * Tm * 4;
+  __syncwarp();
+  // z_t ~ alphan_t * pi[:, z_{t+1}] by inverse CDF on u_t (distributions.py:62-72).  Lane l looks
+  // at frame t-l: if that frame is masked (z = 0, carry unchanged) or its stay bit for the current
+  // next state is set, the frame is settled; one ballot settles the longest such prefix, and only
+  // the first unsettled frame pays for the full prefix sum over the K weights.
+  constexpr int PER = KP / 32;  // states per lane in the slow path: lane*PER .. lane*PER+PER-1
+  const unsigned bring_sa = (unsigned)__cvta_generic_to_shared(bring);
+  auto issue_b = [&](int f0, int cnt) {  // frames f0, f0-1, ..., f0-cnt+1 (those >= 0)
+    const int f = f0 - lane;
+    if (lane < cnt && f >= 0) {
+      const unsigned dst = bring_sa + (unsigned)((f % HMM_BRING) * 32);
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(stay_n + (size_t)f * 4));
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst + 16), "l"(u_n + f));
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst + 20), "l"(mk_n + f));
     }
     asm volatile("cp.async.commit_group;\n" ::);
   };
-  for (int e = lane; e < HMM_STAGE * KP; e += 32) stage[e] = 0.0f;  // padded states stay 0
-  __syncwarp();
 #pragma unroll 1
-  for (int i = 0; i < HMM_STAGE; i++) issue(Tm - 1 - i);
+  for (int b0 = 0; b0 < HMM_BRING / 32; b0++) issue_b(Tm - 1 - 32 * b0, 32);
   int s_next = -1;  // -1: next_potential = ones (distributions.py:76)
+  int t = Tm - 1;
 #pragma unroll 1
-  for (int t = Tm - 1; t >= 0; t--) {
-    asm volatile("cp.async.wait_group %0;\n" ::"n"(HMM_STAGE - 1));
+  while (t >= 0) {
+    asm volatile("cp.async.wait_group 1;\n" ::);
     __syncwarp();
-    const int slot = t % HMM_STAGE;
-    const float uu = um[slot * 2 + 0], mm = um[slot * 2 + 1];
-    int zt = 0;
-    if (mm > 0.0f) {
+    const int f = t - lane;
+    const bool valid = f >= 0;
+    const unsigned* e = bring + (valid ? (f % HMM_BRING) : 0) * 8;
+    const bool masked = valid && !(__uint_as_float(e[5]) > 0.0f);
+    const bool stayb = valid && s_next >= 0 && ((e[s_next >> 5] >> (s_next & 31)) & 1u);
+    const unsigned bal = __ballot_sync(0xffffffffu, masked || stayb);
+    const int r = (bal == 0xffffffffu) ? 32 : (__ffs(~bal) - 1);  // settled frames t, t-1, ..., t-r+1
+    if (lane < r) z_n[f] = masked ? 0 : s_next;
+    int consumed = r;
+    const int fb = t - r;  // first unsettled frame (unmasked by construction) if it exists
+    if (r < 32 && fb >= 0) {
+      const float ub = __uint_as_float(bring[(fb % HMM_BRING) * 8 + 4]);
       float w[PER];
       float run = 0.0f;
 #pragma unroll
-      for (int e = 0; e < PER; e++) {
-        const float np = (s_next < 0) ? 1.0f : piT[s_next * KP + lane * PER + e];
-        run = fmaf(np, stage[slot * KP + lane * PER + e], run);
-        w[e] = run;  // inclusive prefix within the lane
+      for (int q = 0; q < PER; q++) {
+        const int st = lane * PER + q;
+        const float al = (st < K) ? al_n[(size_t)fb * K + st] : 0.0f;
+        const float np = (s_next < 0) ? 1.0f : piT[s_next * KP + st];
+        run = fmaf(np, al, run);
+        w[q] = run;  // inclusive prefix within the lane
       }
       lt[lane] = run;
       __syncwarp();
@@ -199,17 +327,18 @@ __global__ void __launch_bounds__(KP)
         excl += (q < grp) ? g4 : ((q == grp) ? own : 0.0f);
         total += g4;
       }
-      const float thr = uu * total;
+      const float thr = ub * total;
       int cnt = 0;
 #pragma unroll
-      for (int e = 0; e < PER; e++)
-        cnt += __popc(__ballot_sync(0xffffffffu, !(excl + w[e] > thr)));
-      zt = min(cnt, K - 1);
+      for (int q = 0; q < PER; q++) cnt += __popc(__ballot_sync(0xffffffffu, !(excl + w[q] > thr)));
+      const int zt = min(cnt, K - 1);
+      if (lane == 0) z_n[fb] = zt;
       s_next = zt;
+      consumed = r + 1;
     }
-    if (lane == 0) z_n[t] = zt;
-    __syncwarp();  // every lane is done with this slot and with lt
-    issue(t - HMM_STAGE);
+    __syncwarp();  // every lane is done with the consumed slots and with lt
+    issue_b(t - HMM_BRING, consumed);
+    t -= consumed;
   }
   asm volatile("cp.async.wait_group 0;\n" ::);
 }
@@ -311,40 +440,57 @@ __global__ void hmm_ffbs_generic_kernel(const float* __restrict__ ll, const floa
 
 template <int KP>
 static int launch_reg(const float* ll, const float* mask, long long ms, const double* pi,
-                      const float* u, int N, int Tm, int K, int* z, double* loglik, float* alphan,
-                      cudaStream_t st) {
-  auto kern = hmm_ffbs_reg_kernel<KP>;
-  const size_t smem = (size_t)(KP * KP + 2 * HMM_STAGE * KP + HMM_STAGE * 2 + 32) * sizeof(float);
+                      const float* u, int N, int Tm, int K, int chunk_len, int burn_in, int* z,
+                      double* loglik, float* boundary_err, HmmWs ws, cudaStream_t st) {
+  const int nch = hmm_nchunks(Tm, chunk_len);
+  if (nch > 1) {
+    hmm_tv_kernel<<<N, 256, 0, st>>>(mask, ms, Tm, ws.tv);
+    int rc = kpms_last_launch();
+    if (rc) return rc;
+  }
+  hmm_forward_kernel<KP><<<N * nch, KP, 0, st>>>(ll, mask, ms, pi, u, Tm, K, chunk_len, burn_in, loglik, ws);
+  int rc = kpms_last_launch();
+  if (rc) return rc;
+  if (boundary_err) KPMS_CUDA(cudaMemsetAsync(boundary_err, 0, sizeof(float), st));
+  hmm_finish_kernel<<<N, 128, 0, st>>>(ws, nch, K, loglik, (unsigned*)boundary_err);
+  rc = kpms_last_launch();
+  if (rc) return rc;
+  const char* env = getenv("KPMS_HMM_FLAGS");  // debugging: bit 0 = forward pass only
+  if (env && (atoi(env) & 1)) return KPMS_OK;
+  auto kern = hmm_backward_kernel<KP>;
+  const size_t smem = (size_t)(KP * KP + HMM_BRING * 8 + 32) * sizeof(float);
   KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<N, KP, smem, st>>>(ll, mask, ms, pi, u, Tm, K, z, loglik, alphan);
+  kern<<<N, 32, smem, st>>>(mask, ms, pi, u, Tm, K, z, ws);
   return kpms_last_launch();
 }
 
 extern "C" int kpms_hmm_ffbs(const float* ll, const float* mask, int64_t mask_stride,
-                             const double* pi, const float* u, int N, int Tm, int K, int32_t* z,
-                             double* loglik, void* workspace, size_t workspace_bytes,
-                             void* stream) {
+                             const double* pi, const float* u, int N, int Tm, int K, int chunk_len,
+                             int burn_in, int32_t* z, double* loglik, float* boundary_err,
+                             void* workspace, size_t workspace_bytes, void* stream) {
   KPMS_REQUIRE(ll && mask && pi && u && z && workspace, KPMS_ERR_NULL);
   KPMS_REQUIRE(N > 0 && Tm > 0 && K > 0 && mask_stride >= Tm, KPMS_ERR_SHAPE);
   KPMS_REQUIRE(K <= 1024, KPMS_ERR_UNSUPPORTED);
-  KPMS_REQUIRE(kpms_aligned(workspace, 256) &&
-                   workspace_bytes >= kpms_hmm_ffbs_workspace_bytes(N, Tm, K),
-               KPMS_ERR_WORKSPACE);
+  KPMS_REQUIRE(chunk_len <= 0 || burn_in >= 0, KPMS_ERR_SHAPE);
+  if (K > 128) chunk_len = 0;  // the generic kernel walks whole sessions
+  HmmWs ws;
+  const size_t need = hmm_layout(N, Tm, K, chunk_len, workspace, &ws);
+  KPMS_REQUIRE(kpms_aligned(workspace, 256) && workspace_bytes >= need, KPMS_ERR_WORKSPACE);
   cudaStream_t st = (cudaStream_t)stream;
-  float* alphan = (float*)workspace;
-  if (K <= 32) return launch_reg<32>(ll, mask, mask_stride, pi, u, N, Tm, K, z, loglik, alphan, st);
-  if (K <= 64) return launch_reg<64>(ll, mask, mask_stride, pi, u, N, Tm, K, z, loglik, alphan, st);
-  if (K <= 96) return launch_reg<96>(ll, mask, mask_stride, pi, u, N, Tm, K, z, loglik, alphan, st);
-  if (K <= 128) return launch_reg<128>(ll, mask, mask_stride, pi, u, N, Tm, K, z, loglik, alphan, st);
-  char* base = (char*)workspace + kpms_round_up((size_t)N * Tm * K * sizeof(float), 256);
-  float* pf = (float*)base;
-  float* pT = (float*)(base + kpms_round_up((size_t)K * K * sizeof(float), 256));
-  hmm_prep_pi_kernel<<<(K * K + 255) / 256, 256, 0, st>>>(pi, K, pf, pT);
+#define KPMS_HMM_GO(KPV) \
+  return launch_reg<KPV>(ll, mask, mask_stride, pi, u, N, Tm, K, chunk_len, burn_in, z, loglik, boundary_err, ws, st)
+  if (K <= 32) KPMS_HMM_GO(32);
+  if (K <= 64) KPMS_HMM_GO(64);
+  if (K <= 96) KPMS_HMM_GO(96);
+  if (K <= 128) KPMS_HMM_GO(128);
+#undef KPMS_HMM_GO
+  if (boundary_err) KPMS_CUDA(cudaMemsetAsync(boundary_err, 0, sizeof(float), st));
+  hmm_prep_pi_kernel<<<(K * K + 255) / 256, 256, 0, st>>>(pi, K, ws.pf, ws.pT);
   int rc = kpms_last_launch();
   if (rc) return rc;
   const int threads = (K + 31) / 32 * 32;
   const size_t smem = (size_t)(K + 64) * sizeof(float);
-  hmm_ffbs_generic_kernel<<<N, threads, smem, st>>>(ll, mask, mask_stride, pf, pT, u, Tm, K, z,
-                                                    loglik, alphan);
+  hmm_ffbs_generic_kernel<<<N, threads, smem, st>>>(ll, mask, mask_stride, ws.pf, ws.pT, u, Tm, K, z,
+                                                    loglik, ws.alphan);
   return kpms_last_launch();
 }

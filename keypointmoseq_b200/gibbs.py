@@ -27,6 +27,21 @@ THIN_CAP = 16384             # max tables per state handled by the sticky thinni
 LATENTS_CHUNKING = {"chunk_len": "auto", "burn_in": 256, "strict": True, "tol": 1e-10}
 KALMAN_WARPS_PER_SM = 12
 last_latents_boundary_err = None
+# HMM forward-filter chunking (K <= 128): same idea; the filter forgets its start geometrically.
+# "auto" cuts sessions so that about three CTAs per SM are busy; mismatch above `tol` (absolute,
+# on potentials that sum to one) triggers an exact re-run when strict.
+STATESEQ_CHUNKING = {"chunk_len": "auto", "burn_in": 1024, "strict": True, "tol": 1e-5}
+HMM_CTAS_PER_SM = 3
+last_stateseq_boundary_err = None
+
+
+def auto_hmm_chunk_len(N, Tm, burn_in, device):
+    slots = torch.cuda.get_device_properties(device).multi_processor_count * HMM_CTAS_PER_SM
+    nch = max(1, slots // max(N, 1))
+    cl = -(-Tm // nch)
+    if nch == 1 or cl < 4 * max(burn_in, 1):
+        cl = 4 * max(burn_in, 1)
+    return 0 if cl >= Tm else cl
 
 
 def auto_chunk_len(N, T, L, burn_in, device):
@@ -68,24 +83,47 @@ def ar_log_likelihood(*, x, Ab, Q, impl=0, **kwargs):
     return ll
 
 
-def sample_hmm_stateseqs(*, ll, mask, pi, u):
+def _hmm_chunking(N, Tm, K, chunk_len, burn_in, strict, dev):
+    chunk_len = STATESEQ_CHUNKING["chunk_len"] if chunk_len is None else chunk_len
+    burn_in = STATESEQ_CHUNKING["burn_in"] if burn_in is None else burn_in
+    strict = STATESEQ_CHUNKING["strict"] if strict is None else strict
+    if chunk_len == "auto":
+        chunk_len = auto_hmm_chunk_len(N, Tm, int(burn_in), dev) if K <= 128 else 0
+    return int(chunk_len), int(burn_in), bool(strict)
+
+
+def sample_hmm_stateseqs(*, ll, mask, pi, u, chunk_len=None, burn_in=None, strict=None, return_info=False):
     """distributions.py:46-79 batched over sessions: ll (N,Tm,K), mask (N,Tm), u (N,Tm)."""
+    global last_stateseq_boundary_err
     lib = _lib.load()
     ll = f32(ll)
     dev = ll.device
     N, Tm, K = ll.shape
     mask, pi, u = f32(mask, dev), f64(pi, dev), f32(u, dev)
+    chunk_len, burn_in, strict = _hmm_chunking(N, Tm, K, chunk_len, burn_in, strict, dev)
     z = torch.empty((N, Tm), dtype=torch.int32, device=dev)
     loglik = torch.empty((N,), dtype=torch.float64, device=dev)
-    ws = _lib.WORKSPACE.get("hmm", lib.kpms_hmm_ffbs_workspace_bytes(N, Tm, K), dev)
-    _lib.check(lib.kpms_hmm_ffbs(_lib.ptr(ll), _lib.ptr(mask), Tm, _lib.ptr(pi), _lib.ptr(u), N, Tm, K,
-                                 _lib.ptr(z), _lib.ptr(loglik), _lib.ptr(ws), ws.numel(),
-                                 _lib.stream_ptr(dev)), "kpms_hmm_ffbs")
+    berr = torch.zeros((1,), dtype=torch.float32, device=dev)
+
+    def run(cl):
+        ws = _lib.WORKSPACE.get("hmm", lib.kpms_hmm_ffbs_workspace_bytes(N, Tm, K, cl), dev)
+        _lib.check(lib.kpms_hmm_ffbs(_lib.ptr(ll), _lib.ptr(mask), Tm, _lib.ptr(pi), _lib.ptr(u), N, Tm, K, cl,
+                                     burn_in, _lib.ptr(z), _lib.ptr(loglik), _lib.ptr(berr), _lib.ptr(ws),
+                                     ws.numel(), _lib.stream_ptr(dev)), "kpms_hmm_ffbs")
+
+    run(chunk_len)
+    if chunk_len > 0 and strict and float(berr) > STATESEQ_CHUNKING["tol"]:
+        run(0)
+    last_stateseq_boundary_err = berr
+    if return_info:
+        return z, loglik, {"boundary_err": berr}
     return z, loglik
 
 
-def resample_stateseqs(key, *, x, mask, Ab, Q, pi, draws=None, impl=0, **kwargs):
+def resample_stateseqs(key, *, x, mask, Ab, Q, pi, draws=None, impl=0, chunk_len=None, burn_in=None,
+                       strict=None, **kwargs):
     """gibbs.py:107-115 -> (z (N,T-L) int32, marginal log-likelihood (N,) float64)."""
+    global last_stateseq_boundary_err
     lib = _lib.load()
     x = f32(x)
     dev = x.device
@@ -96,13 +134,22 @@ def resample_stateseqs(key, *, x, mask, Ab, Q, pi, draws=None, impl=0, **kwargs)
         u = f32(draws["u"], dev)
     else:
         u = dist.fill_uniform((N, T - L), dist.seed_of(key), dist.STREAM_Z, dev)
+    chunk_len, burn_in, strict = _hmm_chunking(N, T - L, K, chunk_len, burn_in, strict, dev)
     z = torch.empty((N, T - L), dtype=torch.int32, device=dev)
     loglik = torch.empty((N,), dtype=torch.float64, device=dev)
-    ws = _lib.WORKSPACE.get("stateseqs", lib.kpms_resample_stateseqs_workspace_bytes(N, T, D, L, K), dev)
-    _lib.check(lib.kpms_resample_stateseqs(
-        _lib.ptr(x), _lib.ptr(mask), _lib.ptr(Ab), _lib.ptr(Q), _lib.ptr(pi), _lib.ptr(u), N, T, D, L, K,
-        _lib.ptr(z), _lib.ptr(loglik), _lib.ptr(ws), ws.numel(), int(impl), _lib.stream_ptr(dev)),
-        "kpms_resample_stateseqs")
+    berr = torch.zeros((1,), dtype=torch.float32, device=dev)
+
+    def run(cl):
+        ws = _lib.WORKSPACE.get("stateseqs", lib.kpms_resample_stateseqs_workspace_bytes(N, T, D, L, K, cl), dev)
+        _lib.check(lib.kpms_resample_stateseqs(
+            _lib.ptr(x), _lib.ptr(mask), _lib.ptr(Ab), _lib.ptr(Q), _lib.ptr(pi), _lib.ptr(u), N, T, D, L, K,
+            cl, burn_in, _lib.ptr(z), _lib.ptr(loglik), _lib.ptr(berr), _lib.ptr(ws), ws.numel(), int(impl),
+            _lib.stream_ptr(dev)), "kpms_resample_stateseqs")
+
+    run(chunk_len)
+    if chunk_len > 0 and strict and float(berr) > STATESEQ_CHUNKING["tol"]:
+        run(0)
+    last_stateseq_boundary_err = berr
     return z, loglik
 
 

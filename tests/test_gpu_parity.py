@@ -375,3 +375,23 @@ def test_hmm_long_sequence_bench_shape(G):
     assert np.all(np.abs(lg - lo) <= 1e-5 * np.abs(lo))
     valid = mask > 0
     assert (z[valid] == zo[valid]).mean() >= 0.999
+
+
+def test_hmm_chunked_forward_matches_exact(G):
+    """Chunked forward filter (independent CTAs with warm-up) against the sequential one."""
+    import torch
+    ll, mask, pi, u = _hmm_case(11, N=3, T=9000, K=100, ragged=True)
+    kw = dict(ll=T_(ll), mask=T_(mask), pi=T_(pi), u=T_(u), return_info=True)
+    z0, l0, i0 = G.sample_hmm_stateseqs(chunk_len=0, **kw)
+    z1, l1, i1 = G.sample_hmm_stateseqs(chunk_len=1500, burn_in=512, strict=False, **kw)
+    assert float(i0['boundary_err']) == 0.0 and float(i1['boundary_err']) < 1e-5
+    assert float((z0 != z1).float().mean()) < 1e-3
+    assert np.all(np.abs(N_(l0) - N_(l1)) <= 1e-6 * np.abs(N_(l0)))
+    zo, lo = O._hmm_batch(ll, mask, pi, u)
+    valid = mask > 0
+    assert (N_(z1)[valid] == zo[valid]).mean() >= 0.999
+    # a uselessly short warm-up is reported, and strict mode repairs it
+    z2, l2, i2 = G.sample_hmm_stateseqs(chunk_len=1500, burn_in=0, strict=False, **kw)
+    assert float(i2['boundary_err']) > 1e-3
+    z3, l3, i3 = G.sample_hmm_stateseqs(chunk_len=1500, burn_in=0, strict=True, **kw)
+    assert torch.equal(z3, z0) and float(i3['boundary_err']) == 0.0

@@ -51,8 +51,8 @@ def test_argument_validation_without_gpu(lib):
     assert lib.kpms_ar_loglik(one, one, one, 1, 3, 10, 3, 5, one, one, 1 << 20, 0, null) == -2   # T <= L
     assert lib.kpms_ar_loglik(one, one, one, 1, 10, 9, 3, 5, one, one, 1 << 20, 0, null) == -3   # D,L not built
     assert lib.kpms_ar_loglik(one, one, one, 1, 10, 10, 3, 5, one, one, 8, 0, null) == -4        # workspace
-    assert lib.kpms_hmm_ffbs(one, one, 5, one, one, 1, 10, 4, one, one, one, 1 << 20, null) == -2  # stride < Tm
-    assert lib.kpms_hmm_ffbs(one, one, 10, one, one, 1, 10, 2000, one, one, one, 1 << 30, null) == -3
+    assert lib.kpms_hmm_ffbs(one, one, 5, one, one, 1, 10, 4, 0, 0, one, one, null, one, 1 << 20, null) == -2  # stride < Tm
+    assert lib.kpms_hmm_ffbs(one, one, 10, one, one, 1, 10, 2000, 0, 0, one, one, null, one, 1 << 30, null) == -3
     assert lib.kpms_fill_gamma(one, 10, 0.5, 1, 1, null) == -3
     assert lib.kpms_resample_latents_workspace_bytes(0, 10, 8, 2, 10, 3, 5, 0) == 0
 
@@ -61,7 +61,7 @@ def test_workspace_queries_scale(lib):
     a = lib.kpms_resample_latents_workspace_bytes(10, 1000, 8, 2, 10, 3, 50, 0)
     b = lib.kpms_resample_latents_workspace_bytes(20, 1000, 8, 2, 10, 3, 50, 0)
     assert 1.9 < b / a < 2.1 and a > 10 * 998 * 495 * 8
-    assert lib.kpms_hmm_ffbs_workspace_bytes(10, 100, 50) >= 10 * 100 * 50 * 4
+    assert lib.kpms_hmm_ffbs_workspace_bytes(10, 100, 50, 0) >= 10 * 100 * 50 * 4
     assert lib.kpms_ar_stats_workspace_bytes(10, 100, 10, 3, 50) % 256 == 0
 
 
