@@ -38,6 +38,8 @@ struct HmmWs {
   double* llpart;
   float* bnd;   // [N][nch][2][K]
   int* tv;
+  float* Tbuf;    // [N][Tm][K] a @ pi of the tensor-core forward pass (chunked mode only)
+  float* rowmax;  // [N][Tm]
 };
 
 static size_t hmm_layout(int N, int Tm, int K, int chunk_len, void* base, HmmWs* ws) {
@@ -57,6 +59,13 @@ static size_t hmm_layout(int N, int Tm, int K, int chunk_len, void* base, HmmWs*
   p = take((size_t)N * nch * sizeof(double)); if (ws) ws->llpart = (double*)p;
   p = take((size_t)N * nch * 2 * K * sizeof(float)); if (ws) ws->bnd = (float*)p;
   p = take((size_t)N * sizeof(int)); if (ws) ws->tv = (int*)p;
+  if (nch > 1 && K <= 128) {
+    p = take((size_t)N * Tm * K * sizeof(float)); if (ws) ws->Tbuf = (float*)p;
+    p = take((size_t)N * Tm * sizeof(float)); if (ws) ws->rowmax = (float*)p;
+  } else if (ws) {
+    ws->Tbuf = nullptr;
+    ws->rowmax = nullptr;
+  }
   return off;
 }
 
@@ -78,6 +87,11 @@ __global__ void hmm_tv_kernel(const float* __restrict__ mask, long long mask_str
   __syncthreads();
   if (threadIdx.x == 0) tv[n] = cnt;
 }
+
+int kpms_hmm_forward_tc(const float* ll, const float* mask, long long mask_stride, const double* pi,
+                        const float* u, const int* tv, int N, int Tm, int K, int chunk_len, int burn_in,
+                        int nch, float* rowmax, float* a_out, float* T_out, unsigned* stay, double* llpart,
+                        float* bnd, unsigned* err_bits, cudaStream_t st);  // hmm_tc.cu
 
 // ------------------------------------------------------------------ kernel F: forward filter
 template <int KP>
@@ -229,7 +243,7 @@ __global__ void __launch_bounds__(KP, 3)
 
 // loglik[n] = sum of chunk partials (fixed order); largest mismatch between a warmed-up chunk
 // start and its predecessor's end (max abs difference of the normalised potentials)
-__global__ void hmm_finish_kernel(HmmWs ws, int nch, int K, double* __restrict__ loglik,
+__global__ void hmm_finish_kernel(HmmWs ws, int nch, int K, int chunk_len, double* __restrict__ loglik,
                                   unsigned* __restrict__ err_bits) {
   const int n = blockIdx.x;
   if (threadIdx.x == 0 && loglik) {
@@ -239,7 +253,9 @@ __global__ void hmm_finish_kernel(HmmWs ws, int nch, int K, double* __restrict__
   }
   if (!err_bits || nch < 2) return;
   float worst = 0.0f;
+  const int tvn = ws.tv[n];
   for (int c = 0; c + 1 < nch; c++) {
+    if ((c + 1) * chunk_len >= tvn) break;  // the next chunk starts inside the trailing padding
     const float* a = ws.bnd + ((size_t)(n * nch + c) * 2 + 1) * K;
     const float* b = ws.bnd + ((size_t)(n * nch + c + 1) * 2 + 0) * K;
     for (int e = threadIdx.x; e < K; e += blockDim.x) worst = fmaxf(worst, fabsf(a[e] - b[e]));
@@ -448,11 +464,18 @@ static int launch_reg(const float* ll, const float* mask, long long ms, const do
     int rc = kpms_last_launch();
     if (rc) return rc;
   }
-  hmm_forward_kernel<KP><<<N * nch, KP, 0, st>>>(ll, mask, ms, pi, u, Tm, K, chunk_len, burn_in, loglik, ws);
-  int rc = kpms_last_launch();
-  if (rc) return rc;
   if (boundary_err) KPMS_CUDA(cudaMemsetAsync(boundary_err, 0, sizeof(float), st));
-  hmm_finish_kernel<<<N, 128, 0, st>>>(ws, nch, K, loglik, (unsigned*)boundary_err);
+  int rc = KPMS_ERR_UNSUPPORTED;
+  const char* tcenv = getenv("KPMS_HMM_TC");  // "0" forces the CUDA-core forward kernel in chunked mode
+  if (nch > 1 && !(tcenv && tcenv[0] == '0'))
+    rc = kpms_hmm_forward_tc(ll, mask, ms, pi, u, ws.tv, N, Tm, K, chunk_len, burn_in, nch, ws.rowmax,
+                             ws.alphan, ws.Tbuf, ws.stay, ws.llpart, ws.bnd, (unsigned*)boundary_err, st);
+  if (rc == KPMS_ERR_UNSUPPORTED) {
+    hmm_forward_kernel<KP><<<N * nch, KP, 0, st>>>(ll, mask, ms, pi, u, Tm, K, chunk_len, burn_in, loglik, ws);
+    rc = kpms_last_launch();
+  }
+  if (rc) return rc;
+  hmm_finish_kernel<<<N, 128, 0, st>>>(ws, nch, K, chunk_len, loglik, (unsigned*)boundary_err);
   rc = kpms_last_launch();
   if (rc) return rc;
   const char* env = getenv("KPMS_HMM_FLAGS");  // debugging: bit 0 = forward pass only

@@ -1,0 +1,512 @@
+// HMM forward filter on the 5th-generation tensor cores (tcgen05, 3xTF32, TMEM accumulators).
+// Reference: distributions.py:51-60 (_forward_message) — per frame  in_pot' = (a / sum a) @ pi,
+// a = in_pot * exp(ll - max ll).
+//
+// A single session is a chain of K x K mat-vecs, which no tensor core can use.  Cutting every
+// session into chunks with a warm-up (hmm_ffbs.cu) yields thousands of independent chains, and 128
+// chains stepping in lock-step make the per-frame work a real GEMM:
+//     T (128 chains x K) = A (128 x K: the chains' current messages a) @ pi (K x K)
+// Kernel hmm_forward_tc: one CTA = 128 chains, one thread = one chain.  pi (hi / lo TF32 parts)
+// stays resident in shared memory in the UMMA K-major layout; per frame the thread reads T of its
+// chain from TMEM, multiplies by exp(ll - rowmax), accumulates the normaliser and the marginal
+// log-likelihood, writes the message (global, for the backward sampler) and its hi / lo split
+// (shared, next A operand), then one elected thread issues 3 x KD/8 tcgen05.mma.
+// Kernel hmm_stay_tc (frame-parallel): P = a @ pi_su (pi_su[i][j] = pi[i][j] for i < j) and the
+// "stay" bits  P_j <= u T_j < P_j + a_j pi[j][j]  that let the backward sampler skip runs.
+// Messages are stored unnormalised (a, and T = a @ pi in the same units): every consumer only
+// needs ratios.  Masks must be trailing padding (merge_data, util.py:47-60); anything else is
+// flagged through boundary_err so that the caller falls back to the sequential kernel.
+#include "tc_common.cuh"
+
+struct HmmTcArgs {
+  const float* ll;
+  const float* rowmax;
+  const double* pi;
+  const float* u;
+  const int* tv;
+  float* a_out;    // [N][Tm][K] unnormalised messages
+  float* T_out;    // [N][Tm][K] a @ pi
+  unsigned* stay;  // [N][Tm][4]
+  double* llpart;  // [N][nch]
+  float* bnd;      // [N][nch][2][K]
+  int N, Tm, K, chunk_len, burn_in, nch;
+};
+
+template <int KD, int NP>
+struct HTC {
+  static constexpr int SBO = (KD / 4) * 128;
+  static constexpr int A_BYTES = 16 * SBO;
+  static constexpr int B_BYTES = (NP / 8) * SBO;
+  static constexpr int KSTEPS = KD / 8;
+  static constexpr int TMEM_COLS = NP <= 32 ? 32 : (NP <= 64 ? 64 : (NP <= 128 ? 128 : 256));
+  static constexpr uint32_t IDESC = umma_idesc_tf32_m128(NP);
+  static constexpr size_t SMEM = 1024 + 2 * A_BYTES + 2 * B_BYTES + 256;
+};
+
+// max_j ll[row][j] for every frame row (one warp per row)
+__global__ void hmm_rowmax_kernel(const float* __restrict__ ll, long long rows, int K,
+                                  float* __restrict__ rowmax) {
+  const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  float m = -INFINITY;
+  for (int j = lane; j < K; j += 32) m = fmaxf(m, ll[row * K + j]);
+  m = warp_max_f(m);
+  if (lane == 0) rowmax[row] = m;
+}
+
+// flag (as +1e30 in err[0]) sessions whose mask is not of the form  t < tv[n]
+__global__ void hmm_mask_check_kernel(const float* __restrict__ mask, long long mask_stride, int Tm,
+                                      const int* __restrict__ tv, unsigned* __restrict__ err_bits) {
+  const int n = blockIdx.x;
+  const int tvn = tv[n];
+  bool bad = false;
+  for (int t = threadIdx.x; t < Tm; t += blockDim.x)
+    bad |= ((mask[(size_t)n * mask_stride + t] > 0.0f) != (t < tvn));
+  if (__syncthreads_or(bad) && threadIdx.x == 0) atomicMax(err_bits, __float_as_uint(1e30f));
+}
+
+template <int KD, int NP, bool SU>
+__device__ __forceinline__ void load_pi_tile(const double* __restrict__ pi, int K, unsigned char* sB_hi,
+                                             unsigned char* sB_lo) {
+  using C = HTC<KD, NP>;
+  for (int e = threadIdx.x; e < NP * KD; e += blockDim.x) {
+    const int jn = e / KD, i = e % KD;  // B[n = output state j][k = input state i] = pi[i][j]
+    float v = (i < K && jn < K) ? (float)pi[(size_t)i * K + jn] : 0.0f;
+    if (SU && !(i < jn)) v = 0.0f;
+    const uint32_t hi = tf32_rna(v);
+    const uint32_t lo = tf32_rna(v - __uint_as_float(hi));
+    const size_t off = umma_off(jn, i, C::SBO);
+    *reinterpret_cast<uint32_t*>(sB_hi + off) = hi;
+    *reinterpret_cast<uint32_t*>(sB_lo + off) = lo;
+  }
+}
+
+template <int KD, int NP>
+__device__ __forceinline__ void issue_3xtf32(uint32_t tmem, uint32_t a_hi, uint32_t a_lo, uint32_t b_hi,
+                                             uint32_t b_lo, uint32_t mbar_sa) {
+  using C = HTC<KD, NP>;
+  uint32_t acc = 0;
+#pragma unroll
+  for (int ks = 0; ks < C::KSTEPS; ks++) {
+    const uint32_t koff = ks * 2 * TC_LBO;
+    const uint64_t dah = umma_desc(a_hi + koff, TC_LBO, C::SBO), dal = umma_desc(a_lo + koff, TC_LBO, C::SBO);
+    const uint64_t dbh = umma_desc(b_hi + koff, TC_LBO, C::SBO), dbl = umma_desc(b_lo + koff, TC_LBO, C::SBO);
+    umma_tf32(tmem, dah, dbh, C::IDESC, acc);
+    umma_tf32(tmem, dah, dbl, C::IDESC, 1u);
+    umma_tf32(tmem, dal, dbh, C::IDESC, 1u);
+    acc = 1u;
+  }
+  umma_commit(mbar_sa);
+}
+
+__device__ __forceinline__ float ex2_ftz(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// Work split inside a CTA of 512 threads: thread = (row = tid % 128, part = tid / 128).  The warp
+// index modulo 4 equals row / 32, which is the TMEM lane quarter that warp may read.  A row's
+// KD columns are cut into groups of 8; part p owns groups p, p + 4, p + 8, ...  Four warps per
+// scheduler hide the fixed-latency dependencies that a single warp cannot.
+#define HTC_THREADS 512
+template <int KD>
+struct HGroups {
+  static constexpr int G = KD / 8;
+  static constexpr int MAXG = (G + 3) / 4;
+};
+
+__device__ __forceinline__ void ldg8(const float* __restrict__ src, bool ok, float fill, float4& v0, float4& v1) {
+  if (ok) {
+    v0 = __ldg(reinterpret_cast<const float4*>(src));
+    v1 = __ldg(reinterpret_cast<const float4*>(src) + 1);
+  } else {
+    v0 = make_float4(fill, fill, fill, fill);
+    v1 = v0;
+  }
+}
+
+// ------------------------------------------------------------------ forward filter, 128 chains per CTA
+template <int KD, int NP>
+__global__ void __launch_bounds__(HTC_THREADS, 1) hmm_forward_tc_kernel(HmmTcArgs p) {
+  using C = HTC<KD, NP>;
+  using HG = HGroups<KD>;
+  extern __shared__ __align__(1024) unsigned char smem[];
+  unsigned char* sA_hi = smem;
+  unsigned char* sA_lo = sA_hi + C::A_BYTES;
+  unsigned char* sB_hi = sA_lo + C::A_BYTES;
+  unsigned char* sB_lo = sB_hi + C::B_BYTES;
+  uint64_t* mbar = reinterpret_cast<uint64_t*>(sB_lo + C::B_BYTES);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mbar + 1);
+  int* smax = reinterpret_cast<int*>(tmem_slot + 1);
+  __shared__ float psum[2][4][128];  // per-part row sums of frame s (double-buffered by s & 1)
+  __shared__ float pmax[2][4][128];  // per-part row maxima of ll for frame s
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int row = tid & 127, part = tid >> 7;
+  const int K = p.K, Tm = p.Tm, nch = p.nch;
+  const long long unit = (long long)blockIdx.x * 128 + row;
+  const bool has = unit < (long long)p.N * nch;
+  int n = 0, cc = 0, t0 = 0, t1 = 0, tb = 0, tend = 0;
+  if (has) {
+    n = (int)(unit / nch);
+    cc = (int)(unit % nch);
+    t0 = (nch == 1) ? 0 : cc * p.chunk_len;
+    t1 = (nch == 1) ? Tm : min(Tm, t0 + p.chunk_len);
+    const int tvn = p.tv[n];
+    tb = (cc > 0) ? max(0, min(t0, tvn) - p.burn_in) : 0;
+    tend = min(t1, tvn);  // trailing padding: the chain stops at the first masked frame
+  }
+  load_pi_tile<KD, NP, false>(p.pi, K, sB_hi, sB_lo);
+  if (tid == 0) *smax = 0;
+  const uint32_t mbar_sa = (uint32_t)__cvta_generic_to_shared(mbar);
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(mbar_sa));
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::);
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
+                     (uint32_t)__cvta_generic_to_shared(tmem_slot)),
+                 "n"(C::TMEM_COLS));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::);
+  }
+  __syncthreads();
+  if (part == 0) atomicMax(smax, max(tend - tb, 0));
+  const size_t rowbase = (size_t)n * Tm;
+  const float* __restrict__ llp = p.ll;
+  float* __restrict__ aout = p.a_out;
+  float* __restrict__ tout = p.T_out;
+
+  // ll of the current and of the next frame live in registers (this thread's column groups); the
+  // frame after that is fetched while the tensor core works on the current one.
+  float4 llc[HG::MAXG][2], lln[HG::MAXG][2];
+  auto fetch_ll = [&](int t, float4 (&dst)[HG::MAXG][2]) {
+    const bool act = has && (t < tend);
+    const float* llr = llp + (rowbase + t) * K;
+#pragma unroll
+    for (int i = 0; i < HG::MAXG; i++) {
+      const int c = 8 * (part + 4 * i);
+      if (act && c + 4 < K) {
+        ldg8(llr + c, true, 0.f, dst[i][0], dst[i][1]);
+      } else if (act && c < K) {
+        dst[i][0] = __ldg(reinterpret_cast<const float4*>(llr + c));
+        dst[i][1] = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+      } else {
+        const float f = act ? -INFINITY : 0.0f;  // columns beyond K contribute exp(-inf) = 0
+        dst[i][0] = make_float4(f, f, f, f);
+        dst[i][1] = dst[i][0];
+      }
+    }
+  };
+  auto row_max = [&](const float4 (&v)[HG::MAXG][2]) {
+    float m = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < HG::MAXG; i++) {
+      m = fmaxf(m, fmaxf(fmaxf(v[i][0].x, v[i][0].y), fmaxf(v[i][0].z, v[i][0].w)));
+      m = fmaxf(m, fmaxf(fmaxf(v[i][1].x, v[i][1].y), fmaxf(v[i][1].z, v[i][1].w)));
+    }
+    return m;
+  };
+  fetch_ll(tb, llc);
+  fetch_ll(tb + 1, lln);
+  pmax[0][part][row] = row_max(llc);
+  TC_FENCE_PROXY();
+  TC_FENCE_BEFORE();
+  __syncthreads();
+  TC_FENCE_AFTER();
+  const int S = *smax;
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+  const uint32_t a_hi_sa = (uint32_t)__cvta_generic_to_shared(sA_hi), a_lo_sa = (uint32_t)__cvta_generic_to_shared(sA_lo);
+  const uint32_t b_hi_sa = (uint32_t)__cvta_generic_to_shared(sB_hi), b_lo_sa = (uint32_t)__cvta_generic_to_shared(sB_lo);
+  const size_t rowoff = (size_t)(row / 8) * C::SBO + (row % 8) * 16;
+  const float LOG2E = 1.4426950408889634f;
+
+  double logtot = 0.0, prod = 1.0;  // marginal log-likelihood = log prod(norm) + sum(cmax)
+  float cmax_prev = 0.0f;
+  uint32_t parity = 0;
+  for (int s = 0; s <= S; s++) {
+    const int t = tb + s;
+    const int buf = s & 1;
+    const bool active = has && (s < S) && (t < tend);
+    const bool prev_active = has && (s > 0) && (t - 1 < tend);
+    const bool prev_store = prev_active && (t - 1 >= t0);
+    const bool store = active && (t >= t0);
+    const bool bstart = active && (t == t0) && (cc > 0);
+    const bool bend = prev_active && (t == tend) && (nch > 1);
+    // normaliser of the previous frame and maximum of this one, summed / maxed over the four parts
+    float inv = 1.0f / (float)K;
+    if (s > 0) {
+      const float norm = ((psum[buf ^ 1][0][row] + psum[buf ^ 1][1][row]) +
+                          (psum[buf ^ 1][2][row] + psum[buf ^ 1][3][row])) + 1e-16f;
+      inv = __frcp_rn(norm);
+      if (part == 0 && prev_store) {
+        prod *= (double)norm;
+        logtot += (double)cmax_prev;
+        if ((s & 15) == 0) {
+          logtot += log(prod);
+          prod = 1.0;
+        }
+      }
+    }
+    const float cmax = active ? fmaxf(fmaxf(pmax[buf][0][row], pmax[buf][1][row]),
+                                      fmaxf(pmax[buf][2][row], pmax[buf][3][row]))
+                              : 0.0f;
+    cmax_prev = cmax;
+    const float inva = active ? inv : 0.0f;
+    float* ar = aout + (rowbase + t) * K;
+    float* Tr = tout + (rowbase + t - 1) * K;
+    float sum = 0.0f;
+#pragma unroll
+    for (int i = 0; i < HG::MAXG; i++) {
+      const int g = part + 4 * i;
+      if (g < HG::G) {  // warp-uniform
+        const int c = 8 * g;
+        float Tv[8];
+        if (s > 0) {
+          uint32_t tr[16];
+          tmem_ld8(taddr + (uint32_t)c, tr);
+#pragma unroll
+          for (int q = 0; q < 8; q++) Tv[q] = __uint_as_float(tr[q]);
+        } else {
+#pragma unroll
+          for (int q = 0; q < 8; q++) Tv[q] = 1.0f;
+        }
+        if (prev_store) {
+          if (c < K) *reinterpret_cast<float4*>(Tr + c) = make_float4(Tv[0], Tv[1], Tv[2], Tv[3]);
+          if (c + 4 < K) *reinterpret_cast<float4*>(Tr + c + 4) = make_float4(Tv[4], Tv[5], Tv[6], Tv[7]);
+        }
+        if (bstart || bend) {
+          float* bd = p.bnd + ((size_t)(n * nch + cc) * 2 + (bstart ? 0 : 1)) * K;
+          for (int q = 0; q < 8 && c + q < K; q++) bd[c + q] = Tv[q] * inv;
+        }
+        const float l8[8] = {llc[i][0].x, llc[i][0].y, llc[i][0].z, llc[i][0].w,
+                             llc[i][1].x, llc[i][1].y, llc[i][1].z, llc[i][1].w};
+        float a8[8];
+        uint32_t hi[8], lo[8];
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+          a8[q] = (Tv[q] * inva) * ex2_ftz((l8[q] - cmax) * LOG2E);
+          hi[q] = tf32_rna(a8[q]);
+          lo[q] = tf32_rna(a8[q] - __uint_as_float(hi[q]));
+        }
+        sum += ((a8[0] + a8[1]) + (a8[2] + a8[3])) + ((a8[4] + a8[5]) + (a8[6] + a8[7]));
+        if (store) {
+          if (c < K) *reinterpret_cast<float4*>(ar + c) = make_float4(a8[0], a8[1], a8[2], a8[3]);
+          if (c + 4 < K) *reinterpret_cast<float4*>(ar + c + 4) = make_float4(a8[4], a8[5], a8[6], a8[7]);
+        }
+        const size_t off = rowoff + (size_t)(2 * g) * TC_LBO;
+        *reinterpret_cast<uint4*>(sA_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(sA_hi + off + TC_LBO) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+        *reinterpret_cast<uint4*>(sA_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        *reinterpret_cast<uint4*>(sA_lo + off + TC_LBO) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+      }
+    }
+    if (s == S) break;
+    psum[buf][part][row] = sum;
+    pmax[buf ^ 1][part][row] = row_max(lln);
+    TC_FENCE_PROXY();
+    TC_FENCE_BEFORE();
+    __syncthreads();
+    if (tid == 0) {
+      TC_FENCE_AFTER();
+      issue_3xtf32<KD, NP>(tmem_base, a_hi_sa, a_lo_sa, b_hi_sa, b_lo_sa, mbar_sa);
+    }
+#pragma unroll
+    for (int i = 0; i < HG::MAXG; i++) {
+      llc[i][0] = lln[i][0];
+      llc[i][1] = lln[i][1];
+    }
+    fetch_ll(t + 2, lln);  // in flight while the tensor core works
+    mbar_wait(mbar_sa, parity);
+    parity ^= 1u;
+    TC_FENCE_AFTER();
+  }
+  if (has && part == 0) p.llpart[(size_t)n * nch + cc] = logtot + log(prod);
+  TC_FENCE_BEFORE();
+  __syncthreads();
+  if (warp == 0)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "n"(C::TMEM_COLS));
+}
+
+// ------------------------------------------------------------------ stay bits, frame-parallel
+template <int KD, int NP>
+__global__ void __launch_bounds__(HTC_THREADS, 1) hmm_stay_tc_kernel(HmmTcArgs p) {
+  using C = HTC<KD, NP>;
+  using HG = HGroups<KD>;
+  extern __shared__ __align__(1024) unsigned char smem[];
+  unsigned char* sA_hi = smem;
+  unsigned char* sA_lo = sA_hi + C::A_BYTES;
+  unsigned char* sB_hi = sA_lo + C::A_BYTES;
+  unsigned char* sB_lo = sB_hi + C::B_BYTES;
+  uint64_t* mbar = reinterpret_cast<uint64_t*>(sB_lo + C::B_BYTES);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mbar + 1);
+  __shared__ float pjj_s[128];
+  __shared__ __align__(16) unsigned char sbits[128][16];  // one byte per 8-column group
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int row = tid & 127, part = tid >> 7;
+  const int K = p.K, Tm = p.Tm;
+  load_pi_tile<KD, NP, true>(p.pi, K, sB_hi, sB_lo);
+  if (tid < 128) pjj_s[tid] = (tid < K) ? (float)p.pi[(size_t)tid * K + tid] : 0.0f;
+  for (int e = tid; e < 128 * 4; e += HTC_THREADS) reinterpret_cast<unsigned*>(&sbits[0][0])[e] = 0u;
+  const uint32_t mbar_sa = (uint32_t)__cvta_generic_to_shared(mbar);
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(mbar_sa));
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::);
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
+                     (uint32_t)__cvta_generic_to_shared(tmem_slot)),
+                 "n"(C::TMEM_COLS));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::);
+  }
+  TC_FENCE_PROXY();
+  TC_FENCE_BEFORE();
+  __syncthreads();
+  TC_FENCE_AFTER();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+  const uint32_t a_hi_sa = (uint32_t)__cvta_generic_to_shared(sA_hi), a_lo_sa = (uint32_t)__cvta_generic_to_shared(sA_lo);
+  const uint32_t b_hi_sa = (uint32_t)__cvta_generic_to_shared(sB_hi), b_lo_sa = (uint32_t)__cvta_generic_to_shared(sB_lo);
+  const size_t rowoff = (size_t)(row / 8) * C::SBO + (row % 8) * 16;
+  const long long frames = (long long)p.N * Tm;
+  const long long nblk = (frames + 127) / 128;
+  const float* __restrict__ ap = p.a_out;
+  const float* __restrict__ tp = p.T_out;
+  uint32_t parity = 0;
+
+  auto frame_live = [&](long long g) {
+    if (g >= frames) return false;
+    const int n = (int)(g / Tm), t = (int)(g % Tm);
+    return t < p.tv[n];  // masked frames carry no message
+  };
+  auto fetch_row = [&](const float* __restrict__ base, long long g, bool live, float4 (&dst)[HG::MAXG][2]) {
+    const float* r = base + g * K;
+#pragma unroll
+    for (int i = 0; i < HG::MAXG; i++) {
+      const int c = 8 * (part + 4 * i);
+      if (live && c + 4 < K) {
+        ldg8(r + c, true, 0.f, dst[i][0], dst[i][1]);
+      } else if (live && c < K) {
+        dst[i][0] = __ldg(reinterpret_cast<const float4*>(r + c));
+        dst[i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+      } else {
+        dst[i][0] = make_float4(0.f, 0.f, 0.f, 0.f);
+        dst[i][1] = dst[i][0];
+      }
+    }
+  };
+
+  float4 arow[HG::MAXG][2], anext[HG::MAXG][2], trow[HG::MAXG][2];
+  long long blk = blockIdx.x;
+  bool live = frame_live(blk * 128 + row);
+  if (blk < nblk) fetch_row(ap, blk * 128 + row, live, arow);
+  for (; blk < nblk; blk += gridDim.x) {
+    const long long g = blk * 128 + row;
+#pragma unroll
+    for (int i = 0; i < HG::MAXG; i++) {
+      const int gi = part + 4 * i;
+      if (gi < HG::G) {
+        const float a8[8] = {arow[i][0].x, arow[i][0].y, arow[i][0].z, arow[i][0].w,
+                             arow[i][1].x, arow[i][1].y, arow[i][1].z, arow[i][1].w};
+        uint32_t hi[8], lo[8];
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+          hi[q] = tf32_rna(a8[q]);
+          lo[q] = tf32_rna(a8[q] - __uint_as_float(hi[q]));
+        }
+        const size_t off = rowoff + (size_t)(2 * gi) * TC_LBO;
+        *reinterpret_cast<uint4*>(sA_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(sA_hi + off + TC_LBO) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+        *reinterpret_cast<uint4*>(sA_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        *reinterpret_cast<uint4*>(sA_lo + off + TC_LBO) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+      }
+    }
+    TC_FENCE_PROXY();
+    TC_FENCE_BEFORE();
+    __syncthreads();
+    if (tid == 0) {
+      TC_FENCE_AFTER();
+      issue_3xtf32<KD, NP>(tmem_base, a_hi_sa, a_lo_sa, b_hi_sa, b_lo_sa, mbar_sa);
+    }
+    // while the tensor core works: T row and u of this tile, message rows of the next tile
+    fetch_row(tp, g, live, trow);
+    const float uu = live ? __ldg(p.u + g) : 0.0f;
+    const long long gn = (blk + gridDim.x) * 128 + row;
+    const bool live_next = (blk + gridDim.x < nblk) && frame_live(gn);
+    fetch_row(ap, gn, live_next, anext);
+    mbar_wait(mbar_sa, parity);
+    parity ^= 1u;
+    TC_FENCE_AFTER();
+#pragma unroll
+    for (int i = 0; i < HG::MAXG; i++) {
+      const int gi = part + 4 * i;
+      if (gi < HG::G) {
+        const int c = 8 * gi;
+        uint32_t tr[16];
+        tmem_ld8(taddr + (uint32_t)c, tr);
+        const float a8[8] = {arow[i][0].x, arow[i][0].y, arow[i][0].z, arow[i][0].w,
+                             arow[i][1].x, arow[i][1].y, arow[i][1].z, arow[i][1].w};
+        const float t8[8] = {trow[i][0].x, trow[i][0].y, trow[i][0].z, trow[i][0].w,
+                             trow[i][1].x, trow[i][1].y, trow[i][1].z, trow[i][1].w};
+        unsigned bits = 0u;
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+          const float P = __uint_as_float(tr[q]);
+          const float thr = uu * t8[q];
+          const bool st = live && (c + q < K) && (P <= thr) && (P + a8[q] * pjj_s[(c + q) & 127] > thr);
+          bits |= (st ? 1u : 0u) << q;
+        }
+        sbits[row][gi] = (unsigned char)bits;
+      }
+    }
+    TC_FENCE_BEFORE();
+    __syncthreads();
+    if (part == 0 && g < frames)
+      *reinterpret_cast<uint4*>(p.stay + g * 4) = *reinterpret_cast<const uint4*>(&sbits[row][0]);
+    live = live_next;
+#pragma unroll
+    for (int i = 0; i < HG::MAXG; i++) {
+      arow[i][0] = anext[i][0];
+      arow[i][1] = anext[i][1];
+    }
+  }
+  if (warp == 0)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "n"(C::TMEM_COLS));
+}
+
+template <int KD, int NP>
+static int launch_hmm_tc(const HmmTcArgs& a, cudaStream_t st) {
+  using C = HTC<KD, NP>;
+  auto kf = hmm_forward_tc_kernel<KD, NP>;
+  auto ks = hmm_stay_tc_kernel<KD, NP>;
+  KPMS_CUDA(cudaFuncSetAttribute(kf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
+  KPMS_CUDA(cudaFuncSetAttribute(ks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
+  const long long units = (long long)a.N * a.nch;
+  kf<<<(unsigned)((units + 127) / 128), HTC_THREADS, C::SMEM, st>>>(a);
+  int rc = kpms_last_launch();
+  if (rc) return rc;
+  const long long nblk = ((long long)a.N * a.Tm + 127) / 128;
+  ks<<<(unsigned)(nblk < 148 ? nblk : 148), HTC_THREADS, C::SMEM, st>>>(a);
+  return kpms_last_launch();
+}
+
+// Tensor-core forward filter + stay bits.  Returns KPMS_ERR_UNSUPPORTED when K has no instantiation.
+int kpms_hmm_forward_tc(const float* ll, const float* mask, long long mask_stride, const double* pi,
+                        const float* u, const int* tv, int N, int Tm, int K, int chunk_len, int burn_in,
+                        int nch, float* rowmax, float* a_out, float* T_out, unsigned* stay, double* llpart,
+                        float* bnd, unsigned* err_bits, cudaStream_t st) {
+  // rows are moved as float4; K = 128 would need 256 KB of operand tiles
+  if (K > 104 || (K & 3)) return KPMS_ERR_UNSUPPORTED;
+  (void)rowmax;
+  int rc = 0;
+  if (err_bits) {
+    hmm_mask_check_kernel<<<N, 256, 0, st>>>(mask, mask_stride, Tm, tv, err_bits);
+    rc = kpms_last_launch();
+    if (rc) return rc;
+  }
+  HmmTcArgs a{ll, rowmax, pi, u, tv, a_out, T_out, stay, llpart, bnd, N, Tm, K, chunk_len, burn_in, nch};
+  if (K <= 32) return launch_hmm_tc<32, 32>(a, st);
+  if (K <= 64) return launch_hmm_tc<64, 64>(a, st);
+  return launch_hmm_tc<104, 112>(a, st);
+}

@@ -1,0 +1,78 @@
+// Helpers shared by the tcgen05 (5th-generation tensor core) kernels: TF32 splitting, UMMA
+// shared-memory descriptors for the K-major no-swizzle layout, TMEM allocation, MMA issue,
+// mbarrier wait and TMEM loads.
+//
+// K-major no-swizzle operand layout (16-byte units): element (row r, k) of a tile lives at
+//   (r / 8) * SBO + (k / 4) * LBO + (r % 8) * 16 + (k % 4) * 4   bytes,  LBO = 128, SBO = (KD/4)*128
+// i.e. 8-row x 16-byte "core matrices", consecutive along K, then along the rows.
+#pragma once
+#include "common.cuh"
+
+#define TC_LBO 128
+
+__device__ __forceinline__ uint32_t tf32_rna(float v) {
+  uint32_t u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v));
+  return u;
+}
+
+__device__ __forceinline__ size_t umma_off(int r, int k, int sbo) {
+  return (size_t)(r / 8) * sbo + (size_t)(k / 4) * TC_LBO + (r % 8) * 16 + (k % 4) * 4;
+}
+
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;  // descriptor version (Blackwell)
+  return d;                 // base offset 0, layout type 0 = no swizzle
+}
+
+// instruction descriptor: F32 accumulate, TF32 x TF32, both operands K-major, M = 128
+__host__ __device__ constexpr uint32_t umma_idesc_tf32_m128(int n) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+}
+
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem_d),
+      "l"(da), "l"(db), "r"(idesc), "r"(acc));
+}
+
+__device__ __forceinline__ void umma_commit(uint32_t mbar_sa) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(mbar_sa));
+}
+
+__device__ __forceinline__ void mbar_wait(uint32_t mbar_sa, uint32_t parity) {
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}\n"
+        : "=r"(done)
+        : "r"(mbar_sa), "r"(parity));
+  }
+}
+
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, "
+      "%13, %14, %15}, [%16];\n"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::);
+}
+
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];\n"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::);
+}
+
+#define TC_FENCE_BEFORE() asm volatile("tcgen05.fence::before_thread_sync;\n" ::)
+#define TC_FENCE_AFTER() asm volatile("tcgen05.fence::after_thread_sync;\n" ::)
+#define TC_FENCE_PROXY() asm volatile("fence.proxy.async.shared::cta;\n" ::)

@@ -30,22 +30,28 @@ last_latents_boundary_err = None
 # HMM forward-filter chunking (K <= 128): same idea; the filter forgets its start geometrically.
 # "auto" cuts sessions so that about three CTAs per SM are busy; mismatch above `tol` (absolute,
 # on potentials that sum to one) triggers an exact re-run when strict.
-STATESEQ_CHUNKING = {"chunk_len": "auto", "burn_in": 1024, "strict": True, "tol": 1e-5}
+STATESEQ_CHUNKING = {"chunk_len": "auto", "burn_in": 256, "strict": True, "tol": 1e-5}
 HMM_CTAS_PER_SM = 3
 last_stateseq_boundary_err = None
 
 
-def auto_hmm_chunk_len(N, Tm, burn_in, device):
-    slots = torch.cuda.get_device_properties(device).multi_processor_count * HMM_CTAS_PER_SM
-    nch = max(1, slots // max(N, 1))
-    cl = -(-Tm // nch)
-    if nch == 1 or cl < 4 * max(burn_in, 1):
-        cl = 4 * max(burn_in, 1)
-    return 0 if cl >= Tm else cl
+def auto_hmm_chunk_len(N, Tm, K, burn_in, device):
+    """Chunk length of the forward filter.  K <= 104 with K % 4 == 0 runs on the tensor cores,
+    128 chains per CTA: aim at one CTA per SM but keep a chunk at least as long as its warm-up.
+    Other K use the CUDA-core kernel (one CTA per chain, three resident per SM), where longer
+    chunks keep the warm-up overhead small."""
+    sms = torch.cuda.get_device_properties(device).multi_processor_count
+    if K <= 104 and K % 4 == 0:
+        nch = max(1, sms * 128 // max(N, 1))
+        cl = max(-(-Tm // nch), max(burn_in, 1))
+    else:
+        nch = max(1, sms * 3 // max(N, 1))
+        cl = max(-(-Tm // nch), 4 * max(burn_in, 1))
+    return 0 if 2 * cl >= Tm else cl
 
 
 def auto_chunk_len(N, T, L, burn_in, device):
-    """Chunk length such that N * n_chunks is just under one wave of resident warps."""
+    """Kalman chunk length such that N * n_chunks is just under one wave of resident warps."""
     Tt = T - L
     slots = torch.cuda.get_device_properties(device).multi_processor_count * KALMAN_WARPS_PER_SM
     nch = max(1, slots // max(N, 1))
@@ -88,7 +94,7 @@ def _hmm_chunking(N, Tm, K, chunk_len, burn_in, strict, dev):
     burn_in = STATESEQ_CHUNKING["burn_in"] if burn_in is None else burn_in
     strict = STATESEQ_CHUNKING["strict"] if strict is None else strict
     if chunk_len == "auto":
-        chunk_len = auto_hmm_chunk_len(N, Tm, int(burn_in), dev) if K <= 128 else 0
+        chunk_len = auto_hmm_chunk_len(N, Tm, K, int(burn_in), dev) if K <= 128 else 0
     return int(chunk_len), int(burn_in), bool(strict)
 
 

@@ -386,7 +386,7 @@ def test_hmm_chunked_forward_matches_exact(G):
     z1, l1, i1 = G.sample_hmm_stateseqs(chunk_len=1500, burn_in=512, strict=False, **kw)
     assert float(i0['boundary_err']) == 0.0 and float(i1['boundary_err']) < 1e-5
     assert float((z0 != z1).float().mean()) < 1e-3
-    assert np.all(np.abs(N_(l0) - N_(l1)) <= 1e-6 * np.abs(N_(l0)))
+    assert np.all(np.abs(N_(l0) - N_(l1)) <= 1e-5 * np.abs(N_(l0)))   # north_star tolerance
     zo, lo = O._hmm_batch(ll, mask, pi, u)
     valid = mask > 0
     assert (N_(z1)[valid] == zo[valid]).mean() >= 0.999
