@@ -11,9 +11,10 @@ scaling: per-GPU work is fixed).  Data are synthetic draws from the model (SURVE
 
 A "step" is one full sweep (the eight resample_* steps of keypoint_slds.ipynb cell 12).
 `value`  : inputs resident in HBM, CUDA events, max over ranks.
-`e2e`    : the same sweep driven from pinned HOST buffers — every step copies Y, mask and all
-           states to the device, runs the sweep through the public API, and reads the new
-           states and parameters back.
+`e2e`    : the same sweep driven from pinned HOST buffers through parallel.gibbs_sweep_host —
+           every step copies Y, mask and all states to the device (copy stream, ordered by first
+           use), runs the sweep, and reads the new states and parameters back (second copy
+           stream, each state as soon as it is final); the step ends when the host copies do.
 `roofline`: the dominant entry point (kpms_resample_latents: Kalman filter + sampler) timed
            alone with CUDA events on the launching stream.
 `cpu_baseline` / `--impl reference`: the float64 NumPy+numba oracle (the reference's JAX
@@ -304,11 +305,9 @@ def main():
 
         def e2e_step(i, pp_):
             nonlocal par_host
-            dd = {a: b.to(dev, non_blocking=True) for a, b in host.items()}
-            s_in = {a: b.to(dev, non_blocking=True) for a, b in host_st.items()}
-            s_new, p_new = sweep(i, dd, s_in, pp_)
-            for a in out_host:
-                out_host[a].copy_(s_new[a], non_blocking=True)
+            # public host-side API: uploads ordered by first use, downloads as states become final
+            _, p_new, _ = parallel.gibbs_sweep_host((0, i), host, host_st, pp_, hyp, Gamma=Gm,
+                                                    n_sessions_global=N * world, out=out_host, device=dev)
             par_host = {a: b.cpu() for a, b in p_new.items()}   # small; synchronises the step
             return p_new
         pe = p

@@ -343,6 +343,35 @@ def test_full_sweep_runs_with_library_rng(G):
     assert float((S_y / (2 * m)).max()) < 5.0
 
 
+def test_host_pipelined_sweep_equals_device_sweep(G):
+    """parallel.gibbs_sweep_host (uploads ordered by first use, observation statistics deferred
+    past the state sequences, downloads as states become final) must give the very same states
+    and parameters as parallel.gibbs_sweep on device-resident inputs."""
+    import torch
+    from keypointmoseq_b200 import parallel
+    N, T, k, dk, D, L, K = 3, 300, 8, 2, 10, 3, 10
+    d, s, p, Gm = H.problem(seed=77, N=N, T=T, k=k, dk=dk, D=D, L=L, K=K, ragged=True)
+    hp = H.hyp(D, L, K)
+    hpt = {a: (T_(b) if isinstance(b, np.ndarray) else b) for a, b in hp.items()}
+    host_d = {a: torch.as_tensor(b, dtype=torch.float32).pin_memory() for a, b in d.items()}
+    host_s = {a: (torch.as_tensor(b, dtype=torch.float32) if a != 'z' else torch.as_tensor(b.astype(np.int32))).pin_memory()
+              for a, b in s.items()}
+    pr = {a: T_(b) for a, b in p.items()}
+    dev_d = {a: b.cuda() for a, b in host_d.items()}
+    dev_s = {a: b.cuda() for a, b in host_s.items()}
+    st1, pr1 = parallel.gibbs_sweep((3, 1), dev_d, dev_s, pr, hpt, Gamma=T_(Gm))
+    out, pr2, st2 = parallel.gibbs_sweep_host((3, 1), host_d, host_s, pr, hpt, Gamma=T_(Gm))
+    torch.cuda.synchronize()
+    for name in ('z', 'x', 'h', 'v', 's'):
+        assert torch.equal(st1[name].cpu(), out[name]), name
+        assert torch.equal(st2[name].cpu(), out[name]), name
+    for name in pr1:
+        assert torch.equal(pr1[name], pr2[name]), name
+    # a second call reuses the output buffers
+    out2, _, _ = parallel.gibbs_sweep_host((3, 1), host_d, host_s, pr, hpt, Gamma=T_(Gm), out=out)
+    assert out2 is out and torch.equal(st1['x'].cpu(), out['x'])
+
+
 def test_cpu_tensor_is_rejected(G):
     import torch
     from keypointmoseq_b200._lib import KpmsError
