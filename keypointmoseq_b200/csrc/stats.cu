@@ -4,7 +4,7 @@
 
 // ======================================================================== a8: AR statistics
 // Reference: gibbs.py:129-131 (S_out_out, S_out_in, S_in_in), :141-143 (dense one-hot masks).
-// Instead of the reference's dense (K, frames) one-hot, CTA (part, k) scans its slice of z,
+// (Fallback path; the production kernel is ar_stats.cu.)  Instead of the reference's dense (K, frames) one-hot, CTA (part, k) scans its slice of z,
 // compacts the frames whose state is k (deterministic block prefix-sum order), stages their
 // regressors f = [x[t-L..t-1], 1, x[t]] in shared memory as fp64 and accumulates the lower
 // triangle of sum f f^T with one thread per matrix entry.  Per-part partials are combined in
@@ -23,7 +23,7 @@ static inline int ars_parts(long long frames, int K) {
   return (int)p;
 }
 
-extern "C" size_t kpms_ar_stats_workspace_bytes(int N, int T, int D, int L, int K) {
+size_t kpms_ar_stats_scan_workspace_bytes(int N, int T, int D, int L, int K) {
   if (N <= 0 || T <= L || D <= 0 || L <= 0 || K <= 0) return 0;
   const int P = D * L + 1 + D;
   const int parts = ars_parts((long long)N * (T - L), K);
@@ -127,15 +127,16 @@ __global__ void ar_stats_reduce_kernel(const double* __restrict__ partial, int p
   }
 }
 
-extern "C" int kpms_ar_stats(const float* x, const int32_t* z, const float* mask, int N, int T,
-                             int D, int L, int K, double* F, void* workspace,
-                             size_t workspace_bytes, void* stream) {
+// Generic fallback of kpms_ar_stats (ar_stats.cu) for regressor lengths beyond its DMMA tiling.
+int kpms_ar_stats_scan(const float* x, const int32_t* z, const float* mask, int N, int T,
+                       int D, int L, int K, double* F, void* workspace,
+                       size_t workspace_bytes, void* stream) {
   KPMS_REQUIRE(x && z && mask && F && workspace, KPMS_ERR_NULL);
   KPMS_REQUIRE(N > 0 && T > L && D > 0 && L > 0 && K > 0, KPMS_ERR_SHAPE);
   const int P = D * L + 1 + D;
   KPMS_REQUIRE(P * (P + 1) / 2 <= ARS_ACC * ARS_THREADS && K <= 65535, KPMS_ERR_UNSUPPORTED);
   KPMS_REQUIRE(kpms_aligned(workspace, 256) &&
-                   workspace_bytes >= kpms_ar_stats_workspace_bytes(N, T, D, L, K),
+                   workspace_bytes >= kpms_ar_stats_scan_workspace_bytes(N, T, D, L, K),
                KPMS_ERR_WORKSPACE);
   cudaStream_t st = (cudaStream_t)stream;
   const long long frames = (long long)N * (T - L);
