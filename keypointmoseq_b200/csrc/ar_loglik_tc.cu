@@ -249,7 +249,8 @@ static int launch_tc(const float* x, const float* Wf, const float* cst, int N, i
   auto kern = ar_loglik_tc_kernel<DD, LL>;
   KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const long long nblk = ((long long)N * (T - LL) + TC_M - 1) / TC_M;
-  long long stripes = 148 / ntiles;
+  // two CTAs per SM when the operand tiles allow it: one CTA's epilogue overlaps the other's MMAs
+  long long stripes = (smem <= 112 * 1024 ? 2 : 1) * 148 / ntiles;
   if (stripes < 1) stripes = 1;
   if (stripes > nblk) stripes = nblk;
   if (ntiles > 65535) return KPMS_ERR_UNSUPPORTED;

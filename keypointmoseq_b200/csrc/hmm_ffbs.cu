@@ -38,9 +38,21 @@ struct HmmWs {
   double* llpart;
   float* bnd;   // [N][nch][2][K]
   int* tv;
-  float* Tbuf;    // [N][Tm][K] a @ pi of the tensor-core forward pass (chunked mode only)
+  float* Tbuf;    // a @ pi of the tensor-core forward pass (chunked mode only), tiled like alphan
   float* rowmax;  // [N][Tm]
+  // Message layout.  tiled == 0: alphan[n][t][j].  tiled == 1 (tensor-core forward pass): the
+  // chunk chains u = n*nch + t/chunk_len are interleaved 128 at a time so that a CTA stepping 128
+  // chains moves whole 512-byte lines:  float4 index (((u/128)*CL + t%CL) * K/4 + j/4) * 128 + u%128.
+  int tiled, tile_cl, tile_nch;
 };
+
+__device__ __forceinline__ size_t hmm_msg_base4(const HmmWs& ws, int n, int t, int Tm, int K) {
+  // float4 index of chunk 0 of message (n, t); chunk kc lives kc * (tiled ? 128 : 1) further
+  if (!ws.tiled) return ((size_t)n * Tm + t) * (K >> 2);
+  const int cc = t / ws.tile_cl, r = t - cc * ws.tile_cl;
+  const int u = n * ws.tile_nch + cc;
+  return (((size_t)(u >> 7) * ws.tile_cl + r) * (K >> 2)) * 128 + (u & 127);
+}
 
 static size_t hmm_layout(int N, int Tm, int K, int chunk_len, void* base, HmmWs* ws) {
   const int nch = hmm_nchunks(Tm, chunk_len);
@@ -52,7 +64,9 @@ static size_t hmm_layout(int N, int Tm, int K, int chunk_len, void* base, HmmWs*
     return b ? (void*)(b + o) : nullptr;
   };
   void* p;
-  p = take((size_t)N * Tm * K * sizeof(float)); if (ws) ws->alphan = (float*)p;
+  // chunked mode may use the tiled layout: units padded to 128, chunks to their full length
+  const size_t msg = (nch > 1) ? (size_t)((N * (size_t)nch + 127) / 128 * 128) * chunk_len * K : (size_t)N * Tm * K;
+  p = take(msg * sizeof(float)); if (ws) ws->alphan = (float*)p;
   p = take((size_t)K * K * sizeof(float)); if (ws) ws->pf = (float*)p;
   p = take((size_t)K * K * sizeof(float)); if (ws) ws->pT = (float*)p;
   p = take((size_t)N * Tm * 4 * sizeof(unsigned)); if (ws) ws->stay = (unsigned*)p;
@@ -60,11 +74,16 @@ static size_t hmm_layout(int N, int Tm, int K, int chunk_len, void* base, HmmWs*
   p = take((size_t)N * nch * 2 * K * sizeof(float)); if (ws) ws->bnd = (float*)p;
   p = take((size_t)N * sizeof(int)); if (ws) ws->tv = (int*)p;
   if (nch > 1 && K <= 128) {
-    p = take((size_t)N * Tm * K * sizeof(float)); if (ws) ws->Tbuf = (float*)p;
+    p = take(msg * sizeof(float)); if (ws) ws->Tbuf = (float*)p;
     p = take((size_t)N * Tm * sizeof(float)); if (ws) ws->rowmax = (float*)p;
   } else if (ws) {
     ws->Tbuf = nullptr;
     ws->rowmax = nullptr;
+  }
+  if (ws) {
+    ws->tiled = 0;
+    ws->tile_cl = chunk_len;
+    ws->tile_nch = nch;
   }
   return off;
 }
@@ -320,12 +339,17 @@ __global__ void __launch_bounds__(32)
     const int fb = t - r;  // first unsettled frame (unmasked by construction) if it exists
     if (r < 32 && fb >= 0) {
       const float ub = __uint_as_float(bring[(fb % HMM_BRING) * 8 + 4]);
+      const size_t mb4 = ws.tiled ? hmm_msg_base4(ws, n, fb, Tm, K) : 0;
       float w[PER];
       float run = 0.0f;
 #pragma unroll
       for (int q = 0; q < PER; q++) {
         const int st = lane * PER + q;
-        const float al = (st < K) ? al_n[(size_t)fb * K + st] : 0.0f;
+        float al = 0.0f;
+        if (st < K) {
+          if (ws.tiled) al = ws.alphan[(mb4 + (size_t)(st >> 2) * 128) * 4 + (st & 3)];
+          else al = al_n[(size_t)fb * K + st];
+        }
         const float np = (s_next < 0) ? 1.0f : piT[s_next * KP + st];
         run = fmaf(np, al, run);
         w[q] = run;  // inclusive prefix within the lane
@@ -473,6 +497,8 @@ static int launch_reg(const float* ll, const float* mask, long long ms, const do
   if (rc == KPMS_ERR_UNSUPPORTED) {
     hmm_forward_kernel<KP><<<N * nch, KP, 0, st>>>(ll, mask, ms, pi, u, Tm, K, chunk_len, burn_in, loglik, ws);
     rc = kpms_last_launch();
+  } else {
+    ws.tiled = 1;  // the tensor-core pass wrote interleaved messages
   }
   if (rc) return rc;
   hmm_finish_kernel<<<N, 128, 0, st>>>(ws, nch, K, chunk_len, loglik, (unsigned*)boundary_err);

@@ -221,6 +221,7 @@ __global__ void __launch_bounds__(HTC_THREADS, 1) hmm_forward_tc_kernel(HmmTcArg
   const uint32_t b_hi_sa = (uint32_t)__cvta_generic_to_shared(sB_hi), b_lo_sa = (uint32_t)__cvta_generic_to_shared(sB_lo);
   const size_t rowoff = (size_t)(row / 8) * C::SBO + (row % 8) * 16;
   const float LOG2E = 1.4426950408889634f;
+  const int KC4 = K >> 2;
 
   double logtot = 0.0, prod = 1.0;  // marginal log-likelihood = log prod(norm) + sum(cmax)
   float cmax_prev = 0.0f;
@@ -254,8 +255,9 @@ __global__ void __launch_bounds__(HTC_THREADS, 1) hmm_forward_tc_kernel(HmmTcArg
                               : 0.0f;
     cmax_prev = cmax;
     const float inva = active ? inv : 0.0f;
-    float* ar = aout + (rowbase + t) * K;
-    float* Tr = tout + (rowbase + t - 1) * K;
+    // interleaved message tiles (hmm_ffbs.cu: HmmWs): float4 index ((b*CL + r)*K/4 + kc)*128 + row
+    float4* ar4 = reinterpret_cast<float4*>(aout) + ((size_t)blockIdx.x * p.chunk_len + (t - t0)) * KC4 * 128 + row;
+    float4* Tr4 = reinterpret_cast<float4*>(tout) + ((size_t)blockIdx.x * p.chunk_len + (t - 1 - t0)) * KC4 * 128 + row;
     float sum = 0.0f;
 #pragma unroll
     for (int i = 0; i < HG::MAXG; i++) {
@@ -273,8 +275,8 @@ __global__ void __launch_bounds__(HTC_THREADS, 1) hmm_forward_tc_kernel(HmmTcArg
           for (int q = 0; q < 8; q++) Tv[q] = 1.0f;
         }
         if (prev_store) {
-          if (c < K) *reinterpret_cast<float4*>(Tr + c) = make_float4(Tv[0], Tv[1], Tv[2], Tv[3]);
-          if (c + 4 < K) *reinterpret_cast<float4*>(Tr + c + 4) = make_float4(Tv[4], Tv[5], Tv[6], Tv[7]);
+          if (c < K) Tr4[(size_t)(2 * g) * 128] = make_float4(Tv[0], Tv[1], Tv[2], Tv[3]);
+          if (c + 4 < K) Tr4[(size_t)(2 * g + 1) * 128] = make_float4(Tv[4], Tv[5], Tv[6], Tv[7]);
         }
         if (bstart || bend) {
           float* bd = p.bnd + ((size_t)(n * nch + cc) * 2 + (bstart ? 0 : 1)) * K;
@@ -292,8 +294,8 @@ __global__ void __launch_bounds__(HTC_THREADS, 1) hmm_forward_tc_kernel(HmmTcArg
         }
         sum += ((a8[0] + a8[1]) + (a8[2] + a8[3])) + ((a8[4] + a8[5]) + (a8[6] + a8[7]));
         if (store) {
-          if (c < K) *reinterpret_cast<float4*>(ar + c) = make_float4(a8[0], a8[1], a8[2], a8[3]);
-          if (c + 4 < K) *reinterpret_cast<float4*>(ar + c + 4) = make_float4(a8[4], a8[5], a8[6], a8[7]);
+          if (c < K) ar4[(size_t)(2 * g) * 128] = make_float4(a8[0], a8[1], a8[2], a8[3]);
+          if (c + 4 < K) ar4[(size_t)(2 * g + 1) * 128] = make_float4(a8[4], a8[5], a8[6], a8[7]);
         }
         const size_t off = rowoff + (size_t)(2 * g) * TC_LBO;
         *reinterpret_cast<uint4*>(sA_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
@@ -369,40 +371,47 @@ __global__ void __launch_bounds__(HTC_THREADS, 1) hmm_stay_tc_kernel(HmmTcArgs p
   const uint32_t a_hi_sa = (uint32_t)__cvta_generic_to_shared(sA_hi), a_lo_sa = (uint32_t)__cvta_generic_to_shared(sA_lo);
   const uint32_t b_hi_sa = (uint32_t)__cvta_generic_to_shared(sB_hi), b_lo_sa = (uint32_t)__cvta_generic_to_shared(sB_lo);
   const size_t rowoff = (size_t)(row / 8) * C::SBO + (row % 8) * 16;
-  const long long frames = (long long)p.N * Tm;
-  const long long nblk = (frames + 127) / 128;
-  const float* __restrict__ ap = p.a_out;
-  const float* __restrict__ tp = p.T_out;
+  // one tile = the 128 chains of a forward CTA at one in-chunk offset r (interleaved layout)
+  const long long units = (long long)p.N * p.nch;
+  const long long nblk = ((units + 127) / 128) * p.chunk_len;
+  const int KC4 = K >> 2;
+  const float4* __restrict__ ap = reinterpret_cast<const float4*>(p.a_out);
+  const float4* __restrict__ tp = reinterpret_cast<const float4*>(p.T_out);
   uint32_t parity = 0;
 
-  auto frame_live = [&](long long g) {
-    if (g >= frames) return false;
-    const int n = (int)(g / Tm), t = (int)(g % Tm);
-    return t < p.tv[n];  // masked frames carry no message
+  // frame of this thread's row in tile blk: -1 when the row carries no message there
+  auto frame_of = [&](long long blk, bool& inrange) -> long long {
+    inrange = false;
+    if (blk >= nblk) return -1;
+    const long long b = blk / p.chunk_len;
+    const int r = (int)(blk - b * p.chunk_len);
+    const long long u = b * 128 + row;
+    if (u >= units) return -1;
+    const int n = (int)(u / p.nch), cc = (int)(u % p.nch);
+    const int t = cc * p.chunk_len + r;
+    if (t >= Tm) return -1;
+    inrange = true;
+    const long long g = (long long)n * Tm + t;
+    return (t < p.tv[n]) ? g : -(g + 2);  // masked frames carry no message: encoded as negative
   };
-  auto fetch_row = [&](const float* __restrict__ base, long long g, bool live, float4 (&dst)[HG::MAXG][2]) {
-    const float* r = base + g * K;
+  auto fetch_row = [&](const float4* __restrict__ base, long long blk, bool live, float4 (&dst)[HG::MAXG][2]) {
+    const float4* r = base + (size_t)blk * KC4 * 128 + row;
 #pragma unroll
     for (int i = 0; i < HG::MAXG; i++) {
-      const int c = 8 * (part + 4 * i);
-      if (live && c + 4 < K) {
-        ldg8(r + c, true, 0.f, dst[i][0], dst[i][1]);
-      } else if (live && c < K) {
-        dst[i][0] = __ldg(reinterpret_cast<const float4*>(r + c));
-        dst[i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
-      } else {
-        dst[i][0] = make_float4(0.f, 0.f, 0.f, 0.f);
-        dst[i][1] = dst[i][0];
-      }
+      const int gi = part + 4 * i;
+      const int c = 8 * gi;
+      dst[i][0] = (live && c < K) ? __ldg(r + (size_t)(2 * gi) * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
+      dst[i][1] = (live && c + 4 < K) ? __ldg(r + (size_t)(2 * gi + 1) * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
   };
 
   float4 arow[HG::MAXG][2], anext[HG::MAXG][2], trow[HG::MAXG][2];
   long long blk = blockIdx.x;
-  bool live = frame_live(blk * 128 + row);
-  if (blk < nblk) fetch_row(ap, blk * 128 + row, live, arow);
+  bool inr = false;
+  long long g = frame_of(blk, inr);
+  bool live = g >= 0;
+  if (blk < nblk) fetch_row(ap, blk, live, arow);
   for (; blk < nblk; blk += gridDim.x) {
-    const long long g = blk * 128 + row;
 #pragma unroll
     for (int i = 0; i < HG::MAXG; i++) {
       const int gi = part + 4 * i;
@@ -430,11 +439,12 @@ __global__ void __launch_bounds__(HTC_THREADS, 1) hmm_stay_tc_kernel(HmmTcArgs p
       issue_3xtf32<KD, NP>(tmem_base, a_hi_sa, a_lo_sa, b_hi_sa, b_lo_sa, mbar_sa);
     }
     // while the tensor core works: T row and u of this tile, message rows of the next tile
-    fetch_row(tp, g, live, trow);
+    fetch_row(tp, blk, live, trow);
     const float uu = live ? __ldg(p.u + g) : 0.0f;
-    const long long gn = (blk + gridDim.x) * 128 + row;
-    const bool live_next = (blk + gridDim.x < nblk) && frame_live(gn);
-    fetch_row(ap, gn, live_next, anext);
+    bool inr_next = false;
+    const long long g_next = frame_of(blk + gridDim.x, inr_next);
+    const bool live_next = g_next >= 0;
+    fetch_row(ap, blk + gridDim.x, live_next, anext);
     mbar_wait(mbar_sa, parity);
     parity ^= 1u;
     TC_FENCE_AFTER();
@@ -462,9 +472,13 @@ __global__ void __launch_bounds__(HTC_THREADS, 1) hmm_stay_tc_kernel(HmmTcArgs p
     }
     TC_FENCE_BEFORE();
     __syncthreads();
-    if (part == 0 && g < frames)
-      *reinterpret_cast<uint4*>(p.stay + g * 4) = *reinterpret_cast<const uint4*>(&sbits[row][0]);
+    if (part == 0 && inr) {
+      const long long gg = (g >= 0) ? g : -(g + 2);
+      *reinterpret_cast<uint4*>(p.stay + gg * 4) = *reinterpret_cast<const uint4*>(&sbits[row][0]);
+    }
     live = live_next;
+    g = g_next;
+    inr = inr_next;
 #pragma unroll
     for (int i = 0; i < HG::MAXG; i++) {
       arow[i][0] = anext[i][0];
@@ -486,7 +500,7 @@ static int launch_hmm_tc(const HmmTcArgs& a, cudaStream_t st) {
   kf<<<(unsigned)((units + 127) / 128), HTC_THREADS, C::SMEM, st>>>(a);
   int rc = kpms_last_launch();
   if (rc) return rc;
-  const long long nblk = ((long long)a.N * a.Tm + 127) / 128;
+  const long long nblk = ((units + 127) / 128) * a.chunk_len;
   ks<<<(unsigned)(nblk < 148 ? nblk : 148), HTC_THREADS, C::SMEM, st>>>(a);
   return kpms_last_launch();
 }
