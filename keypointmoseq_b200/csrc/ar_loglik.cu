@@ -141,11 +141,15 @@ static int launch_simt(const float* x, const float* Wf, const float* cst, int N,
 }
 
 int kpms_ar_loglik_tc(const float* x, const float* Wf, const float* cst, int N, int T, int D, int L,
-                      int K, float* ll, void* tiles, size_t tile_bytes, cudaStream_t st);  // ar_loglik_tc.cu
+                      int K, float* ll, void* tiles, size_t tile_bytes, int tile_cl, int tile_nch,
+                      cudaStream_t st);  // ar_loglik_tc.cu
 
-extern "C" int kpms_ar_loglik(const float* x, const double* Ab, const double* Q, int N, int T,
-                              int D, int L, int K, float* ll, void* workspace,
-                              size_t workspace_bytes, int impl, void* stream) {
+// tile_cl > 0 asks for ll in the HMM's interleaved layout (tensor-core kernel only); *wrote_tiled
+// reports whether that happened — otherwise ll is (N, T-L, K) row-major.
+int kpms_ar_loglik_impl(const float* x, const double* Ab, const double* Q, int N, int T, int D, int L,
+                        int K, float* ll, void* workspace, size_t workspace_bytes, int impl,
+                        int tile_cl, int tile_nch, int* wrote_tiled, void* stream) {
+  if (wrote_tiled) *wrote_tiled = 0;
   KPMS_REQUIRE(x && Ab && Q && ll && workspace, KPMS_ERR_NULL);
   KPMS_REQUIRE(N > 0 && T > L && D > 0 && L > 0 && K > 0, KPMS_ERR_SHAPE);
   KPMS_REQUIRE(D <= AR_DMAX && kpms_dl_supported(D, L), KPMS_ERR_UNSUPPORTED);
@@ -161,7 +165,13 @@ extern "C" int kpms_ar_loglik(const float* x, const double* Ab, const double* Q,
   int rc = kpms_last_launch();
   if (rc) return rc;
   if (impl == 0) {
-    rc = kpms_ar_loglik_tc(x, Wf, cst, N, T, D, L, K, ll, tiles, kpms_ar_tc_tile_bytes(K, D, L), st);
+    if (tile_cl > 0) {
+      rc = kpms_ar_loglik_tc(x, Wf, cst, N, T, D, L, K, ll, tiles, kpms_ar_tc_tile_bytes(K, D, L), tile_cl,
+                             tile_nch, st);
+      if (rc == KPMS_OK && wrote_tiled) *wrote_tiled = 1;
+      if (rc != KPMS_ERR_UNSUPPORTED) return rc;
+    }
+    rc = kpms_ar_loglik_tc(x, Wf, cst, N, T, D, L, K, ll, tiles, kpms_ar_tc_tile_bytes(K, D, L), 0, 0, st);
     if (rc != KPMS_ERR_UNSUPPORTED) return rc;
   }
 #define KPMS_X(d, l) \
@@ -169,6 +179,13 @@ extern "C" int kpms_ar_loglik(const float* x, const double* Ab, const double* Q,
   KPMS_FOR_EACH_DL(KPMS_X)
 #undef KPMS_X
   return KPMS_ERR_UNSUPPORTED;
+}
+
+extern "C" int kpms_ar_loglik(const float* x, const double* Ab, const double* Q, int N, int T,
+                              int D, int L, int K, float* ll, void* workspace,
+                              size_t workspace_bytes, int impl, void* stream) {
+  return kpms_ar_loglik_impl(x, Ab, Q, N, T, D, L, K, ll, workspace, workspace_bytes, impl, 0, 0, nullptr,
+                             stream);
 }
 
 // ======================================================================================
@@ -251,7 +268,7 @@ extern "C" int kpms_ar_loglik_static(const float* x, const double* Ab, const dou
     float* tiles = cst + kpms_round_up((size_t)K, 64);
     const size_t used = (size_t)(tiles - base);
     const size_t left = used < (size_t)KPMS_AR_STATIC_FLOATS ? ((size_t)KPMS_AR_STATIC_FLOATS - used) * sizeof(float) : 0;
-    rc = kpms_ar_loglik_tc(x, Wf, cst, N, T, D, L, K, ll, tiles, left, st);
+    rc = kpms_ar_loglik_tc(x, Wf, cst, N, T, D, L, K, ll, tiles, left, 0, 0, st);
     if (rc != KPMS_ERR_UNSUPPORTED) return rc;
   }
 #define KPMS_X(d, l) \

@@ -73,7 +73,7 @@ template <int DD, int LL>
 __global__ void __launch_bounds__(TC_M, 1)
     ar_loglik_tc_kernel(const float* __restrict__ x, const unsigned char* __restrict__ tiles,
                         const float* __restrict__ cst, int N, int T, int K, int nstripes,
-                        float* __restrict__ ll) {
+                        int tile_cl, int tile_nch, float* __restrict__ ll) {
   using C = TC<DD, LL>;
   extern __shared__ __align__(1024) unsigned char smem[];
   unsigned char* sA_hi = smem;
@@ -88,7 +88,10 @@ __global__ void __launch_bounds__(TC_M, 1)
   const int k0 = tile * TC_STATES;
   const int Tm = T - LL;
   const long long frames = (long long)N * Tm;
-  const long long nblk = (frames + TC_M - 1) / TC_M;
+  // tile_cl > 0: block = one tile (b, r) of the HMM's interleaved layout (hmm_ffbs.cu: HmmWs) — row i is
+  // frame t = cc*tile_cl + r of chain u = 128 b + i = n*tile_nch + cc, and ll goes out as whole lines.
+  const long long units = (long long)N * tile_nch;
+  const long long nblk = (tile_cl > 0) ? ((units + 127) / 128) * tile_cl : (frames + TC_M - 1) / TC_M;
 
   // ---- one-time setup: weight tile, constants, barrier, tensor memory
   {
@@ -120,11 +123,24 @@ __global__ void __launch_bounds__(TC_M, 1)
 
   for (long long blk = stripe; blk < nblk; blk += nstripes) {
     // ---- A tile: thread r builds row r = frame blk*128 + r (hi and lo parts)
-    const long long g = blk * TC_M + tid;
-    const bool live = g < frames;
+    long long g = blk * TC_M + tid;
+    bool live = g < frames;
     {
       const float* xp = x;
-      if (live) {
+      if (tile_cl > 0) {
+        const long long b = blk / tile_cl;
+        const int r = (int)(blk - b * tile_cl);
+        const long long uu = b * 128 + tid;
+        live = false;
+        if (uu < units) {
+          const int n = (int)(uu / tile_nch), cc = (int)(uu % tile_nch);
+          const int tp = cc * tile_cl + r;
+          if (tp < Tm) {
+            live = true;
+            xp = x + ((size_t)n * T + tp) * DD;
+          }
+        }
+      } else if (live) {
         const int n = (int)(g / Tm), tp = (int)(g % Tm);
         xp = x + ((size_t)n * T + tp) * DD;  // lag window x[tp .. tp+L]: DL+DD contiguous floats
       }
@@ -207,7 +223,16 @@ __global__ void __launch_bounds__(TC_M, 1)
           q[(c0 + i) / DD] = fmaf(v, v, q[(c0 + i) / DD]);
         }
       }
-      if (live) {
+      if (live && tile_cl > 0) {
+        // interleaved layout: float4 index (blk * K/4 + kc) * 128 + row  (K % 4 == 0 guaranteed by the caller)
+        float4* out4 = reinterpret_cast<float4*>(ll) + ((size_t)blk * (K >> 2) + (k0 >> 2)) * 128 + tid;
+#pragma unroll
+        for (int s4 = 0; s4 < TC_STATES; s4 += 4)
+          if (k0 + s4 < K)
+            out4[(size_t)(s4 >> 2) * 128] =
+                make_float4(s_cst[s4] - 0.5f * q[s4], s_cst[s4 + 1] - 0.5f * q[s4 + 1],
+                            s_cst[s4 + 2] - 0.5f * q[s4 + 2], s_cst[s4 + 3] - 0.5f * q[s4 + 3]);
+      } else if (live) {
         float* out = ll + g * K + k0;
         if ((K & 3) == 0 && k0 + TC_STATES <= K) {
 #pragma unroll
@@ -239,7 +264,7 @@ size_t kpms_ar_tc_tile_bytes(int K, int D, int L) {
 
 template <int DD, int LL>
 static int launch_tc(const float* x, const float* Wf, const float* cst, int N, int T, int K, float* ll,
-                     unsigned char* tiles, cudaStream_t st) {
+                     unsigned char* tiles, int tile_cl, int tile_nch, cudaStream_t st) {
   using C = TC<DD, LL>;
   const int ntiles = (K + TC_STATES - 1) / TC_STATES;
   ar_tc_pack_kernel<DD, LL><<<ntiles, 256, 0, st>>>(Wf, K, tiles);
@@ -248,23 +273,27 @@ static int launch_tc(const float* x, const float* Wf, const float* cst, int N, i
   const size_t smem = 1024 + 2 * C::A_BYTES + 2 * C::B_BYTES + TC_STATES * sizeof(float) + 16;
   auto kern = ar_loglik_tc_kernel<DD, LL>;
   KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const long long nblk = ((long long)N * (T - LL) + TC_M - 1) / TC_M;
+  const long long nblk = (tile_cl > 0) ? (((long long)N * tile_nch + 127) / 128) * tile_cl
+                                       : ((long long)N * (T - LL) + TC_M - 1) / TC_M;
   // two CTAs per SM when the operand tiles allow it: one CTA's epilogue overlaps the other's MMAs
   long long stripes = (smem <= 112 * 1024 ? 2 : 1) * 148 / ntiles;
   if (stripes < 1) stripes = 1;
   if (stripes > nblk) stripes = nblk;
   if (ntiles > 65535) return KPMS_ERR_UNSUPPORTED;
-  kern<<<dim3(ntiles, (unsigned)stripes), TC_M, smem, st>>>(x, tiles, cst, N, T, K, (int)stripes, ll);
+  kern<<<dim3(ntiles, (unsigned)stripes), TC_M, smem, st>>>(x, tiles, cst, N, T, K, (int)stripes, tile_cl, tile_nch, ll);
   return kpms_last_launch();
 }
 
 // tiles == nullptr or too small -> KPMS_ERR_UNSUPPORTED (caller falls back to the CUDA-core kernel)
+// tile_cl > 0: write ll in the HMM's interleaved layout for that chunk length (needs K % 4 == 0)
 int kpms_ar_loglik_tc(const float* x, const float* Wf, const float* cst, int N, int T, int D, int L,
-                      int K, float* ll, void* tiles, size_t tile_bytes, cudaStream_t st) {
+                      int K, float* ll, void* tiles, size_t tile_bytes, int tile_cl, int tile_nch,
+                      cudaStream_t st) {
+  if (tile_cl > 0 && (K & 3)) return KPMS_ERR_UNSUPPORTED;
   if (tiles == nullptr || tile_bytes < kpms_ar_tc_tile_bytes(K, D, L) || !kpms_aligned(tiles, 256))
     return KPMS_ERR_UNSUPPORTED;
 #define KPMS_X(d, l) \
-  if (D == d && L == l) return launch_tc<d, l>(x, Wf, cst, N, T, K, ll, (unsigned char*)tiles, st);
+  if (D == d && L == l) return launch_tc<d, l>(x, Wf, cst, N, T, K, ll, (unsigned char*)tiles, tile_cl, tile_nch, st);
   KPMS_FOR_EACH_DL(KPMS_X)
 #undef KPMS_X
   return KPMS_ERR_UNSUPPORTED;

@@ -39,7 +39,7 @@ struct HmmWs {
   float* bnd;   // [N][nch][2][K]
   int* tv;
   float* Tbuf;    // a @ pi of the tensor-core forward pass (chunked mode only), tiled like alphan
-  float* rowmax;  // [N][Tm]
+  float* lltile;  // ll in the interleaved layout when the caller's is row-major
   // Message layout.  tiled == 0: alphan[n][t][j].  tiled == 1 (tensor-core forward pass): the
   // chunk chains u = n*nch + t/chunk_len are interleaved 128 at a time so that a CTA stepping 128
   // chains moves whole 512-byte lines:  float4 index (((u/128)*CL + t%CL) * K/4 + j/4) * 128 + u%128.
@@ -75,10 +75,10 @@ static size_t hmm_layout(int N, int Tm, int K, int chunk_len, void* base, HmmWs*
   p = take((size_t)N * sizeof(int)); if (ws) ws->tv = (int*)p;
   if (nch > 1 && K <= 128) {
     p = take(msg * sizeof(float)); if (ws) ws->Tbuf = (float*)p;
-    p = take((size_t)N * Tm * sizeof(float)); if (ws) ws->rowmax = (float*)p;
+    p = take(msg * sizeof(float)); if (ws) ws->lltile = (float*)p;
   } else if (ws) {
     ws->Tbuf = nullptr;
-    ws->rowmax = nullptr;
+    ws->lltile = nullptr;
   }
   if (ws) {
     ws->tiled = 0;
@@ -107,10 +107,11 @@ __global__ void hmm_tv_kernel(const float* __restrict__ mask, long long mask_str
   if (threadIdx.x == 0) tv[n] = cnt;
 }
 
-int kpms_hmm_forward_tc(const float* ll, const float* mask, long long mask_stride, const double* pi,
-                        const float* u, const int* tv, int N, int Tm, int K, int chunk_len, int burn_in,
-                        int nch, float* rowmax, float* a_out, float* T_out, unsigned* stay, double* llpart,
-                        float* bnd, unsigned* err_bits, cudaStream_t st);  // hmm_tc.cu
+bool kpms_hmm_tc_supported(int Tm, int K, int chunk_len);  // hmm_tc.cu
+int kpms_hmm_forward_tc(const float* ll, int ll_tiled, float* ll_scratch, const float* mask,
+                        long long mask_stride, const double* pi, const float* u, const int* tv, int N,
+                        int Tm, int K, int chunk_len, int burn_in, int nch, float* a_out, float* T_out,
+                        unsigned* stay, double* llpart, float* bnd, unsigned* err_bits, cudaStream_t st);
 
 // ------------------------------------------------------------------ kernel F: forward filter
 template <int KP>
@@ -479,7 +480,7 @@ __global__ void hmm_ffbs_generic_kernel(const float* __restrict__ ll, const floa
 }
 
 template <int KP>
-static int launch_reg(const float* ll, const float* mask, long long ms, const double* pi,
+static int launch_reg(const float* ll, int ll_tiled, const float* mask, long long ms, const double* pi,
                       const float* u, int N, int Tm, int K, int chunk_len, int burn_in, int* z,
                       double* loglik, float* boundary_err, HmmWs ws, cudaStream_t st) {
   const int nch = hmm_nchunks(Tm, chunk_len);
@@ -490,10 +491,10 @@ static int launch_reg(const float* ll, const float* mask, long long ms, const do
   }
   if (boundary_err) KPMS_CUDA(cudaMemsetAsync(boundary_err, 0, sizeof(float), st));
   int rc = KPMS_ERR_UNSUPPORTED;
-  const char* tcenv = getenv("KPMS_HMM_TC");  // "0" forces the CUDA-core forward kernel in chunked mode
-  if (nch > 1 && !(tcenv && tcenv[0] == '0'))
-    rc = kpms_hmm_forward_tc(ll, mask, ms, pi, u, ws.tv, N, Tm, K, chunk_len, burn_in, nch, ws.rowmax,
+  if (nch > 1)
+    rc = kpms_hmm_forward_tc(ll, ll_tiled, ws.lltile, mask, ms, pi, u, ws.tv, N, Tm, K, chunk_len, burn_in, nch,
                              ws.alphan, ws.Tbuf, ws.stay, ws.llpart, ws.bnd, (unsigned*)boundary_err, st);
+  if (rc == KPMS_ERR_UNSUPPORTED && ll_tiled) return KPMS_ERR_UNSUPPORTED;  // only the tensor-core pass reads tiles
   if (rc == KPMS_ERR_UNSUPPORTED) {
     hmm_forward_kernel<KP><<<N * nch, KP, 0, st>>>(ll, mask, ms, pi, u, Tm, K, chunk_len, burn_in, loglik, ws);
     rc = kpms_last_launch();
@@ -513,10 +514,12 @@ static int launch_reg(const float* ll, const float* mask, long long ms, const do
   return kpms_last_launch();
 }
 
-extern "C" int kpms_hmm_ffbs(const float* ll, const float* mask, int64_t mask_stride,
-                             const double* pi, const float* u, int N, int Tm, int K, int chunk_len,
-                             int burn_in, int32_t* z, double* loglik, float* boundary_err,
-                             void* workspace, size_t workspace_bytes, void* stream) {
+// ll_tiled != 0: ll is in the interleaved layout of HmmWs for this (chunk_len); only valid when
+// kpms_hmm_tc_supported(Tm, K, chunk_len).
+int kpms_hmm_ffbs_impl(const float* ll, int ll_tiled, const float* mask, int64_t mask_stride,
+                       const double* pi, const float* u, int N, int Tm, int K, int chunk_len,
+                       int burn_in, int32_t* z, double* loglik, float* boundary_err,
+                       void* workspace, size_t workspace_bytes, void* stream) {
   KPMS_REQUIRE(ll && mask && pi && u && z && workspace, KPMS_ERR_NULL);
   KPMS_REQUIRE(N > 0 && Tm > 0 && K > 0 && mask_stride >= Tm, KPMS_ERR_SHAPE);
   KPMS_REQUIRE(K <= 1024, KPMS_ERR_UNSUPPORTED);
@@ -527,7 +530,7 @@ extern "C" int kpms_hmm_ffbs(const float* ll, const float* mask, int64_t mask_st
   KPMS_REQUIRE(kpms_aligned(workspace, 256) && workspace_bytes >= need, KPMS_ERR_WORKSPACE);
   cudaStream_t st = (cudaStream_t)stream;
 #define KPMS_HMM_GO(KPV) \
-  return launch_reg<KPV>(ll, mask, mask_stride, pi, u, N, Tm, K, chunk_len, burn_in, z, loglik, boundary_err, ws, st)
+  return launch_reg<KPV>(ll, ll_tiled, mask, mask_stride, pi, u, N, Tm, K, chunk_len, burn_in, z, loglik, boundary_err, ws, st)
   if (K <= 32) KPMS_HMM_GO(32);
   if (K <= 64) KPMS_HMM_GO(64);
   if (K <= 96) KPMS_HMM_GO(96);
@@ -542,4 +545,12 @@ extern "C" int kpms_hmm_ffbs(const float* ll, const float* mask, int64_t mask_st
   hmm_ffbs_generic_kernel<<<N, threads, smem, st>>>(ll, mask, mask_stride, ws.pf, ws.pT, u, Tm, K, z,
                                                     loglik, ws.alphan);
   return kpms_last_launch();
+}
+
+extern "C" int kpms_hmm_ffbs(const float* ll, const float* mask, int64_t mask_stride,
+                             const double* pi, const float* u, int N, int Tm, int K, int chunk_len,
+                             int burn_in, int32_t* z, double* loglik, float* boundary_err,
+                             void* workspace, size_t workspace_bytes, void* stream) {
+  return kpms_hmm_ffbs_impl(ll, 0, mask, mask_stride, pi, u, N, Tm, K, chunk_len, burn_in, z, loglik,
+                            boundary_err, workspace, workspace_bytes, stream);
 }

@@ -17,6 +17,7 @@
 // needs ratios.  Masks must be trailing padding (merge_data, util.py:47-60); anything else is
 // flagged through boundary_err so that the caller falls back to the sequential kernel.
 #include "tc_common.cuh"
+#include <stdlib.h>
 
 struct HmmTcArgs {
   const float* ll;
@@ -180,22 +181,23 @@ __global__ void __launch_bounds__(HTC_THREADS, 1) hmm_forward_tc_kernel(HmmTcArg
   // ll of the current and of the next frame live in registers (this thread's column groups); the
   // frame after that is fetched while the tensor core works on the current one.
   float4 llc[HG::MAXG][2], lln[HG::MAXG][2];
+  // ll arrives in the interleaved layout (see HmmWs): float4 index ((b*CL + r)*K/4 + kc)*128 + row
+  // of the chain that OWNS frame t — during the warm-up that is the previous chunk of the session.
+  const float4* __restrict__ ll4 = reinterpret_cast<const float4*>(llp);
+  const int KC4f = K >> 2;
   auto fetch_ll = [&](int t, float4 (&dst)[HG::MAXG][2]) {
     const bool act = has && (t < tend);
-    const float* llr = llp + (rowbase + t) * K;
+    const int tt = act ? t : 0;
+    const int co = tt / p.chunk_len, ro = tt - co * p.chunk_len;
+    const int uo = n * nch + co;
+    const float4* src = ll4 + ((size_t)(uo >> 7) * p.chunk_len + ro) * KC4f * 128 + (uo & 127);
 #pragma unroll
     for (int i = 0; i < HG::MAXG; i++) {
-      const int c = 8 * (part + 4 * i);
-      if (act && c + 4 < K) {
-        ldg8(llr + c, true, 0.f, dst[i][0], dst[i][1]);
-      } else if (act && c < K) {
-        dst[i][0] = __ldg(reinterpret_cast<const float4*>(llr + c));
-        dst[i][1] = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
-      } else {
-        const float f = act ? -INFINITY : 0.0f;  // columns beyond K contribute exp(-inf) = 0
-        dst[i][0] = make_float4(f, f, f, f);
-        dst[i][1] = dst[i][0];
-      }
+      const int gi = part + 4 * i;
+      const int c = 8 * gi;
+      const float f = act ? -INFINITY : 0.0f;  // columns beyond K contribute exp(-inf) = 0
+      dst[i][0] = (act && c < K) ? __ldg(src + (size_t)(2 * gi) * 128) : make_float4(f, f, f, f);
+      dst[i][1] = (act && c + 4 < K) ? __ldg(src + (size_t)(2 * gi + 1) * 128) : make_float4(f, f, f, f);
     }
   };
   auto row_max = [&](const float4 (&v)[HG::MAXG][2]) {
@@ -505,21 +507,72 @@ static int launch_hmm_tc(const HmmTcArgs& a, cudaStream_t st) {
   return kpms_last_launch();
 }
 
-// Tensor-core forward filter + stay bits.  Returns KPMS_ERR_UNSUPPORTED when K has no instantiation.
-int kpms_hmm_forward_tc(const float* ll, const float* mask, long long mask_stride, const double* pi,
-                        const float* u, const int* tv, int N, int Tm, int K, int chunk_len, int burn_in,
-                        int nch, float* rowmax, float* a_out, float* T_out, unsigned* stay, double* llpart,
-                        float* bnd, unsigned* err_bits, cudaStream_t st) {
-  // rows are moved as float4; K = 128 would need 256 KB of operand tiles
-  if (K > 104 || (K & 3)) return KPMS_ERR_UNSUPPORTED;
-  (void)rowmax;
+// Row-major ll (N, Tm, K) -> interleaved tiles.  One CTA per tile (b, r): 128 chains x K values,
+// read as whole rows (coalesced), transposed through shared memory, written as whole lines.
+__global__ void __launch_bounds__(256) hmm_ll_tile_kernel(const float* __restrict__ ll, int N, int Tm, int K,
+                                                          int chunk_len, int nch, float* __restrict__ out) {
+  extern __shared__ float4 tl[];  // [K/4][129]
+  __shared__ long long src_row[128];
+  const int KC4 = K >> 2;
+  const long long blk = blockIdx.x;
+  const long long b = blk / chunk_len;
+  const int r = (int)(blk - b * chunk_len);
+  const long long units = (long long)N * nch;
+  if (threadIdx.x < 128) {
+    const long long u = b * 128 + threadIdx.x;
+    long long g = -1;
+    if (u < units) {
+      const int n = (int)(u / nch), cc = (int)(u % nch);
+      const int t = cc * chunk_len + r;
+      if (t < Tm) g = (long long)n * Tm + t;
+    }
+    src_row[threadIdx.x] = g;
+  }
+  __syncthreads();
+  const float4* ll4 = reinterpret_cast<const float4*>(ll);
+  for (int i = threadIdx.x; i < 128 * KC4; i += 256) {
+    const int row = i / KC4, kc = i - row * KC4;
+    const long long g = src_row[row];
+    tl[kc * 129 + row] = (g >= 0) ? __ldg(ll4 + (size_t)g * KC4 + kc) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  __syncthreads();
+  float4* dst = reinterpret_cast<float4*>(out) + (size_t)blk * KC4 * 128;
+  for (int i = threadIdx.x; i < 128 * KC4; i += 256) {
+    const int kc = i >> 7, row = i & 127;
+    dst[i] = tl[kc * 129 + row];
+  }
+}
+
+bool kpms_hmm_tc_supported(int Tm, int K, int chunk_len) {
+  const char* tcenv = getenv("KPMS_HMM_TC");  // "0" forces the CUDA-core forward kernel in chunked mode
+  if (tcenv && tcenv[0] == '0') return false;
+  return chunk_len > 0 && chunk_len < Tm && K <= 104 && (K & 3) == 0;
+}
+
+// Tensor-core forward filter + stay bits.  `ll_tiled` != 0: ll is already in the interleaved
+// layout; otherwise it is (N, Tm, K) row-major and is transposed into `ll_scratch` first.
+// Returns KPMS_ERR_UNSUPPORTED when K has no instantiation.
+int kpms_hmm_forward_tc(const float* ll, int ll_tiled, float* ll_scratch, const float* mask,
+                        long long mask_stride, const double* pi, const float* u, const int* tv, int N,
+                        int Tm, int K, int chunk_len, int burn_in, int nch, float* a_out, float* T_out,
+                        unsigned* stay, double* llpart, float* bnd, unsigned* err_bits, cudaStream_t st) {
+  if (!kpms_hmm_tc_supported(Tm, K, chunk_len)) return KPMS_ERR_UNSUPPORTED;
   int rc = 0;
   if (err_bits) {
     hmm_mask_check_kernel<<<N, 256, 0, st>>>(mask, mask_stride, Tm, tv, err_bits);
     rc = kpms_last_launch();
     if (rc) return rc;
   }
-  HmmTcArgs a{ll, rowmax, pi, u, tv, a_out, T_out, stay, llpart, bnd, N, Tm, K, chunk_len, burn_in, nch};
+  if (!ll_tiled) {
+    const long long tiles = (((long long)N * nch + 127) / 128) * chunk_len;
+    const size_t smem = (size_t)(K >> 2) * 129 * sizeof(float4);
+    KPMS_CUDA(cudaFuncSetAttribute(hmm_ll_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    hmm_ll_tile_kernel<<<(unsigned)tiles, 256, smem, st>>>(ll, N, Tm, K, chunk_len, nch, ll_scratch);
+    rc = kpms_last_launch();
+    if (rc) return rc;
+    ll = ll_scratch;
+  }
+  HmmTcArgs a{ll, nullptr, pi, u, tv, a_out, T_out, stay, llpart, bnd, N, Tm, K, chunk_len, burn_in, nch};
   if (K <= 32) return launch_hmm_tc<32, 32>(a, st);
   if (K <= 64) return launch_hmm_tc<64, 64>(a, st);
   return launch_hmm_tc<104, 112>(a, st);
