@@ -38,6 +38,8 @@ struct HmmWs {
   double* llpart;
   float* bnd;   // [N][nch][2][K]
   int* tv;
+  int* carry_warm;  // [N][nch] carry a backward chunk starts from (after its warm-up)
+  int* carry_out;   // [N][nch] carry a backward chunk leaves behind
   float* Tbuf;    // a @ pi of the tensor-core forward pass (chunked mode only), tiled like alphan
   float* lltile;  // ll in the interleaved layout when the caller's is row-major
   // Message layout.  tiled == 0: alphan[n][t][j].  tiled == 1 (tensor-core forward pass): the
@@ -73,6 +75,8 @@ static size_t hmm_layout(int N, int Tm, int K, int chunk_len, void* base, HmmWs*
   p = take((size_t)N * nch * sizeof(double)); if (ws) ws->llpart = (double*)p;
   p = take((size_t)N * nch * 2 * K * sizeof(float)); if (ws) ws->bnd = (float*)p;
   p = take((size_t)N * sizeof(int)); if (ws) ws->tv = (int*)p;
+  p = take((size_t)N * nch * sizeof(int)); if (ws) ws->carry_warm = (int*)p;
+  p = take((size_t)N * nch * sizeof(int)); if (ws) ws->carry_out = (int*)p;
   if (nch > 1 && K <= 128) {
     p = take(msg * sizeof(float)); if (ws) ws->Tbuf = (float*)p;
     p = take(msg * sizeof(float)); if (ws) ws->lltile = (float*)p;
@@ -285,34 +289,48 @@ __global__ void hmm_finish_kernel(HmmWs ws, int nch, int K, int chunk_len, doubl
 }
 
 // ------------------------------------------------------------------ kernel B: backward sampler
+// One warp per session chunk; the warps of a CTA share pi^T.  z_t depends on z_{t+1}, but two
+// backward chains driven by the SAME uniforms coalesce as soon as they pick the same state once,
+// which sticky transitions make a matter of a few frames.  A chunk [t0, t1) therefore starts
+// `burn_in` frames above t1 with an empty carry, discards those frames, and records the carry it
+// arrives with at t1; hmm_bcheck_kernel compares it with the carry the chunk above actually left
+// behind.  All boundaries equal  =>  the result is exactly the sequential one.
+#define HMM_BWARPS 8
 template <int KP>
-__global__ void __launch_bounds__(32)
+__global__ void __launch_bounds__(HMM_BWARPS * 32)
     hmm_backward_kernel(const float* __restrict__ mask, long long mask_stride,
-                        const double* __restrict__ pi, const float* __restrict__ u, int Tm, int K,
-                        int* __restrict__ z, HmmWs ws) {
-  const int n = blockIdx.x, lane = threadIdx.x;
+                        const double* __restrict__ pi, const float* __restrict__ u, int N, int Tm, int K,
+                        int chunk_len, int burn_in, int* __restrict__ z, HmmWs ws) {
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   extern __shared__ __align__(16) float piT[];  // [KP][KP]: piT[s*KP+i] = pi[i][s]
-  unsigned* bring = reinterpret_cast<unsigned*>(piT + KP * KP);   // [HMM_BRING][8] stay words, u, mask
+  unsigned* bring = reinterpret_cast<unsigned*>(piT + KP * KP) + (size_t)wib * (HMM_BRING * 8 + 32);
   float* lt = reinterpret_cast<float*>(bring + HMM_BRING * 8);    // [32] lane totals (slow path)
-  for (int idx = lane; idx < KP * KP; idx += 32) {
+  for (int idx = threadIdx.x; idx < KP * KP; idx += HMM_BWARPS * 32) {
     int s = idx / KP, i = idx % KP;
     piT[idx] = (s < K && i < K) ? (float)pi[(size_t)i * K + s] : 0.0f;
   }
+  __syncthreads();
+  const int nch = hmm_nchunks(Tm, chunk_len);
+  const long long unit = (long long)blockIdx.x * HMM_BWARPS + wib;
+  if (unit >= (long long)N * nch) return;
+  const int n = (int)(unit / nch), cc = (int)(unit % nch);
+  const int t0 = (nch == 1) ? 0 : cc * chunk_len;
+  const int t1 = (nch == 1) ? Tm : min(Tm, t0 + chunk_len);
+  const int ts = (cc == nch - 1) ? t1 - 1 : min(Tm, t1 + burn_in) - 1;  // first frame visited
   const float* al_n = ws.alphan + (size_t)n * Tm * K;
   const float* mk_n = mask + (size_t)n * mask_stride;
   const float* u_n = u + (size_t)n * Tm;
   int* z_n = z + (size_t)n * Tm;
   const unsigned* stay_n = ws.stay + (size_t)n * Tm * 4;
-  __syncwarp();
   // z_t ~ alphan_t * pi[:, z_{t+1}] by inverse CDF on u_t (distributions.py:62-72).  Lane l looks
   // at frame t-l: if that frame is masked (z = 0, carry unchanged) or its stay bit for the current
   // next state is set, the frame is settled; one ballot settles the longest such prefix, and only
   // the first unsettled frame pays for the full prefix sum over the K weights.
   constexpr int PER = KP / 32;  // states per lane in the slow path: lane*PER .. lane*PER+PER-1
   const unsigned bring_sa = (unsigned)__cvta_generic_to_shared(bring);
-  auto issue_b = [&](int f0, int cnt) {  // frames f0, f0-1, ..., f0-cnt+1 (those >= 0)
+  auto issue_b = [&](int f0, int cnt) {  // frames f0, f0-1, ..., f0-cnt+1 (those >= t0)
     const int f = f0 - lane;
-    if (lane < cnt && f >= 0) {
+    if (lane < cnt && f >= t0) {
       const unsigned dst = bring_sa + (unsigned)((f % HMM_BRING) * 32);
       asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(stay_n + (size_t)f * 4));
       asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(dst + 16), "l"(u_n + f));
@@ -321,33 +339,48 @@ __global__ void __launch_bounds__(32)
     asm volatile("cp.async.commit_group;\n" ::);
   };
 #pragma unroll 1
-  for (int b0 = 0; b0 < HMM_BRING / 32; b0++) issue_b(Tm - 1 - 32 * b0, 32);
+  for (int b0 = 0; b0 < HMM_BRING / 32; b0++) issue_b(ts - 32 * b0, 32);
   int s_next = -1;  // -1: next_potential = ones (distributions.py:76)
-  int t = Tm - 1;
+  if (lane == 0) ws.carry_warm[unit] = -1;  // the carry in use when there is no warm-up
+  int t = ts;
+  int lb = (ts >= t1) ? t1 : t0;  // warm-up phase first (frames >= t1, nothing written), then the chunk
 #pragma unroll 1
-  while (t >= 0) {
+  while (t >= t0) {
+    if (t < lb) {  // warm-up finished: remember the carry this chunk starts from
+      if (lane == 0) ws.carry_warm[unit] = s_next;
+      lb = t0;
+    }
     asm volatile("cp.async.wait_group 1;\n" ::);
     __syncwarp();
     const int f = t - lane;
-    const bool valid = f >= 0;
+    const bool valid = f >= lb;
+    const bool keep = lb == t0;  // frames of the chunk proper are written
     const unsigned* e = bring + (valid ? (f % HMM_BRING) : 0) * 8;
     const bool masked = valid && !(__uint_as_float(e[5]) > 0.0f);
     const bool stayb = valid && s_next >= 0 && ((e[s_next >> 5] >> (s_next & 31)) & 1u);
     const unsigned bal = __ballot_sync(0xffffffffu, masked || stayb);
     const int r = (bal == 0xffffffffu) ? 32 : (__ffs(~bal) - 1);  // settled frames t, t-1, ..., t-r+1
-    if (lane < r) z_n[f] = masked ? 0 : s_next;
+    if (keep && lane < r) z_n[f] = masked ? 0 : s_next;
     int consumed = r;
     const int fb = t - r;  // first unsettled frame (unmasked by construction) if it exists
-    if (r < 32 && fb >= 0) {
+    if (r < 32 && fb >= lb) {
       const float ub = __uint_as_float(bring[(fb % HMM_BRING) * 8 + 4]);
       const size_t mb4 = ws.tiled ? hmm_msg_base4(ws, n, fb, Tm, K) : 0;
       float w[PER];
       float run = 0.0f;
+      float al4[4] = {0.f, 0.f, 0.f, 0.f};
+      if (PER == 4 && ws.tiled) {  // the lane's four states are one 16-byte piece of the tile
+        if (lane * 4 < K) {
+          const float4 v = __ldg(reinterpret_cast<const float4*>(ws.alphan) + mb4 + (size_t)lane * 128);
+          al4[0] = v.x; al4[1] = v.y; al4[2] = v.z; al4[3] = v.w;
+        }
+      }
 #pragma unroll
       for (int q = 0; q < PER; q++) {
         const int st = lane * PER + q;
         float al = 0.0f;
-        if (st < K) {
+        if (PER == 4 && ws.tiled) al = al4[q & 3];
+        else if (st < K) {
           if (ws.tiled) al = ws.alphan[(mb4 + (size_t)(st >> 2) * 128) * 4 + (st & 3)];
           else al = al_n[(size_t)fb * K + st];
         }
@@ -373,7 +406,7 @@ __global__ void __launch_bounds__(32)
 #pragma unroll
       for (int q = 0; q < PER; q++) cnt += __popc(__ballot_sync(0xffffffffu, !(excl + w[q] > thr)));
       const int zt = min(cnt, K - 1);
-      if (lane == 0) z_n[fb] = zt;
+      if (keep && lane == 0) z_n[fb] = zt;
       s_next = zt;
       consumed = r + 1;
     }
@@ -382,6 +415,18 @@ __global__ void __launch_bounds__(32)
     t -= consumed;
   }
   asm volatile("cp.async.wait_group 0;\n" ::);
+  if (lane == 0) {
+    ws.carry_out[unit] = s_next;
+  }
+}
+
+// chunk cc must have started from the carry that chunk cc + 1 left behind
+__global__ void hmm_bcheck_kernel(HmmWs ws, int N, int nch, unsigned* __restrict__ err_bits) {
+  const long long unit = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (unit >= (long long)N * nch) return;
+  const int cc = (int)(unit % nch);
+  if (cc == nch - 1) return;
+  if (ws.carry_warm[unit] != ws.carry_out[unit + 1]) atomicMax(err_bits, __float_as_uint(2.0f));
 }
 
 // Generic kernel for K > 128 (K <= 1024): thread j owns state j, pi / pi^T in fp32 in global
@@ -508,9 +553,14 @@ static int launch_reg(const float* ll, int ll_tiled, const float* mask, long lon
   const char* env = getenv("KPMS_HMM_FLAGS");  // debugging: bit 0 = forward pass only
   if (env && (atoi(env) & 1)) return KPMS_OK;
   auto kern = hmm_backward_kernel<KP>;
-  const size_t smem = (size_t)(KP * KP + HMM_BRING * 8 + 32) * sizeof(float);
+  const size_t smem = (size_t)(KP * KP + HMM_BWARPS * (HMM_BRING * 8 + 32)) * sizeof(float);
   KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<N, 32, smem, st>>>(mask, ms, pi, u, Tm, K, z, ws);
+  const long long units = (long long)N * nch;
+  kern<<<(unsigned)((units + HMM_BWARPS - 1) / HMM_BWARPS), HMM_BWARPS * 32, smem, st>>>(
+      mask, ms, pi, u, N, Tm, K, chunk_len, burn_in, z, ws);
+  rc = kpms_last_launch();
+  if (rc || nch == 1 || !boundary_err) return rc;
+  hmm_bcheck_kernel<<<(unsigned)((units + 255) / 256), 256, 0, st>>>(ws, N, nch, (unsigned*)boundary_err);
   return kpms_last_launch();
 }
 
