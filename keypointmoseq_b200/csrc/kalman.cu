@@ -699,15 +699,20 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 3)
     double Lc[NN];
 #pragma unroll
     for (int i = 0; i < NN; i++) {
-      double a0 = (i == c) ? 1.0 : 0.0, a1 = 0.0;
+      double a0 = (i == c) ? 1.0 : 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
 #pragma unroll
       for (int q = 0; q + 1 < i; q += 2) {
         const double2 mm = *reinterpret_cast<const double2*>(Ms + Wt::moff(i) + q);
-        a0 = fma(-mm.x, Lc[q], a0);
-        a1 = fma(-mm.y, Lc[q + 1], a1);
+        if (q & 2) {
+          a2 = fma(-mm.x, Lc[q], a2);
+          a3 = fma(-mm.y, Lc[q + 1], a3);
+        } else {
+          a0 = fma(-mm.x, Lc[q], a0);
+          a1 = fma(-mm.y, Lc[q + 1], a1);
+        }
       }
       if (i & 1) a0 = fma(-Ms[Wt::moff(i) + i - 1], Lc[i - 1], a0);
-      Lc[i] = (a0 + a1) * dv[i];
+      Lc[i] = ((a0 + a1) + (a2 + a3)) * dv[i];
     }
     // rows of L to shared memory, eta_c - f for the mean column, L and eta_c to the workspace
 #pragma unroll
@@ -733,6 +738,9 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 3)
       constexpr int RB = (NN + 7) / 8;       // 8-row blocks of T
       constexpr int CB0 = OFF / 8;           // first column block that holds a dense column
       const int g = lane >> 2, qd = lane & 3;
+      // Column c < OFF of T is 100 x row DD + c of L, so block b < CB0 of T is zero below row
+      // DD + 8 b + 7: its last contributing 4-row chunk.
+      auto tkmax = [](int b) constexpr { return (b < CB0) ? ((DD + 8 * b + 7) / 4 < KQ - 1 ? (DD + 8 * b + 7) / 4 : KQ - 1) : KQ - 1; };
       // dense column blocks of T by DMMA: T[:, 8cb..8cb+7] = L^T F[:, 8cb..]
       double Tacc[RB][NB - CB0][2];
 #pragma unroll
@@ -755,6 +763,7 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 3)
         }
 #pragma unroll
         for (int rb = 0; rb < RB; rb++) {
+          if (kq < 2 * rb) continue;  // L is lower triangular: L[q][r] = 0 for q < r (8 rb <= r)
           const double av = Ls[q * RS + 8 * rb + g];   // L[q][r]: rows >= NN and columns >= NN are zero
 #pragma unroll
           for (int cb = 0; cb < NB - CB0; cb++)
@@ -780,7 +789,7 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 3)
 #pragma unroll
         for (int b = 0; b < NB; b++) {
           const int cf = 8 * b + g;
-          if (b < CB0) Tk[kq][b] = 100.0 * Ls[(DD + cf) * RS + r];
+          if (b < CB0) Tk[kq][b] = (kq <= tkmax(b)) ? 100.0 * Ls[(DD + cf) * RS + r] : 0.0;
           else Tk[kq][b] = Ms[r * Wt::TS + (cf - 8 * CB0)];
         }
       }
@@ -794,10 +803,12 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 3)
 #pragma unroll
         for (int ib = 0; ib < NB; ib++)
 #pragma unroll
-          for (int jb = 0; jb <= ib; jb++)
+          for (int jb = 0; jb <= ib; jb++) {
+            if (kq > tkmax(jb) || kq > tkmax(ib)) continue;  // structural zeros of the unit-column blocks
             asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
                          : "+d"(Zacc[ib * (ib + 1) / 2 + jb][0]), "+d"(Zacc[ib * (ib + 1) / 2 + jb][1])
                          : "d"(Tk[kq][ib]), "d"(Tk[kq][jb]));
+          }
       }
 #pragma unroll
       for (int ib = 0; ib < NB; ib++)
