@@ -579,6 +579,16 @@ __global__ void __launch_bounds__(KAL_NT, 1)
 // ~4.2 k warp instructions per step, of which ~2.1 k are DFMA; eight such warps per SM.
 #define KW_WARPS 4
 
+// 1/sqrt(x) for the pivots of an SPD matrix (x > 0, normal): hardware seed (2^-22) and one
+// third-order correction, without rsqrt()'s special-case handling.
+__device__ __forceinline__ double rsqrt_pos(double x) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  const double e = fma(-x, y * y, 1.0);
+  const double p = fma(0.375, e, 0.5);
+  return fma(y * e, p, y);
+}
+
 template <int NN, int DD>
 __global__ void __launch_bounds__(KW_WARPS * 32, 3)
     kalman_forward_warp_kernel(const float* __restrict__ mask, const int* __restrict__ z,
@@ -676,7 +686,7 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 3)
     double piv = __shfl_sync(FULL, Wc[NN - 1], NN - 1);
 #pragma unroll
     for (int k = NN - 1; k >= 0; k--) {
-      const double rs = rsqrt(piv);
+      const double rs = rsqrt_pos(piv);
       const double m = Wc[k] * rs;
       if (k > 0) {
         // next pivot W[k-1][k-1] - M[k][k-1]^2 is known to lane k-1 from its own registers:
@@ -857,7 +867,7 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 3)
 #pragma unroll
     for (int k = NN - 1; k >= 0; k--) {
       const double piv = __shfl_sync(FULL, Wc[k], k);
-      const double rs = rsqrt(piv);
+      const double rs = rsqrt_pos(piv);
       const double m = Wc[k] * rs;
       if (c <= k) Ls[k * RS + c] = m;
       if (c == 0) dv[k] = rs;

@@ -60,7 +60,7 @@ __device__ __forceinline__ void ytild_kp(const float* __restrict__ Yf, const dou
 }
 
 // ======================================================================== a13
-#define OV_BLOCKS (148 * 2)
+#define OV_BLOCKS (148 * 4)
 #define OV_THREADS 256
 
 extern "C" size_t kpms_obs_variance_stats_workspace_bytes(int N, int T, int k) {
@@ -79,9 +79,10 @@ __global__ void __launch_bounds__(OV_THREADS)
   const int k = dm.k, dk = dm.dk, D = dm.D;
   load_cd(Cdfull, k * dk, D, Cs);
   __syncthreads();
-  double acc[OBS_KPMAX + 1];
-#pragma unroll
-  for (int i = 0; i <= OBS_KPMAX; i++) acc[i] = 0.0;
+  // per-thread accumulators live in shared memory ([entry][thread], conflict-free): keeping 33
+  // doubles in registers across the unrolled keypoint loop costs 255 registers and occupancy
+  double* accs = Cs + (size_t)k * dk * (D + 1);
+  for (int i = 0; i <= k; i++) accs[i * OV_THREADS + threadIdx.x] = 0.0;
   const long long frames = (long long)dm.N * dm.T;
   for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < frames;
        g += (long long)gridDim.x * blockDim.x) {
@@ -94,37 +95,32 @@ __global__ void __launch_bounds__(OV_THREADS)
       double vv[OBS_DKMAX];
 #pragma unroll
       for (int dim = 0; dim < OBS_DKMAX; dim++) vv[dim] = (dim < dk) ? (double)v[g * dk + dim] : 0.0;
+#pragma unroll 2
+      for (int kp = 0; kp < k; kp++) {
+        double yb[OBS_DKMAX], yt[OBS_DKMAX];
+        ybar_kp(Cs, kp, dk, D, xr, yb);
+        ytild_kp(Y + ((size_t)g * k + kp) * dk, vv, cs, sn, dk, yt);
+        double e = 0.0;
 #pragma unroll
-      for (int kp = 0; kp < OBS_KPMAX; kp++) {
-        if (kp < k) {
-          double yb[OBS_DKMAX], yt[OBS_DKMAX];
-          ybar_kp(Cs, kp, dk, D, xr, yb);
-          ytild_kp(Y + ((size_t)g * k + kp) * dk, vv, cs, sn, dk, yt);
-          double e = 0.0;
-#pragma unroll
-          for (int dim = 0; dim < OBS_DKMAX; dim++) {
-            const double r = yt[dim] - yb[dim];
-            e = fma(r, r, e);
-          }
-          acc[kp] += m * e / (double)s[(size_t)g * k + kp];
+        for (int dim = 0; dim < OBS_DKMAX; dim++) {
+          const double r = yt[dim] - yb[dim];
+          e = fma(r, r, e);
         }
+        accs[kp * OV_THREADS + threadIdx.x] += m * e / (double)s[(size_t)g * k + kp];
       }
-      acc[OBS_KPMAX] += m;
+      accs[k * OV_THREADS + threadIdx.x] += m;
     }
   }
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-  for (int i = 0; i <= OBS_KPMAX; i++) {
-    if (i < k || i == OBS_KPMAX) {
-      double w = warp_sum_d(acc[i]);
-      __syncthreads();
-      if (lane == 0) red[warp] = w;
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        double t = 0.0;
-        for (int q = 0; q < OV_THREADS / 32; q++) t += red[q];
-        partial[(size_t)blockIdx.x * (OBS_KPMAX + 1) + i] = t;
-      }
+  for (int i = 0; i <= k; i++) {
+    double w = warp_sum_d(accs[i * OV_THREADS + threadIdx.x]);
+    __syncthreads();
+    if (lane == 0) red[warp] = w;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double t = 0.0;
+      for (int q = 0; q < OV_THREADS / 32; q++) t += red[q];
+      partial[(size_t)blockIdx.x * (OBS_KPMAX + 1) + (i < k ? i : OBS_KPMAX)] = t;
     }
   }
 }
@@ -157,7 +153,8 @@ extern "C" int kpms_obs_variance_stats(const float* Y, const float* mask, const 
                KPMS_ERR_WORKSPACE);
   cudaStream_t st = (cudaStream_t)stream;
   ObsDims dm{N, T, k, dk, D};
-  const size_t smem = (size_t)k * dk * (D + 1) * sizeof(double);
+  const size_t smem = ((size_t)k * dk * (D + 1) + (size_t)(k + 1) * OV_THREADS) * sizeof(double);
+  KPMS_CUDA(cudaFuncSetAttribute(obs_variance_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   obs_variance_kernel<<<OV_BLOCKS, OV_THREADS, smem, st>>>(Y, mask, v, h, x, s, Cdfull, dm,
                                                           (double*)workspace);
   rc = kpms_last_launch();
