@@ -290,8 +290,15 @@ def main():
         peak, peak_src = float(mp["hbm_gbs"]), "measured"
     except Exception:
         pass
+    traffic = None
+    try:   # measured DRAM bytes of the entry point's kernels (one ncu --set full capture of this workload)
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r01_latents_traffic.json")))
+        if int(tj["frames"]) == N * T:
+            traffic = float(tj["total"])
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel": "kpms_resample_latents (kalman_forward + kalman_backward)",
+                "traffic": traffic, "algorithmic_bytes_per_launch": N * T * bytes_per_frame, "kernel": "kpms_resample_latents (kalman_forward + kalman_backward)",
                 "algorithmic_bytes_per_frame": bytes_per_frame, "ms_per_launch": lat_ms, "peak_source": peak_src}
 
     # ---- end-to-end arm: host buffers in, host buffers out, every step
@@ -348,6 +355,7 @@ def main():
                                                 if G.LATENTS_CHUNKING["chunk_len"] == "auto" else G.LATENTS_CHUNKING["chunk_len"]),
                            "kalman_burn_in": G.LATENTS_CHUNKING["burn_in"],
                            "kalman_boundary_err": boundary_err,
+                           "chunk_fallbacks": dict(G.FALLBACKS),
                            "l2": "per-step working set (>= 20 GB of filter workspace + ll/alphan) far exceeds the 126 MB L2"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline,
                 "cpu_baseline": cpu, "breakdown_ms": bd}

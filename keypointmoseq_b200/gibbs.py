@@ -33,6 +33,8 @@ last_latents_boundary_err = None
 STATESEQ_CHUNKING = {"chunk_len": "auto", "burn_in": 256, "strict": True, "tol": 1e-5}
 HMM_CTAS_PER_SM = 3
 last_stateseq_boundary_err = None
+# how often a chunked pass failed its boundary check and was redone exactly (diagnostics)
+FALLBACKS = {"stateseqs": 0, "latents": 0}
 
 
 def auto_hmm_chunk_len(N, Tm, K, burn_in, device):
@@ -111,15 +113,25 @@ def sample_hmm_stateseqs(*, ll, mask, pi, u, chunk_len=None, burn_in=None, stric
     loglik = torch.empty((N,), dtype=torch.float64, device=dev)
     berr = torch.zeros((1,), dtype=torch.float32, device=dev)
 
-    def run(cl):
+    def run(cl, bi):
         ws = _lib.WORKSPACE.get("hmm", lib.kpms_hmm_ffbs_workspace_bytes(N, Tm, K, cl), dev)
         _lib.check(lib.kpms_hmm_ffbs(_lib.ptr(ll), _lib.ptr(mask), Tm, _lib.ptr(pi), _lib.ptr(u), N, Tm, K, cl,
-                                     burn_in, _lib.ptr(z), _lib.ptr(loglik), _lib.ptr(berr), _lib.ptr(ws),
+                                     bi, _lib.ptr(z), _lib.ptr(loglik), _lib.ptr(berr), _lib.ptr(ws),
                                      ws.numel(), _lib.stream_ptr(dev)), "kpms_hmm_ffbs")
 
-    run(chunk_len)
+    run(chunk_len, burn_in)
     if chunk_len > 0 and strict and float(berr) > STATESEQ_CHUNKING["tol"]:
-        run(0)
+        # warm-up too short for this model: once more with four times the warm-up, then exactly
+        FALLBACKS["stateseqs"] += 1
+        burn2 = 4 * max(burn_in, 64)
+        cl2 = auto_hmm_chunk_len(N, Tm, K, burn2, dev)
+        ok = False
+        if cl2 > 0 and float(berr) < 1e29:    # 1e30 flags a mask that is not trailing padding
+            run(cl2, burn2)
+            ok = float(berr) <= STATESEQ_CHUNKING["tol"]
+        if not ok:
+            FALLBACKS["stateseqs_exact"] = FALLBACKS.get("stateseqs_exact", 0) + 1
+            run(0, 0)
     last_stateseq_boundary_err = berr
     if return_info:
         return z, loglik, {"boundary_err": berr}
@@ -145,16 +157,28 @@ def resample_stateseqs(key, *, x, mask, Ab, Q, pi, draws=None, impl=0, chunk_len
     loglik = torch.empty((N,), dtype=torch.float64, device=dev)
     berr = torch.zeros((1,), dtype=torch.float32, device=dev)
 
-    def run(cl):
+    Tm = T - L
+
+    def run(cl, bi):
         ws = _lib.WORKSPACE.get("stateseqs", lib.kpms_resample_stateseqs_workspace_bytes(N, T, D, L, K, cl), dev)
         _lib.check(lib.kpms_resample_stateseqs(
             _lib.ptr(x), _lib.ptr(mask), _lib.ptr(Ab), _lib.ptr(Q), _lib.ptr(pi), _lib.ptr(u), N, T, D, L, K,
-            cl, burn_in, _lib.ptr(z), _lib.ptr(loglik), _lib.ptr(berr), _lib.ptr(ws), ws.numel(), int(impl),
+            cl, bi, _lib.ptr(z), _lib.ptr(loglik), _lib.ptr(berr), _lib.ptr(ws), ws.numel(), int(impl),
             _lib.stream_ptr(dev)), "kpms_resample_stateseqs")
 
-    run(chunk_len)
+    run(chunk_len, burn_in)
     if chunk_len > 0 and strict and float(berr) > STATESEQ_CHUNKING["tol"]:
-        run(0)
+        # warm-up too short for this model: once more with four times the warm-up, then exactly
+        FALLBACKS["stateseqs"] += 1
+        burn2 = 4 * max(burn_in, 64)
+        cl2 = auto_hmm_chunk_len(N, Tm, K, burn2, dev)
+        ok = False
+        if cl2 > 0 and float(berr) < 1e29:    # 1e30 flags a mask that is not trailing padding
+            run(cl2, burn2)
+            ok = float(berr) <= STATESEQ_CHUNKING["tol"]
+        if not ok:
+            FALLBACKS["stateseqs_exact"] = FALLBACKS.get("stateseqs_exact", 0) + 1
+            run(0, 0)
     last_stateseq_boundary_err = berr
     return z, loglik
 
@@ -190,18 +214,29 @@ def resample_latents(key, *, Y, mask, v, h, z, s, Cd, sigmasq, Ab, Q, Gamma=None
     loglik = torch.empty((N,), dtype=torch.float64, device=dev) if return_info else None
     berr = torch.zeros((2,), dtype=torch.float64, device=dev)
 
-    def run(cl):
+    def run(cl, bi):
         nbytes = lib.kpms_resample_latents_workspace_bytes(N, T, k, dk, D, L, K, int(cl))
         ws = _lib.WORKSPACE.get("latents", nbytes, dev)
         _lib.check(lib.kpms_resample_latents(
             _lib.ptr(Y), _lib.ptr(mask), _lib.ptr(v), _lib.ptr(h), _lib.ptr(z), _lib.ptr(s), _lib.ptr(Cdfull),
             _lib.ptr(sigmasq), _lib.ptr(Ab), _lib.ptr(Q), _lib.ptr(w), _lib.ptr(w_last), N, T, k, dk, D, L, K,
-            int(cl), int(burn_in), _lib.ptr(x), _lib.ptr(loglik), _lib.ptr(berr), _lib.ptr(ws),
+            int(cl), int(bi), _lib.ptr(x), _lib.ptr(loglik), _lib.ptr(berr), _lib.ptr(ws),
             ws.numel(), _lib.stream_ptr(dev)), "kpms_resample_latents")
 
-    run(chunk_len)
+    run(chunk_len, burn_in)
     if chunk_len > 0 and strict and float(berr.max()) > LATENTS_CHUNKING["tol"]:
-        run(0)   # warm-up too short for this model: redo exactly (one warp per session)
+        # warm-up too short for this model: once more with four times the warm-up, then exactly
+        # (one warp per session)
+        FALLBACKS["latents"] += 1
+        burn2 = 4 * max(int(burn_in), 64)
+        cl2 = auto_chunk_len(N, T, L, burn2, dev)
+        ok = False
+        if cl2 > 0:
+            run(cl2, burn2)
+            ok = float(berr.max()) <= LATENTS_CHUNKING["tol"]
+        if not ok:
+            FALLBACKS["latents_exact"] = FALLBACKS.get("latents_exact", 0) + 1
+            run(0, 0)
     last_latents_boundary_err = berr
     if return_info:
         return x, {"loglik": loglik, "boundary_err": berr}

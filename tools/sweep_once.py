@@ -18,6 +18,12 @@ hyp = {}
 for h in default_hypparams(D, L, K):
     hyp.update({a: (tt(b) if isinstance(b, np.ndarray) else b) for a, b in h.items()})
 for i in range(reps):
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
     s, p = parallel.gibbs_sweep((0, i), d, s, p, hyp, Gamma=tt(Gamma))
+    b.record()
+    torch.cuda.synchronize()
+    print(i, "ms", round(a.elapsed_time(b), 2), "hmm berr", float(G.last_stateseq_boundary_err), "kalman berr",
+          G.last_latents_boundary_err.tolist(), dict(G.FALLBACKS), flush=True)
 torch.cuda.synchronize()
 print("ok", float(s['x'].abs().mean()))
