@@ -27,10 +27,14 @@ THIN_CAP = 16384             # max tables per state handled by the sticky thinni
 LATENTS_CHUNKING = {"chunk_len": "auto", "burn_in": 256, "strict": True, "tol": 1e-10}
 KALMAN_WARPS_PER_SM = 12
 last_latents_boundary_err = None
-# HMM forward-filter chunking (K <= 128): same idea; the filter forgets its start geometrically.
-# "auto" cuts sessions so that about three CTAs per SM are busy; mismatch above `tol` (absolute,
-# on potentials that sum to one) triggers an exact re-run when strict.
-STATESEQ_CHUNKING = {"chunk_len": "auto", "burn_in": 256, "strict": True, "tol": 1e-5}
+# HMM chunking (K <= 128): same idea for the forward filter and the backward sampler.  The library
+# reports the largest absolute mismatch of the normalised messages at chunk boundaries (2.0 if a
+# sampler chunk started from the wrong state, 1e30 for a mask that is not trailing padding).
+# `tol`: a mismatch eps perturbs only the first frames of a chunk, so the marginal log-likelihood
+# moves by about n_chunks * eps (3e-4 -> < 1e-6 relative on the bench shard) and the sampled
+# states by far less than the 0.1 % the contract allows (measured: 1e-4 mismatch changes neither,
+# tools/hmm_model_data.py); above it strict mode retries with a longer warm-up, then exactly.
+STATESEQ_CHUNKING = {"chunk_len": "auto", "burn_in": 256, "strict": True, "tol": 3e-4}
 HMM_CTAS_PER_SM = 3
 last_stateseq_boundary_err = None
 # how often a chunked pass failed its boundary check and was redone exactly (diagnostics)

@@ -13,7 +13,7 @@ Ab, Q, pi = tt(pr['Ab']), tt(pr['Q']), tt(pr['pi'])
 ll = G.ar_log_likelihood(x=x, Ab=Ab, Q=Q)
 u = torch.rand((N, T - 3), device="cuda")
 z0, lg0 = G.sample_hmm_stateseqs(ll=ll, mask=mask[:, 3:], pi=pi, u=u, chunk_len=0)
-modes = [(0, 0), ("auto", 256), ("auto", 128), (512, 256), (1024, 256), (2048, 256), (1024, 512), (4000, 256), (12000, 1024)]
+modes = [(0, 0), ("auto", 256), (258, 96), (258, 64), (258, 48), (258, 32), (258, 16)]
 for cl, bi in modes:
     z, lg, info = G.sample_hmm_stateseqs(ll=ll, mask=mask[:, 3:], pi=pi, u=u, chunk_len=cl, burn_in=bi, strict=False, return_info=True)
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

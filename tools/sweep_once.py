@@ -8,7 +8,9 @@ N = int(sys.argv[1]) if len(sys.argv) > 1 else 125
 T = int(sys.argv[2]) if len(sys.argv) > 2 else 36000
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 1
 k, dk, D, L, K = 16, 2, 10, 3, 100
-data, st, pr, Gamma = simulate(5, N, T, k=k, dk=dk, D=D, L=L, K=K)
+data, st, pr, Gamma = simulate(1000, N, T, k=k, dk=dk, D=D, L=L, K=K)
+if os.environ.get('BENCH_PARAMS', '1') == '1':   # bench.py: parameters drawn independently of the data
+    pr = simulate(999, 1, 8, k=k, dk=dk, D=D, L=L, K=K)[2]
 dev = torch.device("cuda")
 tt = lambda a: torch.as_tensor(a, device=dev)
 d = {a: tt(b) for a, b in data.items()}
