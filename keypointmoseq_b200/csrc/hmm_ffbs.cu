@@ -293,35 +293,22 @@ __global__ void hmm_finish_kernel(HmmWs ws, int nch, int K, int chunk_len, doubl
 // backward chains driven by the SAME uniforms coalesce as soon as they pick the same state once,
 // which sticky transitions make a matter of a few frames.  A chunk [t0, t1) therefore starts
 // `burn_in` frames above t1 with an empty carry, discards those frames, and records the carry it
-// arrives with at t1; hmm_bcheck_kernel compares it with the carry the chunk above actually left
-// behind.  All boundaries equal  =>  the result is exactly the sequential one.
+// arrives with at t1.  hmm_brepair_kernel then walks every session's chunks from the top and
+// redoes, from the true carry, the few chunks whose warm-up had not coalesced: the result is
+// exactly the sequential sampler's for the given messages.
 #define HMM_BWARPS 8
+
+// Walk frames ts, ts-1, ..., t0 of session n.  Frames >= t1 are a warm-up (nothing written);
+// `s_next` is the carry to start from (-1: next_potential = ones, distributions.py:76).
+// Returns the carry after frame t0; *carry_at_t1 receives the carry in use below t1.
 template <int KP>
-__global__ void __launch_bounds__(HMM_BWARPS * 32)
-    hmm_backward_kernel(const float* __restrict__ mask, long long mask_stride,
-                        const double* __restrict__ pi, const float* __restrict__ u, int N, int Tm, int K,
-                        int chunk_len, int burn_in, int* __restrict__ z, HmmWs ws) {
-  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-  extern __shared__ __align__(16) float piT[];  // [KP][KP]: piT[s*KP+i] = pi[i][s]
-  unsigned* bring = reinterpret_cast<unsigned*>(piT + KP * KP) + (size_t)wib * (HMM_BRING * 8 + 32);
-  float* lt = reinterpret_cast<float*>(bring + HMM_BRING * 8);    // [32] lane totals (slow path)
-  for (int idx = threadIdx.x; idx < KP * KP; idx += HMM_BWARPS * 32) {
-    int s = idx / KP, i = idx % KP;
-    piT[idx] = (s < K && i < K) ? (float)pi[(size_t)i * K + s] : 0.0f;
-  }
-  __syncthreads();
-  const int nch = hmm_nchunks(Tm, chunk_len);
-  const long long unit = (long long)blockIdx.x * HMM_BWARPS + wib;
-  if (unit >= (long long)N * nch) return;
-  const int n = (int)(unit / nch), cc = (int)(unit % nch);
-  const int t0 = (nch == 1) ? 0 : cc * chunk_len;
-  const int t1 = (nch == 1) ? Tm : min(Tm, t0 + chunk_len);
-  const int ts = (cc == nch - 1) ? t1 - 1 : min(Tm, t1 + burn_in) - 1;  // first frame visited
+__device__ __forceinline__ int hmm_backward_walk(const float* __restrict__ mk_n, const float* __restrict__ u_n,
+                                                 const unsigned* __restrict__ stay_n, int* __restrict__ z_n,
+                                                 const HmmWs& ws, const float* piT, unsigned* bring, float* lt,
+                                                 int n, int Tm, int K, int t0, int t1, int ts, int s_next,
+                                                 int* carry_at_t1) {
+  const int lane = threadIdx.x & 31;
   const float* al_n = ws.alphan + (size_t)n * Tm * K;
-  const float* mk_n = mask + (size_t)n * mask_stride;
-  const float* u_n = u + (size_t)n * Tm;
-  int* z_n = z + (size_t)n * Tm;
-  const unsigned* stay_n = ws.stay + (size_t)n * Tm * 4;
   // z_t ~ alphan_t * pi[:, z_{t+1}] by inverse CDF on u_t (distributions.py:62-72).  Lane l looks
   // at frame t-l: if that frame is masked (z = 0, carry unchanged) or its stay bit for the current
   // next state is set, the frame is settled; one ballot settles the longest such prefix, and only
@@ -340,14 +327,13 @@ __global__ void __launch_bounds__(HMM_BWARPS * 32)
   };
 #pragma unroll 1
   for (int b0 = 0; b0 < HMM_BRING / 32; b0++) issue_b(ts - 32 * b0, 32);
-  int s_next = -1;  // -1: next_potential = ones (distributions.py:76)
-  if (lane == 0) ws.carry_warm[unit] = -1;  // the carry in use when there is no warm-up
+  int carry1 = s_next;  // the carry in use when there is no warm-up
   int t = ts;
   int lb = (ts >= t1) ? t1 : t0;  // warm-up phase first (frames >= t1, nothing written), then the chunk
 #pragma unroll 1
   while (t >= t0) {
     if (t < lb) {  // warm-up finished: remember the carry this chunk starts from
-      if (lane == 0) ws.carry_warm[unit] = s_next;
+      carry1 = s_next;
       lb = t0;
     }
     asm volatile("cp.async.wait_group 1;\n" ::);
@@ -415,18 +401,86 @@ __global__ void __launch_bounds__(HMM_BWARPS * 32)
     t -= consumed;
   }
   asm volatile("cp.async.wait_group 0;\n" ::);
+  __syncwarp();
+  *carry_at_t1 = carry1;
+  return s_next;
+}
+
+template <int KP>
+__device__ __forceinline__ void hmm_load_piT(const double* __restrict__ pi, int K, float* piT) {
+  for (int idx = threadIdx.x; idx < KP * KP; idx += blockDim.x) {
+    int s = idx / KP, i = idx % KP;
+    piT[idx] = (s < K && i < K) ? (float)pi[(size_t)i * K + s] : 0.0f;  // piT[s*KP+i] = pi[i][s]
+  }
+  __syncthreads();
+}
+
+template <int KP>
+__global__ void __launch_bounds__(HMM_BWARPS * 32)
+    hmm_backward_kernel(const float* __restrict__ mask, long long mask_stride,
+                        const double* __restrict__ pi, const float* __restrict__ u, int N, int Tm, int K,
+                        int chunk_len, int burn_in, int* __restrict__ z, HmmWs ws) {
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  extern __shared__ __align__(16) float piT[];  // [KP][KP]
+  unsigned* bring = reinterpret_cast<unsigned*>(piT + KP * KP) + (size_t)wib * (HMM_BRING * 8 + 32);
+  float* lt = reinterpret_cast<float*>(bring + HMM_BRING * 8);    // [32] lane totals (slow path)
+  hmm_load_piT<KP>(pi, K, piT);
+  const int nch = hmm_nchunks(Tm, chunk_len);
+  const long long unit = (long long)blockIdx.x * HMM_BWARPS + wib;
+  if (unit >= (long long)N * nch) return;
+  const int n = (int)(unit / nch), cc = (int)(unit % nch);
+  const int t0 = (nch == 1) ? 0 : cc * chunk_len;
+  const int t1 = (nch == 1) ? Tm : min(Tm, t0 + chunk_len);
+  const int ts = (cc == nch - 1) ? t1 - 1 : min(Tm, t1 + burn_in) - 1;  // first frame visited
+  int carry1;
+  const int out = hmm_backward_walk<KP>(mask + (size_t)n * mask_stride, u + (size_t)n * Tm,
+                                        ws.stay + (size_t)n * Tm * 4, z + (size_t)n * Tm, ws, piT, bring, lt,
+                                        n, Tm, K, t0, t1, ts, -1, &carry1);
   if (lane == 0) {
-    ws.carry_out[unit] = s_next;
+    ws.carry_warm[unit] = carry1;
+    ws.carry_out[unit] = out;
   }
 }
 
-// chunk cc must have started from the carry that chunk cc + 1 left behind
-__global__ void hmm_bcheck_kernel(HmmWs ws, int N, int nch, unsigned* __restrict__ err_bits) {
-  const long long unit = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (unit >= (long long)N * nch) return;
-  const int cc = (int)(unit % nch);
-  if (cc == nch - 1) return;
-  if (ws.carry_warm[unit] != ws.carry_out[unit + 1]) atomicMax(err_bits, __float_as_uint(2.0f));
+// One warp per session walks its chunks from the top: a chunk whose warm-up did not arrive at the
+// carry the chunk above really left behind is sampled again from that carry (sequentially, its
+// own frames only).  Usually nothing, or a handful of chunks, needs redoing.
+template <int KP>
+__global__ void __launch_bounds__(HMM_BWARPS * 32)
+    hmm_brepair_kernel(const float* __restrict__ mask, long long mask_stride,
+                       const double* __restrict__ pi, const float* __restrict__ u, int N, int Tm, int K,
+                       int chunk_len, int* __restrict__ z, HmmWs ws) {
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  extern __shared__ __align__(16) float piT[];
+  unsigned* bring = reinterpret_cast<unsigned*>(piT + KP * KP) + (size_t)wib * (HMM_BRING * 8 + 32);
+  float* lt = reinterpret_cast<float*>(bring + HMM_BRING * 8);
+  const int nch = hmm_nchunks(Tm, chunk_len);
+  const int n = blockIdx.x * HMM_BWARPS + wib;
+  // skip the table load when no session of this CTA has a mismatch
+  int need = 0;
+  if (n < N)
+    for (int cc = lane; cc + 1 < nch; cc += 32)
+      need |= __ldcg(&ws.carry_warm[(size_t)n * nch + cc]) != __ldcg(&ws.carry_out[(size_t)n * nch + cc + 1]);
+  if (!__syncthreads_or(need)) return;
+  hmm_load_piT<KP>(pi, K, piT);
+  if (n >= N) return;
+  for (int cc = nch - 2; cc >= 0; cc--) {
+    const size_t unit = (size_t)n * nch + cc;
+    const int want = __ldcg(&ws.carry_out[unit + 1]);  // L2: lane 0 may have just rewritten it
+    if (__ldcg(&ws.carry_warm[unit]) == want) continue;  // warp-uniform
+    const int t0 = cc * chunk_len, t1 = min(Tm, t0 + chunk_len);
+    int carry1;
+    const int out = hmm_backward_walk<KP>(mask + (size_t)n * mask_stride, u + (size_t)n * Tm,
+                                          ws.stay + (size_t)n * Tm * 4, z + (size_t)n * Tm, ws, piT, bring,
+                                          lt, n, Tm, K, t0, t1, t1 - 1, want, &carry1);
+    __syncwarp();
+    if (lane == 0) {
+      ws.carry_warm[unit] = want;
+      ws.carry_out[unit] = out;
+    }
+    __syncwarp();
+    __threadfence_block();
+  }
 }
 
 // Generic kernel for K > 128 (K <= 1024): thread j owns state j, pi / pi^T in fp32 in global
@@ -556,11 +610,15 @@ static int launch_reg(const float* ll, int ll_tiled, const float* mask, long lon
   const size_t smem = (size_t)(KP * KP + HMM_BWARPS * (HMM_BRING * 8 + 32)) * sizeof(float);
   KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const long long units = (long long)N * nch;
+  const char* eb = getenv("KPMS_HMM_BWD_BURN");  // testing: warm-up of the sampler only (0 = every chunk repaired)
   kern<<<(unsigned)((units + HMM_BWARPS - 1) / HMM_BWARPS), HMM_BWARPS * 32, smem, st>>>(
-      mask, ms, pi, u, N, Tm, K, chunk_len, burn_in, z, ws);
+      mask, ms, pi, u, N, Tm, K, chunk_len, eb ? atoi(eb) : burn_in, z, ws);
   rc = kpms_last_launch();
-  if (rc || nch == 1 || !boundary_err) return rc;
-  hmm_bcheck_kernel<<<(unsigned)((units + 255) / 256), 256, 0, st>>>(ws, N, nch, (unsigned*)boundary_err);
+  if (rc || nch == 1) return rc;
+  auto rep = hmm_brepair_kernel<KP>;
+  KPMS_CUDA(cudaFuncSetAttribute(rep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  rep<<<(unsigned)((N + HMM_BWARPS - 1) / HMM_BWARPS), HMM_BWARPS * 32, smem, st>>>(mask, ms, pi, u, N, Tm, K,
+                                                                                   chunk_len, z, ws);
   return kpms_last_launch();
 }
 

@@ -473,3 +473,23 @@ def test_ar_stats_empty_states_and_ragged(G, D, L, K, T):
     # run to run bit-reproducible
     again = N_(G.ar_sufficient_stats(nlags=L, num_states=K, mask=T_(d['mask']), x=T_(s['x']), z=T_(z)))
     assert np.array_equal(got, again)
+
+
+def test_hmm_backward_chunks_are_repaired(G, monkeypatch):
+    """With no warm-up at all every sampler chunk starts from the wrong carry; the device-side
+    repair pass must then reproduce, bit for bit, what well warmed-up chunks give."""
+    import torch
+    ll, mask, pi, u = _hmm_case(21, N=6, T=3000, K=100, ragged=True)
+    kw = dict(ll=T_(ll), mask=T_(mask), pi=T_(pi), u=T_(u), chunk_len=300, burn_in=256, strict=False,
+              return_info=True)
+    z_ref, l_ref, i_ref = G.sample_hmm_stateseqs(**kw)
+    monkeypatch.setenv("KPMS_HMM_BWD_BURN", "0")
+    z_rep, l_rep, i_rep = G.sample_hmm_stateseqs(**kw)
+    monkeypatch.setenv("KPMS_HMM_BWD_BURN", "3")
+    z_rep3, _, _ = G.sample_hmm_stateseqs(**kw)
+    torch.cuda.synchronize()
+    assert torch.equal(z_ref, z_rep) and torch.equal(z_ref, z_rep3)
+    assert torch.equal(l_ref, l_rep)
+    zo, lo = O._hmm_batch(ll, mask, pi, u)
+    valid = mask > 0
+    assert (N_(z_rep)[valid] == zo[valid]).mean() >= 0.999
