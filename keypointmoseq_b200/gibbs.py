@@ -30,11 +30,12 @@ last_latents_boundary_err = None
 # HMM chunking (K <= 128): same idea for the forward filter and the backward sampler.  The library
 # reports the largest absolute mismatch of the normalised messages at chunk boundaries (1e30 for a
 # mask that is not trailing padding); sampler chunks are repaired on the device and never fail.
-# `tol`: a mismatch eps perturbs only the first frames of a chunk, so the marginal log-likelihood
-# moves by about n_chunks * eps (3e-4 -> < 1e-6 relative on the bench shard) and the sampled
-# states by far less than the 0.1 % the contract allows (measured: 1e-4 mismatch changes neither,
-# tools/hmm_model_data.py); above it strict mode retries with a longer warm-up, then exactly.
-STATESEQ_CHUNKING = {"chunk_len": "auto", "burn_in": 256, "strict": True, "tol": 3e-4}
+# `tol`: a mismatch eps perturbs only the first frames of a chunk and decays geometrically.
+# Measured on the bench shard (tools/hmm_model_data.py, 17.5 k chunks): 1e-4 changes neither the
+# sampled states nor the marginal log-likelihood; 5e-2 moves the log-likelihood by 6e-6 relative
+# (the contract allows 1e-5) and 3e-5 of the states (contract: 1e-3).  1e-3 keeps a factor 50 of
+# margin; above it strict mode retries with a longer warm-up, then runs the sequential kernels.
+STATESEQ_CHUNKING = {"chunk_len": "auto", "burn_in": 256, "strict": True, "tol": 1e-3}
 HMM_CTAS_PER_SM = 3
 last_stateseq_boundary_err = None
 # how often a chunked pass failed its boundary check and was redone exactly (diagnostics)
