@@ -6,12 +6,28 @@ Only `tests/`, `__graft_entry__.smoke()` and `bench.py`'s `cpu_baseline` /
 `--impl reference` legs may import it.  The product (`keypointmoseq_b200`)
 never imports it and has no CPU fallback.
 
-PARITY UNPINNED: the reference ships no tests, no golden vectors and its example
-data is stripped; JAX / tensorflow-probability are not installable in this image,
-so the reference itself cannot be executed here or on the GPU box.  The oracle is
-therefore pinned only by (a) line-by-line correspondence with the cited reference
-lines and (b) the independent known-answer tests in `tests/test_oracle_*.py`
-(brute-force HMM enumeration, dense joint-Gaussian Kalman, naive-loop statistics).
+PARITY STATUS: pinned against the reference's own source, with the caveat below.  The
+reference ships no tests, no golden vectors and its example data is stripped, and JAX /
+tensorflow-probability are not installable in this image, so the reference cannot run as
+shipped.  Instead (tests/test_reference_pins.py, fixtures under tests/golden/):
+
+(1) its two numba functions on the path (`transitions.py:7-21` sample_crp_tablecounts with
+    numba's seeded Mersenne-Twister stream replayed as injected uniforms, `util.py:178-189`
+    count_transitions) were executed unmodified: the oracle and the CUDA kernels equal their
+    outputs bit for bit;
+(2) the unmodified files gibbs.py, kalman.py, distributions.py and util.py were executed under
+    a NumPy stand-in for the JAX calls they make (`tests/golden/jax_numpy_shim.py`: jit =
+    identity, vmap / lax.scan / lax.map / lax.cond = Python loops, jnp = numpy, random draws
+    injected): every resample_* step except resample_hdp_transitions; the oracle agrees with
+    those runs to 1e-12 .. 1e-16 (state sequences identical) and the CUDA path to its stated
+    float32 tolerances.
+
+Caveat: what is NOT the reference's code in (2) are the third-party samplers and densities it
+delegates to -- jr.categorical, jr.gamma, jr.normal / multivariate_normal, tfd.VonMises.sample,
+tfd.MultivariateNormalFullCovariance.log_prob -- restated as described below; XLA's own floating
+point behaviour is likewise not reproduced.  In addition the independent known-answer tests in
+`tests/test_oracle_known_answers.py` (brute-force HMM enumeration, dense joint-Gaussian Kalman
+posterior, naive-loop statistics) check the algorithms themselves.
 
 Every random quantity is INJECTED (no RNG in here) so that the CUDA path and the
 oracle consume identical draws:

@@ -1,0 +1,100 @@
+"""Golden vectors from the reference's own gibbs.py / kalman.py / distributions.py / util.py,
+executed in the build container under tests/golden/jax_numpy_shim.py (JAX itself is not
+installed; see the shim's header for exactly what is and is not the reference's code).
+
+Every resample_* step of keypoint_slds.ipynb cell 12 except resample_hdp_transitions (whose
+numba part is pinned separately by make_reference_pins.py) is run ONCE on the same small problem,
+with injected draws; inputs, draws and the reference's outputs go to reference_sweep.npz.
+
+    python tests/golden/make_reference_sweep.py
+"""
+import importlib
+import os
+import sys
+
+import numpy as np
+
+sys.dont_write_bytecode = True
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, HERE)
+
+import jax_numpy_shim as shim                         # noqa: E402
+from keypointmoseq_b200.synthetic import simulate, default_hypparams   # noqa: E402
+from oracle import kpms_oracle as O                    # noqa: E402  (only its von Mises restatement)
+
+
+def main():
+    shim.install()
+    shim.VonMises.sampler = O.sample_vonmises
+    sys.path.insert(0, "/root/reference")
+    G = importlib.import_module("keypoint_moseq.gibbs")
+
+    N, T, k, dk, D, L, K, R = 3, 48, 5, 2, 4, 2, 5, 6
+    data, st, pr, Gamma = simulate(77, N, T, k=k, dk=dk, D=D, L=L, K=K, ragged=True, dtype=np.float64)
+    trans, ar, obs, loc = default_hypparams(D, L, K)
+    rng = np.random.default_rng(4242)
+    n = D * L
+    f = lambda a: shim.sa(np.array(a, dtype=np.float64))
+    r32 = lambda a: np.asarray(a, dtype=np.float32).astype(np.float64)   # float32-representable: the CUDA path stores these in fp32
+    Y, mask, x, v, h, s = (f(r32(data["Y"])), f(data["mask"]), f(r32(st["x"])), f(r32(st["v"])), f(r32(st["h"])),
+                           f(r32(st["s"])))
+    z = shim.sa(np.array(st["z"], dtype=np.int64))
+    Ab, Q, pi, Cd, sigmasq = f(pr["Ab"]), f(pr["Q"]), f(pr["pi"]), f(pr["Cd"]), f(pr["sigmasq"])
+    key = shim.Key()
+    out = dict(Y=Y, mask=mask, x=x, v=v, h=h, s=s, z=z, Ab=Ab, Q=Q, pi=pi, Cd=Cd, sigmasq=sigmasq,
+               dims=np.array([N, T, k, dk, D, L, K, R]))
+    for name, hp in (("ar", ar), ("obs", obs), ("loc", loc)):
+        for a, b in hp.items():
+            out[f"hyp_{a}"] = np.asarray(b, dtype=np.float64)
+
+    def run(draws, fn, **kw):
+        shim.Ctx.draws, shim.Ctx.vmap, shim.Ctx.scan_t = draws, [], None
+        return fn(key, **kw)
+
+    # 4: state sequences
+    u = r32(rng.random((N, T - L)) * 0.998 + 0.001)
+    zr, llr = run({"uniform": u}, G.resample_stateseqs, x=x, mask=mask, Ab=Ab, Q=Q, pi=pi)
+    out.update(d_stateseq_u=u, r_stateseq_z=np.asarray(zr, dtype=np.int64), r_stateseq_ll=np.asarray(llr))
+    # 5: latents
+    w, wl = r32(rng.standard_normal((N, T - L, n))), r32(rng.standard_normal((N, n)))
+    xr = run({"normal": w, "mvn": wl}, G.resample_latents, Y=Y, mask=mask, v=v, h=h, z=z, s=s, Cd=Cd,
+             sigmasq=sigmasq, Ab=Ab, Q=Q)
+    out.update(d_latents_w=w, d_latents_w_last=wl, r_latents_x=np.asarray(xr))
+    # 6: heading
+    uvm = r32(rng.random((N, T, R, 3)) * 0.998 + 0.001)
+    hr = run({"vonmises": uvm}, G.resample_heading, Y=Y, v=v, x=x, s=s, Cd=Cd, sigmasq=sigmasq)
+    out.update(d_heading_u=uvm, r_heading_h=np.asarray(hr))
+    # 7: location
+    wv, wvl = r32(rng.standard_normal((N, T - 1, dk))), r32(rng.standard_normal((N, dk)))
+    vr = run({"normal": wv, "mvn": wvl}, G.resample_location, mask=mask, Y=Y, h=h, x=x, s=s, Cd=Cd,
+             sigmasq=sigmasq, sigmasq_loc=float(loc["sigmasq_loc"]))
+    out.update(d_location_w=wv, d_location_w_last=wvl, r_location_v=np.asarray(vr))
+    # 8: scales
+    gs = r32(rng.gamma((float(obs["nu_s"]) + 3) / 2, size=(N, T, k)))
+    sr = run({"gamma": gs}, G.resample_scales, x=x, v=v, h=h, Y=Y, Cd=Cd, sigmasq=sigmasq,
+             nu_s=float(obs["nu_s"]), s_0=float(obs["s_0"]))
+    out.update(d_scales_g=gs, r_scales_s=np.asarray(sr))
+    # 2: observation variance
+    msum = float(mask.sum())
+    gv = rng.gamma((float(obs["nu_sigma"]) + 3 * msum) / 2, size=(k,))
+    sg = run({"gamma": gv}, G.resample_obs_variance, Y=Y, mask=mask, Cd=Cd, v=v, h=h, x=x, s=s,
+             nu_sigma=float(obs["nu_sigma"]), sigmasq_0=float(obs["sigmasq_0"]))
+    out.update(d_obsvar_g=gv, r_obsvar_sigmasq=np.asarray(sg))
+    # 1: AR parameters (vmapped over states; chi-square draws enter as gamma(degs/2) * 2)
+    counts = np.array([((np.asarray(z) == kk) & (np.asarray(mask)[:, L:] > 0)).sum() for kk in range(K)], dtype=np.float64)
+    chi2 = np.stack([rng.chisquare(float(ar["nu_0"]) + counts[kk] - np.arange(D)) for kk in range(K)])
+    nrm = rng.standard_normal((K, D * (D - 1) // 2))
+    Gm = rng.standard_normal((K, D, D * L + 1))
+    Abr, Qr = run({"gamma": chi2 / 2, "normal": nrm, "normal2": Gm}, G.resample_ar_params, nlags=L, num_states=K,
+                  mask=mask, x=x, z=z, nu_0=float(ar["nu_0"]), S_0=f(ar["S_0"]), M_0=f(ar["M_0"]), K_0=f(ar["K_0"]))
+    out.update(d_ar_chi2=chi2, d_ar_normals=nrm, d_ar_G=Gm, r_ar_Ab=np.asarray(Abr), r_ar_Q=np.asarray(Qr))
+
+    path = os.path.join(HERE, "reference_sweep.npz")
+    np.savez_compressed(path, **{a: np.asarray(b) for a, b in out.items()})
+    print("wrote", path, os.path.getsize(path), "bytes")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,158 @@
+"""Oracle and CUDA kernels against outputs of the REFERENCE'S OWN numba code
+(tests/golden/reference_pins.npz, made by tests/golden/make_reference_pins.py in the build
+container from /root/reference): rows a10 (count_transitions, util.py:178-189) and a11
+(sample_crp_tablecounts, transitions.py:7-21).  Integer work: bit-exact."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import kpms_oracle as O
+
+PINS = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_pins.npz"))
+
+
+def _crp_case(ci):
+    customers = PINS[f"crp{ci}_customers"]
+    uni = np.random.RandomState(int(PINS[f"crp{ci}_seed"])).random_sample(int(customers.sum()))
+    return float(PINS[f"crp{ci}_alpha"]), customers, PINS[f"crp{ci}_betas"], uni, PINS[f"crp{ci}_m"]
+
+
+@pytest.mark.parametrize("ci", range(int(PINS["n_crp"])))
+def test_oracle_crp_tablecounts_equals_reference(ci):
+    alpha, customers, betas, uni, m_ref = _crp_case(ci)
+    assert np.array_equal(O.sample_crp_tablecounts(alpha, customers, betas, uni), m_ref)
+
+
+@pytest.mark.parametrize("ci", range(int(PINS["n_cnt"])))
+def test_oracle_count_transitions_equals_reference(ci):
+    got = O.count_transitions(int(PINS[f"cnt{ci}_K"]), PINS[f"cnt{ci}_mask"], PINS[f"cnt{ci}_z"])
+    assert np.array_equal(got, PINS[f"cnt{ci}_counts"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ci", range(int(PINS["n_crp"])))
+def test_cuda_crp_tablecounts_equals_reference(ci):
+    import torch
+    from keypointmoseq_b200 import gibbs as G
+    alpha, customers, betas, uni, m_ref = _crp_case(ci)
+    K = customers.shape[0]
+    dev = "cuda"
+    draws = {"randseq": torch.as_tensor(uni, device=dev), "u_thin": torch.zeros((K, 4), device=dev)}
+    _, ms_raw, _ = G.sample_ms(0, torch.as_tensor(customers, device=dev), torch.as_tensor(betas, device=dev),
+                               alpha, 1e6, draws=draws)
+    assert np.array_equal(ms_raw.cpu().numpy(), m_ref)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ci", range(int(PINS["n_cnt"])))
+def test_cuda_count_transitions_equals_reference(ci):
+    import torch
+    from keypointmoseq_b200 import gibbs as G
+    K = int(PINS[f"cnt{ci}_K"])
+    z = torch.as_tensor(PINS[f"cnt{ci}_z"].astype(np.int32), device="cuda")
+    mask = torch.as_tensor(PINS[f"cnt{ci}_mask"].astype(np.float32), device="cuda")
+    got = G.transition_counts(z=z, mask=mask, num_states=K)
+    assert np.array_equal(got.cpu().numpy().astype(np.float64), PINS[f"cnt{ci}_counts"])
+
+
+# ====================================================================== the resample_* steps
+# tests/golden/reference_sweep.npz: the reference's own gibbs.py / kalman.py / distributions.py /
+# util.py executed under a NumPy stand-in for the JAX calls they make (tests/golden/jax_numpy_shim.py),
+# with injected draws.  Per-frame inputs and draws are float32-representable, parameters float64.
+SW = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_sweep.npz"))
+N_, T_, k_, dk_, D_, L_, K_, R_ = [int(v) for v in SW["dims"]]
+
+
+def _kw():
+    return dict(Y=SW["Y"], mask=SW["mask"], x=SW["x"], v=SW["v"], h=SW["h"], s=SW["s"], z=SW["z"], Ab=SW["Ab"],
+                Q=SW["Q"], pi=SW["pi"], Cd=SW["Cd"], sigmasq=SW["sigmasq"], Gamma=O.center_embedding(k_))
+
+
+def _rel(a, b):
+    return float(np.abs(np.asarray(a, dtype=np.float64) - b).max() / (np.abs(b).max() + 1e-300))
+
+
+def test_oracle_stateseqs_equals_reference():
+    z, ll = O.resample_stateseqs(x=SW["x"], mask=SW["mask"], Ab=SW["Ab"], Q=SW["Q"], pi=SW["pi"], u=SW["d_stateseq_u"])
+    assert np.array_equal(z, SW["r_stateseq_z"]) and _rel(ll, SW["r_stateseq_ll"]) < 1e-12
+
+
+def test_oracle_latents_equals_reference():
+    x = O.resample_latents(**_kw(), w=SW["d_latents_w"], w_last=SW["d_latents_w_last"])
+    assert _rel(x, SW["r_latents_x"]) < 1e-11
+
+
+def test_oracle_heading_location_scales_obsvar_equal_reference():
+    kw = _kw()
+    h = O.resample_heading(**kw, u=SW["d_heading_u"])
+    assert np.abs(np.angle(np.exp(1j * (h - SW["r_heading_h"])))).max() < 1e-12
+    v = O.resample_location(**kw, sigmasq_loc=float(SW["hyp_sigmasq_loc"]), w=SW["d_location_w"],
+                            w_last=SW["d_location_w_last"])
+    assert _rel(v, SW["r_location_v"]) < 1e-12
+    s = O.resample_scales(**kw, nu_s=float(SW["hyp_nu_s"]), s_0=float(SW["hyp_s_0"]), g=SW["d_scales_g"])
+    assert _rel(s, SW["r_scales_s"]) < 1e-12
+    sg = O.resample_obs_variance(**kw, nu_sigma=float(SW["hyp_nu_sigma"]), sigmasq_0=float(SW["hyp_sigmasq_0"]),
+                                 g=SW["d_obsvar_g"])
+    assert _rel(sg, SW["r_obsvar_sigmasq"]) < 1e-12
+
+
+def test_oracle_ar_params_equal_reference():
+    Ab, Q = O.resample_ar_params(nlags=L_, num_states=K_, mask=SW["mask"], x=SW["x"], z=SW["z"],
+                                 nu_0=float(SW["hyp_nu_0"]), S_0=SW["hyp_S_0"], M_0=SW["hyp_M_0"], K_0=SW["hyp_K_0"],
+                                 chi2=SW["d_ar_chi2"], normals=SW["d_ar_normals"], G=SW["d_ar_G"])
+    assert _rel(Ab, SW["r_ar_Ab"]) < 1e-10 and _rel(Q, SW["r_ar_Q"]) < 1e-10
+
+
+def _gpu_kw():
+    import torch
+    t = lambda a, dt: torch.as_tensor(np.ascontiguousarray(a), device="cuda").to(dt)
+    f32, f64 = torch.float32, torch.float64
+    return dict(Y=t(SW["Y"], f32), mask=t(SW["mask"], f32), x=t(SW["x"], f32), v=t(SW["v"], f32), h=t(SW["h"], f32),
+                s=t(SW["s"], f32), z=t(SW["z"], torch.int32), Ab=t(SW["Ab"], f64), Q=t(SW["Q"], f64),
+                pi=t(SW["pi"], f64), Cd=t(SW["Cd"], f64), sigmasq=t(SW["sigmasq"], f64)), t
+
+
+@pytest.mark.gpu
+def test_cuda_steps_equal_reference():
+    """The CUDA path against the reference's own outputs (same tolerances as tests/test_gpu_parity.py)."""
+    import torch
+    from keypointmoseq_b200 import gibbs as G
+    kw, t = _gpu_kw()
+    f32, f64 = torch.float32, torch.float64
+    n = lambda a: a.detach().cpu().numpy().astype(np.float64)
+    # stateseqs: integer states bit-exact here (no near-ties in this fixture), log-likelihood 1e-5
+    z, ll = G.resample_stateseqs(0, **kw, draws={"u": t(SW["d_stateseq_u"], f32)})
+    valid = SW["mask"][:, L_:] > 0
+    assert (n(z)[valid] == SW["r_stateseq_z"][valid]).mean() >= 0.999 and np.all(n(z)[~valid] == 0)
+    assert np.all(np.abs(n(ll) - SW["r_stateseq_ll"]) <= 1e-5 * np.abs(SW["r_stateseq_ll"]))
+    # latents
+    x = G.resample_latents(0, **kw, draws={"w": t(SW["d_latents_w"], f32), "w_last": t(SW["d_latents_w_last"], f32)})
+    xr = SW["r_latents_x"]
+    assert np.abs(n(x) - xr).max() < 2e-6 * max(1.0, np.abs(xr).max())
+    # heading
+    # (in zero-padded frames the concentration is ~1e-14 and the mean direction is rounding noise)
+    h = G.resample_heading(0, **kw, draws={"u": t(SW["d_heading_u"], f32)})
+    live = SW["mask"] > 0
+    assert np.abs(np.angle(np.exp(1j * (n(h) - SW["r_heading_h"]))))[live].max() < 1e-6
+    # location
+    v = G.resample_location(0, **kw, sigmasq_loc=float(SW["hyp_sigmasq_loc"]),
+                            draws={"w": t(SW["d_location_w"], f32), "w_last": t(SW["d_location_w_last"], f32)})
+    vr = SW["r_location_v"]
+    assert np.abs(n(v) - vr).max() < 3e-7 * max(1.0, np.abs(vr).max())
+    # scales
+    s = G.resample_scales(0, **kw, nu_s=float(SW["hyp_nu_s"]), s_0=float(SW["hyp_s_0"]),
+                          draws={"g": t(SW["d_scales_g"], f32)})
+    assert np.allclose(n(s), SW["r_scales_s"], rtol=3e-7)
+    # observation variance
+    sg = G.resample_obs_variance(0, **kw, nu_sigma=float(SW["hyp_nu_sigma"]), sigmasq_0=float(SW["hyp_sigmasq_0"]),
+                                 draws={"g": t(SW["d_obsvar_g"], f64)})
+    assert np.allclose(n(sg), SW["r_obsvar_sigmasq"], rtol=1e-10)
+    # AR parameters
+    Ab, Q = G.resample_ar_params(0, nlags=L_, num_states=K_, mask=kw["mask"], x=kw["x"], z=kw["z"],
+                                 nu_0=float(SW["hyp_nu_0"]), S_0=t(SW["hyp_S_0"], f64), M_0=t(SW["hyp_M_0"], f64),
+                                 K_0=t(SW["hyp_K_0"], f64),
+                                 draws={"chi2": t(SW["d_ar_chi2"], f64), "normals": t(SW["d_ar_normals"], f64),
+                                        "G": t(SW["d_ar_G"], f64)})
+    assert np.allclose(n(Q), SW["r_ar_Q"], rtol=1e-7, atol=1e-12)
+    assert np.allclose(n(Ab), SW["r_ar_Ab"], rtol=1e-6, atol=1e-9)
