@@ -164,6 +164,154 @@ extern "C" int kpms_obs_variance_stats(const float* Y, const float* mask, const 
   return kpms_last_launch();
 }
 
+// ======================================================================== (f)1: moments for Cd
+// Reference: gibbs.py:58-82 (resample_obs_params).  The reference materialises per-frame
+// (k-1)x(k-1) and k*d x (D+1)(k-1)d temporaries; all it needs from the data are, per keypoint j,
+//   W[j] = sum_f w_fj xt_f xt_f^T   (D+1 x D+1),   V[j] = sum_f w_fj xt_f Ytild_fj^T   (D+1 x dk),
+//   w_fj = mask_f / (s_fj sigmasq_j),  xt = [x; 1],  Ytild = R(-h)(Y - v)        (util.py:140-166)
+// (S_xx = sum_j Gamma_j Gamma_j^T (x) W[j], S_yx = sum_j Gamma_j (x) V[j]; the 330-dim Gaussian draw
+// stays with the host-side dense algebra).  CTA = tile of OP_TILE frames staged in shared memory in
+// fp64; thread <-> up to OP_PAIRS (keypoint, row a) pairs, whose D+1+dk accumulators stay in
+// registers for the whole launch; per-CTA partials are combined in fixed order (reproducible).
+#define OP_THREADS 256
+#define OP_TILE 64
+#define OP_PAIRS 3
+#define OP_BLOCKS (148 * 2)
+#define OP_ACC (OBS_XMAX + 1 + OBS_DKMAX)
+
+extern "C" size_t kpms_obs_params_stats_workspace_bytes(int N, int T, int k, int dk, int D) {
+  if (N <= 0 || T <= 0 || k <= 0 || D <= 0) return 0;
+  (void)dk;
+  return kpms_round_up((size_t)OP_BLOCKS * k * (D + 1) * OP_ACC * sizeof(double), 256);
+}
+
+__global__ void __launch_bounds__(OP_THREADS)
+    obs_params_stats_kernel(const float* __restrict__ Y, const float* __restrict__ mask,
+                            const float* __restrict__ v, const float* __restrict__ h,
+                            const float* __restrict__ x, const float* __restrict__ s,
+                            const double* __restrict__ sigmasq, ObsDims dm, double* __restrict__ partial) {
+  extern __shared__ __align__(16) double sm[];
+  const int k = dm.k, dk = dm.dk, D = dm.D, D1 = D + 1;
+  double* xt = sm;                         // [OP_TILE][D1]
+  double* yt = xt + OP_TILE * D1;          // [OP_TILE][k*dk]
+  double* wt = yt + OP_TILE * k * dk;      // [OP_TILE][k]
+  double* rot = wt + OP_TILE * k;          // [OP_TILE][2 + dk + 1]: cos, sin, v, mask
+  double* isg = rot + OP_TILE * (3 + dk);  // [k] 1 / sigmasq
+  for (int i = threadIdx.x; i < k; i += blockDim.x) isg[i] = 1.0 / sigmasq[i];
+  const int npairs = k * D1;
+  int pj[OP_PAIRS], pa[OP_PAIRS];
+  double acc[OP_PAIRS][OP_ACC];
+#pragma unroll
+  for (int q = 0; q < OP_PAIRS; q++) {
+    const int p = threadIdx.x + q * OP_THREADS;
+    pj[q] = (p < npairs) ? p / D1 : -1;
+    pa[q] = (p < npairs) ? p % D1 : 0;
+#pragma unroll
+    for (int e = 0; e < OP_ACC; e++) acc[q][e] = 0.0;
+  }
+  const long long frames = (long long)dm.N * dm.T;
+  for (long long f0 = (long long)blockIdx.x * OP_TILE; f0 < frames; f0 += (long long)gridDim.x * OP_TILE) {
+    const int rows = (int)min((long long)OP_TILE, frames - f0);
+    __syncthreads();  // previous tile fully consumed
+    for (int r = threadIdx.x; r < OP_TILE; r += blockDim.x) {
+      const long long f = f0 + r;
+      double* ro = rot + r * (3 + dk);
+      if (r < rows) {
+        double sn, cs;
+        sincos((double)h[f], &sn, &cs);
+        ro[0] = cs;
+        ro[1] = sn;
+        for (int c = 0; c < dk; c++) ro[2 + c] = (double)v[f * dk + c];
+        ro[2 + dk] = (double)mask[f];
+        for (int a = 0; a < D; a++) xt[r * D1 + a] = (double)x[f * D + a];
+        xt[r * D1 + D] = 1.0;
+      } else {
+        ro[0] = 1.0;
+        ro[1] = 0.0;
+        for (int c = 0; c < dk; c++) ro[2 + c] = 0.0;
+        ro[2 + dk] = 0.0;
+        for (int a = 0; a < D1; a++) xt[r * D1 + a] = 0.0;
+      }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < OP_TILE * k; i += blockDim.x) {   // coalesced over (frame, keypoint)
+      const int r = i / k, j = i - r * k;
+      const double* ro = rot + r * (3 + dk);
+      double w = 0.0, y0 = 0.0, y1 = 0.0, y2 = 0.0;
+      if (r < rows) {
+        const long long f = f0 + r;
+        const float* Yf = Y + ((size_t)f * k + j) * dk;
+        rot_inv(ro[0], ro[1], (double)Yf[0] - ro[2], (double)Yf[1] - ro[3], y0, y1);
+        if (dk > 2) y2 = (double)Yf[2] - ro[4];
+        w = ro[2 + dk] * isg[j] / (double)s[(size_t)f * k + j];
+      }
+      wt[r * k + j] = w;
+      yt[(r * k + j) * dk + 0] = y0;
+      yt[(r * k + j) * dk + 1] = y1;
+      if (dk > 2) yt[(r * k + j) * dk + 2] = y2;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < OP_PAIRS; q++) {
+      if (pj[q] < 0) continue;
+      const int j = pj[q], a = pa[q];
+      for (int r = 0; r < OP_TILE; r++) {
+        const double wa = wt[r * k + j] * xt[r * D1 + a];
+#pragma unroll
+        for (int b = 0; b <= OBS_XMAX; b++)
+          if (b < D1) acc[q][b] = fma(wa, xt[r * D1 + b], acc[q][b]);
+#pragma unroll
+        for (int c = 0; c < OBS_DKMAX; c++)
+          if (c < dk) acc[q][OBS_XMAX + 1 + c] = fma(wa, yt[(r * k + j) * dk + c], acc[q][OBS_XMAX + 1 + c]);
+      }
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < OP_PAIRS; q++) {
+    const int p = threadIdx.x + q * OP_THREADS;
+    if (p < npairs) {
+      double* o = partial + ((size_t)blockIdx.x * npairs + p) * OP_ACC;
+#pragma unroll
+      for (int e = 0; e < OP_ACC; e++) o[e] = acc[q][e];
+    }
+  }
+}
+
+__global__ void obs_params_reduce_kernel(const double* __restrict__ partial, int blocks, int k, int D, int dk,
+                                         double* __restrict__ W, double* __restrict__ V) {
+  const int D1 = D + 1, npairs = k * D1;
+  const int p = blockIdx.x, e = threadIdx.x;  // pair, accumulator entry
+  if (p >= npairs || e >= OP_ACC) return;
+  double t = 0.0;
+  for (int b = 0; b < blocks; b++) t += partial[((size_t)b * npairs + p) * OP_ACC + e];
+  const int j = p / D1, a = p % D1;
+  if (e < D1) W[((size_t)j * D1 + a) * D1 + e] = t;
+  else if (e >= OBS_XMAX + 1 && e - (OBS_XMAX + 1) < dk) V[((size_t)j * D1 + a) * dk + (e - (OBS_XMAX + 1))] = t;
+}
+
+extern "C" int kpms_obs_params_stats(const float* Y, const float* mask, const float* v, const float* h,
+                                     const float* x, const float* s, const double* sigmasq, int N, int T,
+                                     int k, int dk, int D, double* W, double* V, void* workspace,
+                                     size_t workspace_bytes, void* stream) {
+  KPMS_REQUIRE(Y && mask && v && h && x && s && sigmasq && W && V && workspace, KPMS_ERR_NULL);
+  int rc = obs_check(N, T, k, dk, D);
+  if (rc) return rc;
+  KPMS_REQUIRE(k * (D + 1) <= OP_PAIRS * OP_THREADS, KPMS_ERR_UNSUPPORTED);
+  KPMS_REQUIRE(kpms_aligned(workspace, 256) &&
+                   workspace_bytes >= kpms_obs_params_stats_workspace_bytes(N, T, k, dk, D),
+               KPMS_ERR_WORKSPACE);
+  cudaStream_t st = (cudaStream_t)stream;
+  ObsDims dm{N, T, k, dk, D};
+  const size_t smem = ((size_t)OP_TILE * ((D + 1) + k * dk + k + 3 + dk) + k) * sizeof(double);
+  KPMS_CUDA(cudaFuncSetAttribute(obs_params_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  obs_params_stats_kernel<<<OP_BLOCKS, OP_THREADS, smem, st>>>(Y, mask, v, h, x, s, sigmasq, dm,
+                                                              (double*)workspace);
+  rc = kpms_last_launch();
+  if (rc) return rc;
+  obs_params_reduce_kernel<<<k * (D + 1), 32, 0, st>>>((const double*)workspace, OP_BLOCKS, k, D, dk, W, V);
+  return kpms_last_launch();
+}
+
 // ======================================================================== a14
 __global__ void __launch_bounds__(256)
     scales_kernel(const float* __restrict__ Y, const float* __restrict__ v,

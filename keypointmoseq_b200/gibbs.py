@@ -330,6 +330,54 @@ def obs_variance_stats(*, Y, mask, Cd, v, h, x, s, Gamma=None, **kwargs):
     return S_y, msum
 
 
+# ------------------------------------------------------------------------ (f)1
+def obs_params_stats(*, Y, mask, sigmasq, v, h, x, s, **kwargs):
+    """Per-keypoint weighted moments of gibbs.py:58-82 -> (W (k,D+1,D+1), V (k,D+1,dk)) float64."""
+    lib = _lib.load()
+    Y = f32(Y)
+    dev = Y.device
+    N, T, k, dk = Y.shape
+    mask, v, h, x, s = f32(mask, dev), f32(v, dev), f32(h, dev), f32(x, dev), f32(s, dev)
+    sigmasq = f64(sigmasq, dev)
+    D = x.shape[-1]
+    W = torch.empty((k, D + 1, D + 1), dtype=torch.float64, device=dev)
+    V = torch.empty((k, D + 1, dk), dtype=torch.float64, device=dev)
+    ws = _lib.WORKSPACE.get("obsparams", lib.kpms_obs_params_stats_workspace_bytes(N, T, k, dk, D), dev)
+    _lib.check(lib.kpms_obs_params_stats(
+        _lib.ptr(Y), _lib.ptr(mask), _lib.ptr(v), _lib.ptr(h), _lib.ptr(x), _lib.ptr(s), _lib.ptr(sigmasq),
+        N, T, k, dk, D, _lib.ptr(W), _lib.ptr(V), _lib.ptr(ws), ws.numel(), _lib.stream_ptr(dev)),
+        "kpms_obs_params_stats")
+    return W, V
+
+
+def sample_obs_params(key, W, V, Gamma, *, sigmasq_C, draws=None):
+    """gibbs.py:69-82 given the (possibly all-reduced) moments -> Cd ((k-1) dk, D+1) float64."""
+    dev = W.device
+    k, D1, dk = V.shape
+    Gamma = f64(Gamma, dev)
+    S4 = torch.einsum('ji,jl,jab->aibl', Gamma, Gamma, W)                       # gibbs.py:69-74
+    S_xx = torch.kron(S4.reshape(D1 * (k - 1), D1 * (k - 1)).contiguous(),
+                      torch.eye(dk, dtype=torch.float64, device=dev))
+    S_yx = torch.einsum('ji,jac->aic', Gamma, V).reshape(-1)                    # gibbs.py:77-80
+    n = dk * D1 * (k - 1)
+    Sigma_n = torch.linalg.inv(torch.eye(n, dtype=torch.float64, device=dev) / sigmasq_C + S_xx)
+    Sigma_n = 0.5 * (Sigma_n + Sigma_n.T)
+    mu_n = Sigma_n @ S_yx
+    if draws is not None:
+        w = f64(draws["w"], dev)
+    else:
+        w = torch.randn((n,), dtype=torch.float64, device=dev, generator=dist.torch_generator(dist.seed_of(key), 13, dev))
+    draw = mu_n + torch.linalg.cholesky(Sigma_n) @ w                            # jr.multivariate_normal
+    return draw.reshape(D1, dk * (k - 1)).T.contiguous()
+
+
+def resample_obs_params(key, *, Y, mask, sigmasq, v, h, x, s, sigmasq_C, Gamma=None, draws=None, **kwargs):
+    """gibbs.py:58-82 -> Cd ((k-1) dk, D+1) float64."""
+    W, V = obs_params_stats(Y=Y, mask=mask, sigmasq=sigmasq, v=v, h=h, x=x, s=s)
+    k = Y.shape[2]
+    return sample_obs_params(key, W, V, _gamma(Gamma, k, W.device), sigmasq_C=sigmasq_C, draws=draws)
+
+
 def sample_obs_variance(key, S_y, msum, *, nu_sigma, sigmasq_0, draws=None):
     """gibbs.py:94-96 given the (possibly all-reduced) statistics."""
     variance = (nu_sigma * sigmasq_0 + S_y) / (nu_sigma + 3 * msum)   # literal 3: gibbs.py:94

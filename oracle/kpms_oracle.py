@@ -487,6 +487,44 @@ def resample_obs_variance(*, Y, mask, Cd, v, h, x, s, nu_sigma, sigmasq_0, Gamma
     return sample_scaled_inv_chi2(degs, variance, g)
 
 
+def obs_params_stats(*, Y, mask, sigmasq, v, h, x, s, **kwargs):
+    """The per-keypoint weighted moments behind gibbs.py:58-82: with w_fj = mask_f / (s_fj sigmasq_j),
+    W[j] = sum_f w_fj xt_f xt_f^T  (D+1, D+1)  and  V[j] = sum_f w_fj xt_f Ytild_fj^T  (D+1, d),
+    xt = pad_affine(x).  (S_xx = sum_j Gamma_j Gamma_j^T (x) W[j], S_yx = sum_j Gamma_j (x) V[j].)"""
+    k, d = Y.shape[-2:]
+    D = x.shape[-1]
+    m = mask.reshape(-1)
+    sf = s.reshape(-1, k)
+    xt = pad_affine(x.reshape(-1, D))
+    Yt = inverse_affine_transform(Y, v, h).reshape(-1, k, d)
+    w = m[:, None] / (sf * sigmasq[None, :])                       # (F, k)
+    W = np.einsum('fj,fa,fb->jab', w, xt, xt)
+    V = np.einsum('fj,fa,fjc->jac', w, xt, Yt)
+    return W, V
+
+
+def obs_params_posterior(W, V, Gamma, sigmasq_C):
+    """gibbs.py:69-80 from the moments: S_xx[(a,i),(b,l)] (x) I_d, S_yx[((a,i),c)], then
+    Sigma_n = inv(I / sigmasq_C + S_xx), mu_n = Sigma_n S_yx."""
+    k, D1, d = V.shape
+    S4 = np.einsum('ji,jl,jab->aibl', Gamma, Gamma, W)                # (D+1, k-1, D+1, k-1)
+    S_xx = np.kron(S4.reshape(D1 * (k - 1), D1 * (k - 1)), np.eye(d))
+    S_yx = np.einsum('ji,jac->aic', Gamma, V).reshape(-1)
+    Sigma_n = np.linalg.inv(np.eye(d * D1 * (k - 1)) / sigmasq_C + S_xx)
+    return Sigma_n @ S_yx, Sigma_n
+
+
+def resample_obs_params(*, Y, mask, sigmasq, v, h, x, s, sigmasq_C, Gamma, w, **kwargs):
+    """gibbs.py:58-82 -> Cd ((k-1) d, D+1).  `w` (d (D+1) (k-1),) standard normals for
+    jr.multivariate_normal(key, mu_n, Sigma_n) = mu_n + cholesky(Sigma_n) @ w."""
+    k, d = Y.shape[-2:]
+    D = x.shape[-1]
+    W, V = obs_params_stats(Y=Y, mask=mask, sigmasq=sigmasq, v=v, h=h, x=x, s=s)
+    mu_n, Sigma_n = obs_params_posterior(W, V, Gamma, sigmasq_C)
+    draw = mu_n + np.linalg.cholesky(Sigma_n) @ w
+    return draw.reshape(D + 1, d * (k - 1)).T
+
+
 def resample_scales(*, x, v, h, Y, Cd, sigmasq, nu_s, s_0, Gamma, g, **kwargs):
     """gibbs.py:117-125.  `g` (N,T,k) ~ Gamma((nu_s+3)/2, 1).  No mask."""
     k, d = Y.shape[-2:]

@@ -91,6 +91,12 @@ def main():
                   mask=mask, x=x, z=z, nu_0=float(ar["nu_0"]), S_0=f(ar["S_0"]), M_0=f(ar["M_0"]), K_0=f(ar["K_0"]))
     out.update(d_ar_chi2=chi2, d_ar_normals=nrm, d_ar_G=Gm, r_ar_Ab=np.asarray(Abr), r_ar_Q=np.asarray(Qr))
 
+    # (f)1: observation matrix Cd (not part of the notebook's sweep; gibbs.py:58-82)
+    wc = rng.standard_normal(dk * (D + 1) * (k - 1))
+    Cdr = run({"mvn": wc}, G.resample_obs_params, Y=Y, mask=mask, sigmasq=sigmasq, v=v, h=h, x=x, s=s,
+              sigmasq_C=float(obs["sigmasq_C"]))
+    out.update(d_obsparams_w=wc, r_obsparams_Cd=np.asarray(Cdr))
+
     path = os.path.join(HERE, "reference_sweep.npz")
     np.savez_compressed(path, **{a: np.asarray(b) for a, b in out.items()})
     print("wrote", path, os.path.getsize(path), "bytes")

@@ -104,6 +104,13 @@ def test_oracle_ar_params_equal_reference():
     assert _rel(Ab, SW["r_ar_Ab"]) < 1e-10 and _rel(Q, SW["r_ar_Q"]) < 1e-10
 
 
+def test_oracle_obs_params_equals_reference():
+    Cd = O.resample_obs_params(Y=SW["Y"], mask=SW["mask"], sigmasq=SW["sigmasq"], v=SW["v"], h=SW["h"], x=SW["x"],
+                               s=SW["s"], sigmasq_C=float(SW["hyp_sigmasq_C"]), Gamma=O.center_embedding(k_),
+                               w=SW["d_obsparams_w"])
+    assert _rel(Cd, SW["r_obsparams_Cd"]) < 1e-11
+
+
 def _gpu_kw():
     import torch
     t = lambda a, dt: torch.as_tensor(np.ascontiguousarray(a), device="cuda").to(dt)
@@ -156,3 +163,31 @@ def test_cuda_steps_equal_reference():
                                         "G": t(SW["d_ar_G"], f64)})
     assert np.allclose(n(Q), SW["r_ar_Q"], rtol=1e-7, atol=1e-12)
     assert np.allclose(n(Ab), SW["r_ar_Ab"], rtol=1e-6, atol=1e-9)
+
+
+@pytest.mark.gpu
+def test_cuda_obs_params_equals_reference_and_oracle():
+    """SURVEY.md §8(f) rank 1: resample_obs_params (gibbs.py:58-82)."""
+    import torch
+    from keypointmoseq_b200 import gibbs as G
+    kw, t = _gpu_kw()
+    Cd = G.resample_obs_params(0, Y=kw["Y"], mask=kw["mask"], sigmasq=kw["sigmasq"], v=kw["v"], h=kw["h"],
+                               x=kw["x"], s=kw["s"], sigmasq_C=float(SW["hyp_sigmasq_C"]),
+                               draws={"w": t(SW["d_obsparams_w"], torch.float64)})
+    got = Cd.cpu().numpy()
+    assert got.shape == SW["r_obsparams_Cd"].shape
+    assert _rel(got, SW["r_obsparams_Cd"]) < 1e-9
+    # the moments themselves, at a larger size, against the oracle
+    from keypointmoseq_b200.synthetic import simulate
+    d, s, p, Gm = simulate(9, 3, 500, k=16, dk=2, D=10, L=3, K=6, ragged=True, dtype=np.float32)
+    f64 = lambda a: np.asarray(a, dtype=np.float64)
+    Wo, Vo = O.obs_params_stats(Y=f64(d["Y"]), mask=f64(d["mask"]), sigmasq=p["sigmasq"], v=f64(s["v"]),
+                                h=f64(s["h"]), x=f64(s["x"]), s=f64(s["s"]))
+    c = lambda a: torch.as_tensor(a, device="cuda")
+    W, V = G.obs_params_stats(Y=c(d["Y"]), mask=c(d["mask"]), sigmasq=c(p["sigmasq"]), v=c(s["v"]), h=c(s["h"]),
+                              x=c(s["x"]), s=c(s["s"]))
+    assert _rel(W.cpu().numpy(), Wo) < 1e-11 and _rel(V.cpu().numpy(), Vo) < 1e-11
+    # default RNG path: finite, right shape
+    Cd2 = G.resample_obs_params(3, Y=c(d["Y"]), mask=c(d["mask"]), sigmasq=c(p["sigmasq"]), v=c(s["v"]),
+                                h=c(s["h"]), x=c(s["x"]), s=c(s["s"]), sigmasq_C=0.1)
+    assert Cd2.shape == (15 * 2, 11) and torch.isfinite(Cd2).all()
