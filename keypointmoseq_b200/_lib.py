@@ -40,6 +40,8 @@ SIGNATURES = {
     "kpms_obs_variance_stats_workspace_bytes": (c_size_t, [c_int] * 3),
     "kpms_obs_variance_stats": (c_int, [P] * 7 + [c_int] * 5 + [P, P, P, c_size_t, P]),
     "kpms_obs_params_stats_workspace_bytes": (c_size_t, [c_int] * 5),
+    "kpms_log_joint_workspace_bytes": (c_size_t, []),
+    "kpms_log_joint": (c_int, [P] * 13 + [c_double] * 3 + [c_int] * 7 + [P, P, c_size_t, P]),
     "kpms_obs_params_stats": (c_int, [P] * 7 + [c_int] * 5 + [P, P, P, c_size_t, P]),
     "kpms_resample_scales": (c_int, [P] * 6 + [c_double, c_double, P] + [c_int] * 5 + [P, P]),
     "kpms_resample_heading": (c_int, [P] * 7 + [c_int] * 6 + [P, P, P, P]),

@@ -312,6 +312,155 @@ extern "C" int kpms_obs_params_stats(const float* Y, const float* mask, const fl
   return kpms_last_launch();
 }
 
+// ======================================================================== (f)2: log joint
+// Reference: util.py:232-275 (log_joint_likelihood): five masked sums over frames.  One thread
+// per frame evaluates its share of every term; per-CTA partials, fixed-order reduction.
+//   'Y': -1/2 |Ytild - Ybar|^2 / (s sigmasq) - dk/2 log(2 pi s sigmasq)       weight mask[t]
+//   'x': log N(x_t; Ab[z] [x_{t-L..t-1}; 1], Q[z])                            weight mask[t], t >= L
+//   'z': log pi[z_{t-L}, z_{t-L+1}]                                           weight mask[t+1], t >= L
+//   'v': -|v_t - v_{t+1}|^2 / (2 sigmasq_loc) - dk/2 log(2 pi sigmasq_loc)    weight mask[t+1]
+//   's': -nu_s s_0 / (2 s) - (1 + nu_s/2) log s                               weight mask[t]
+#define LJ_THREADS 256
+#define LJ_BLOCKS (148 * 4)
+
+extern "C" size_t kpms_log_joint_workspace_bytes(void) { return kpms_round_up((size_t)LJ_BLOCKS * 5 * sizeof(double), 256); }
+
+__global__ void __launch_bounds__(LJ_THREADS)
+    log_joint_kernel(const float* __restrict__ Y, const float* __restrict__ mask, const float* __restrict__ x,
+                     const float* __restrict__ s, const float* __restrict__ v, const float* __restrict__ h,
+                     const int* __restrict__ z, const double* __restrict__ pi, const double* __restrict__ Ab,
+                     const double* __restrict__ Qinv, const double* __restrict__ logdetQ,
+                     const double* __restrict__ Cdfull, const double* __restrict__ sigmasq, double sigmasq_loc,
+                     double nu_s, double s_0, ObsDims dm, int L, int K, double* __restrict__ partial) {
+  extern __shared__ __align__(16) double Cs[];
+  __shared__ double red[LJ_THREADS / 32][5];
+  const int k = dm.k, dk = dm.dk, D = dm.D, T = dm.T, Tm = T - L, P1 = D * L + 1;
+  double* sig = Cs + (size_t)k * dk * (D + 1);
+  load_cd(Cdfull, k * dk, D, Cs);
+  for (int i = threadIdx.x; i < k; i += blockDim.x) sig[i] = sigmasq[i];
+  __syncthreads();
+  double acc[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+  const double lv = -0.5 * (double)dk * log(2.0 * KPMS_PI * sigmasq_loc);
+  const long long frames = (long long)dm.N * T;
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < frames;
+       g += (long long)gridDim.x * blockDim.x) {
+    const int n = (int)(g / T), t = (int)(g % T);
+    const double m = (double)mask[g];
+    const double m1 = (t + 1 < T) ? (double)mask[g + 1] : 0.0;
+    if (m != 0.0) {
+      double xr[OBS_XMAX];
+      load_x(x, (size_t)g, D, xr);
+      double sn, cs;
+      sincos((double)h[g], &sn, &cs);
+      double vv[OBS_DKMAX];
+#pragma unroll
+      for (int dim = 0; dim < OBS_DKMAX; dim++) vv[dim] = (dim < dk) ? (double)v[g * dk + dim] : 0.0;
+      double aY = 0.0, aS = 0.0;
+      for (int kp = 0; kp < k; kp++) {
+        double yb[OBS_DKMAX], yt[OBS_DKMAX];
+        ybar_kp(Cs, kp, dk, D, xr, yb);
+        ytild_kp(Y + ((size_t)g * k + kp) * dk, vv, cs, sn, dk, yt);
+        double e = 0.0;
+#pragma unroll
+        for (int dim = 0; dim < OBS_DKMAX; dim++) {
+          const double r = yt[dim] - yb[dim];
+          e = fma(r, r, e);
+        }
+        const double sv = (double)s[(size_t)g * k + kp], R = sv * sig[kp];
+        aY += -0.5 * e / R - 0.5 * (double)dk * log(2.0 * KPMS_PI * R);
+        aS += -nu_s * s_0 / sv * 0.5 - (1.0 + 0.5 * nu_s) * log(sv);
+      }
+      acc[0] = fma(m, aY, acc[0]);
+      acc[4] = fma(m, aS, acc[4]);
+      if (t >= L) {
+        const int zt = z[(size_t)n * Tm + (t - L)];
+        const double* A = Ab + (size_t)zt * D * P1;
+        const float* win = x + ((size_t)n * T + (t - L)) * D;   // x[t-L .. t-1], oldest first
+        double d[OBS_XMAX];
+#pragma unroll
+        for (int a = 0; a < OBS_XMAX; a++) {
+          d[a] = 0.0;
+          if (a < D) {
+            double p = A[a * P1 + P1 - 1];
+            for (int q = 0; q < P1 - 1; q++) p = fma(A[a * P1 + q], (double)win[q], p);
+            d[a] = p - xr[a];
+          }
+        }
+        const double* Qi = Qinv + (size_t)zt * D * D;
+        double qf = 0.0;
+#pragma unroll
+        for (int a = 0; a < OBS_XMAX; a++)
+          if (a < D) {
+            double r = 0.0;
+#pragma unroll
+            for (int b = 0; b < OBS_XMAX; b++)
+              if (b < D) r = fma(Qi[a * D + b], d[b], r);
+            qf = fma(d[a], r, qf);
+          }
+        acc[1] = fma(m, -0.5 * qf - 0.5 * logdetQ[zt] - 0.5 * (double)D * KPMS_LOG_2PI, acc[1]);
+      }
+    }
+    if (m1 != 0.0) {
+      double d2 = 0.0;
+      for (int dim = 0; dim < dk; dim++) {
+        const double dd = (double)v[g * dk + dim] - (double)v[(g + 1) * dk + dim];
+        d2 = fma(dd, dd, d2);
+      }
+      acc[3] = fma(m1, -0.5 * d2 / sigmasq_loc + lv, acc[3]);
+      if (t >= L) {
+        const int za = z[(size_t)n * Tm + (t - L)], zb = z[(size_t)n * Tm + (t - L) + 1];
+        acc[2] = fma(m1, log(pi[(size_t)za * K + zb]), acc[2]);
+      }
+    }
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int i = 0; i < 5; i++) {
+    const double w = warp_sum_d(acc[i]);
+    if (lane == 0) red[warp][i] = w;
+  }
+  __syncthreads();
+  if (threadIdx.x < 5) {
+    double t = 0.0;
+    for (int q = 0; q < LJ_THREADS / 32; q++) t += red[q][threadIdx.x];
+    partial[(size_t)blockIdx.x * 5 + threadIdx.x] = t;
+  }
+}
+
+__global__ void log_joint_reduce_kernel(const double* __restrict__ partial, int blocks, double* __restrict__ out) {
+  const int i = threadIdx.x;
+  if (i >= 5) return;
+  double t = 0.0;
+  for (int b = 0; b < blocks; b++) t += partial[(size_t)b * 5 + i];
+  out[i] = t;
+}
+
+extern "C" int kpms_log_joint(const float* Y, const float* mask, const float* x, const float* s, const float* v,
+                              const float* h, const int32_t* z, const double* pi, const double* Ab,
+                              const double* Qinv, const double* logdetQ, const double* Cdfull,
+                              const double* sigmasq, double sigmasq_loc, double nu_s, double s_0, int N, int T,
+                              int k, int dk, int D, int L, int K, double* out5, void* workspace,
+                              size_t workspace_bytes, void* stream) {
+  KPMS_REQUIRE(Y && mask && x && s && v && h && z && pi && Ab && Qinv && logdetQ && Cdfull && sigmasq && out5 &&
+                   workspace,
+               KPMS_ERR_NULL);
+  int rc = obs_check(N, T, k, dk, D);
+  if (rc) return rc;
+  KPMS_REQUIRE(L > 0 && T > L && K > 0, KPMS_ERR_SHAPE);
+  KPMS_REQUIRE(kpms_aligned(workspace, 256) && workspace_bytes >= kpms_log_joint_workspace_bytes(),
+               KPMS_ERR_WORKSPACE);
+  cudaStream_t st = (cudaStream_t)stream;
+  ObsDims dm{N, T, k, dk, D};
+  const size_t smem = ((size_t)k * dk * (D + 1) + k) * sizeof(double);
+  log_joint_kernel<<<LJ_BLOCKS, LJ_THREADS, smem, st>>>(Y, mask, x, s, v, h, z, pi, Ab, Qinv, logdetQ, Cdfull,
+                                                       sigmasq, sigmasq_loc, nu_s, s_0, dm, L, K,
+                                                       (double*)workspace);
+  rc = kpms_last_launch();
+  if (rc) return rc;
+  log_joint_reduce_kernel<<<1, 32, 0, st>>>((const double*)workspace, LJ_BLOCKS, out5);
+  return kpms_last_launch();
+}
+
 // ======================================================================== a14
 __global__ void __launch_bounds__(256)
     scales_kernel(const float* __restrict__ Y, const float* __restrict__ v,

@@ -330,6 +330,42 @@ def obs_variance_stats(*, Y, mask, Cd, v, h, x, s, Gamma=None, **kwargs):
     return S_y, msum
 
 
+# ------------------------------------------------------------------------ (f)2: diagnostics
+def log_joint_likelihood(*, Y, mask, x, s, v, h, z, pi, Ab, Q, Cd, sigmasq, sigmasq_loc, nu_s, s_0,
+                         Gamma=None, **kwargs):
+    """util.py:266-275 -> dict {'Y','x','z','v','s'} of float64 scalars (device tensors)."""
+    lib = _lib.load()
+    Y = f32(Y)
+    dev = Y.device
+    N, T, k, dk = Y.shape
+    mask, x, s, v, h = f32(mask, dev), f32(x, dev), f32(s, dev), f32(v, dev), f32(h, dev)
+    z = i32(z, dev)
+    pi, Ab, Q, sigmasq = f64(pi, dev), f64(Ab, dev), f64(Q, dev), f64(sigmasq, dev)
+    K, D, L = _dims(Ab)
+    Cdfull = expand_Cd(f64(Cd, dev), _gamma(Gamma, k, dev), dk)
+    Qinv = torch.linalg.inv(Q).contiguous()                     # util.py:237-238
+    logdet = torch.linalg.slogdet(Q)[1].contiguous()
+    out = torch.empty((5,), dtype=torch.float64, device=dev)
+    ws = _lib.WORKSPACE.get("logjoint", lib.kpms_log_joint_workspace_bytes(), dev)
+    _lib.check(lib.kpms_log_joint(
+        _lib.ptr(Y), _lib.ptr(mask), _lib.ptr(x), _lib.ptr(s), _lib.ptr(v), _lib.ptr(h), _lib.ptr(z), _lib.ptr(pi),
+        _lib.ptr(Ab), _lib.ptr(Qinv), _lib.ptr(logdet), _lib.ptr(Cdfull), _lib.ptr(sigmasq), float(sigmasq_loc),
+        float(nu_s), float(s_0), N, T, k, dk, D, L, K, _lib.ptr(out), _lib.ptr(ws), ws.numel(),
+        _lib.stream_ptr(dev)), "kpms_log_joint")
+    return {name: out[i] for i, name in enumerate(("Y", "x", "z", "v", "s"))}
+
+
+def stateseq_stats(stateseqs, mask):
+    """util.py:41-45 -> (usage (max state + 1,), durations of the runs of the flattened unmasked
+    sequence), both int64 device tensors.  Index bookkeeping only (no kernel of its own)."""
+    z = stateseqs
+    m = mask[..., -z.shape[-1]:]
+    sq = z.reshape(-1)[m.reshape(-1) > 0].to(torch.int64)
+    usage = torch.bincount(sq)
+    durations = torch.unique_consecutive(sq, return_counts=True)[1]
+    return usage, durations
+
+
 # ------------------------------------------------------------------------ (f)1
 def obs_params_stats(*, Y, mask, sigmasq, v, h, x, s, **kwargs):
     """Per-keypoint weighted moments of gibbs.py:58-82 -> (W (k,D+1,D+1), V (k,D+1,dk)) float64."""

@@ -613,6 +613,41 @@ def resample_ar_params(*, nlags, num_states, mask, x, z, nu_0, S_0, M_0, K_0,
     return Ab, Q
 
 
+# ---- diagnostics ------------------------------------
+
+def log_joint_likelihood(*, Y, mask, x, s, v, h, z, pi, Ab, Q, Cd, sigmasq, sigmasq_loc, nu_s, s_0,
+                         Gamma, **kwargs):
+    """util.py:232-275 -> dict of the five masked log-probability sums 'Y','x','z','v','s'."""
+    k, d = Y.shape[-2:]
+    nlags = Ab.shape[2] // Ab.shape[1]
+    na = None
+    Ybar = expected_Ybar(x, Cd, Gamma, k, d)
+    sqerr = ((Y - affine_transform(Ybar, v, h)) ** 2).sum(-1)
+    lpY = -0.5 * sqerr / s / sigmasq - d / 2 * np.log(2 * s * sigmasq * np.pi)
+    Qinv, Qdet = np.linalg.inv(Q), np.linalg.det(Q)
+    x_pred = (Ab[z] @ pad_affine(get_lags(x, nlags))[..., na])[..., 0]
+    dd = x_pred - x[:, nlags:]
+    lpx = (-(dd[..., na, :] * Qinv[z] * dd[..., :, na]).sum((2, 3)) / 2
+           - np.log(Qdet[z]) / 2 - np.log(2 * np.pi) * Q.shape[-1] / 2)
+    lpz = np.log(pi[z[:, :-1], z[:, 1:]])
+    dv = v[:, :-1] - v[:, 1:]
+    lpv = -(dv ** 2).sum(-1) / sigmasq_loc / 2 - v.shape[-1] / 2 * np.log(sigmasq_loc * 2 * np.pi)
+    lps = -nu_s * s_0 / s / 2 - (1 + nu_s / 2) * np.log(s)
+    return {'Y': (lpY * mask[:, :, na]).sum(), 'x': (lpx * mask[:, nlags:]).sum(),
+            'z': (lpz * mask[:, nlags + 1:]).sum(), 'v': (lpv * mask[:, 1:]).sum(),
+            's': (lps * mask[:, :, na]).sum()}
+
+
+def stateseq_stats(stateseqs, mask):
+    """util.py:41-45 -> (usage = bincount of the unmasked states, durations = run lengths of the
+    flattened unmasked sequence)."""
+    sq = np.asarray(stateseqs).reshape(-1)[mask[..., -stateseqs.shape[-1]:].reshape(-1) > 0]
+    usage = np.bincount(sq)
+    change = np.flatnonzero(np.diff(sq)) + 1
+    edges = np.concatenate([[0], change, [sq.size]])
+    return usage, np.diff(edges)
+
+
 # ---- transitions.py ------------------------------------------------------------
 
 def sample_crp_tablecounts(concentration, customers, colweights, randseq):

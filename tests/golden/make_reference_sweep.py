@@ -97,6 +97,15 @@ def main():
               sigmasq_C=float(obs["sigmasq_C"]))
     out.update(d_obsparams_w=wc, r_obsparams_Cd=np.asarray(Cdr))
 
+    # (f)2: diagnostics (util.py:232-275, 41-45)
+    U = importlib.import_module("keypoint_moseq.util")
+    shim.Ctx.draws, shim.Ctx.vmap, shim.Ctx.scan_t = {}, [], None
+    lj = U.log_joint_likelihood(Y=Y, mask=mask, x=x, s=s, v=v, h=h, z=z, pi=pi, Ab=Ab, Q=Q, Cd=Cd, sigmasq=sigmasq,
+                                sigmasq_loc=float(loc["sigmasq_loc"]), nu_s=float(obs["nu_s"]), s_0=float(obs["s_0"]))
+    out["r_logjoint"] = np.array([float(lj[a]) for a in ("Y", "x", "z", "v", "s")])
+    usage, durations = U.stateseq_stats(np.asarray(z), np.asarray(mask))
+    out.update(r_usage=np.asarray(usage, dtype=np.int64), r_durations=np.asarray(durations, dtype=np.int64))
+
     path = os.path.join(HERE, "reference_sweep.npz")
     np.savez_compressed(path, **{a: np.asarray(b) for a, b in out.items()})
     print("wrote", path, os.path.getsize(path), "bytes")

@@ -111,6 +111,15 @@ def test_oracle_obs_params_equals_reference():
     assert _rel(Cd, SW["r_obsparams_Cd"]) < 1e-11
 
 
+def test_oracle_diagnostics_equal_reference():
+    lj = O.log_joint_likelihood(**_kw(), sigmasq_loc=float(SW["hyp_sigmasq_loc"]), nu_s=float(SW["hyp_nu_s"]),
+                                s_0=float(SW["hyp_s_0"]))
+    got = np.array([lj[a] for a in ("Y", "x", "z", "v", "s")])
+    assert np.all(np.abs(got - SW["r_logjoint"]) <= 1e-12 * np.abs(SW["r_logjoint"]))
+    usage, durations = O.stateseq_stats(SW["z"], SW["mask"])
+    assert np.array_equal(usage, SW["r_usage"]) and np.array_equal(durations, SW["r_durations"])
+
+
 def _gpu_kw():
     import torch
     t = lambda a, dt: torch.as_tensor(np.ascontiguousarray(a), device="cuda").to(dt)
@@ -191,3 +200,17 @@ def test_cuda_obs_params_equals_reference_and_oracle():
     Cd2 = G.resample_obs_params(3, Y=c(d["Y"]), mask=c(d["mask"]), sigmasq=c(p["sigmasq"]), v=c(s["v"]),
                                 h=c(s["h"]), x=c(s["x"]), s=c(s["s"]), sigmasq_C=0.1)
     assert Cd2.shape == (15 * 2, 11) and torch.isfinite(Cd2).all()
+
+
+@pytest.mark.gpu
+def test_cuda_diagnostics_equal_reference():
+    """SURVEY.md §8(f) rank 2: log_joint_likelihood (util.py:232-275) and stateseq_stats (util.py:41-45)."""
+    from keypointmoseq_b200 import gibbs as G
+    kw, t = _gpu_kw()
+    lj = G.log_joint_likelihood(**kw, sigmasq_loc=float(SW["hyp_sigmasq_loc"]), nu_s=float(SW["hyp_nu_s"]),
+                                s_0=float(SW["hyp_s_0"]))
+    got = np.array([float(lj[a]) for a in ("Y", "x", "z", "v", "s")])
+    assert np.all(np.abs(got - SW["r_logjoint"]) <= 1e-9 * np.abs(SW["r_logjoint"])), (got, SW["r_logjoint"])
+    usage, durations = G.stateseq_stats(kw["z"], kw["mask"])
+    assert np.array_equal(usage.cpu().numpy(), SW["r_usage"])
+    assert np.array_equal(durations.cpu().numpy(), SW["r_durations"])
