@@ -911,43 +911,37 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 3)
 // ------------------------------------------------------------------ backward sampler
 // One warp per session (or session chunk).  x_t = L (L^T h + w_t),
 // h = eta_c + A^T Qinv (x_{t+1} - B) with A^T Qinv = [100 E | F_D] (see file header).
+// The packed filter record of a step (lower-triangular L row by row, then eta_c) is copied
+// global -> shared with cp.async, one step ahead, and read IN PLACE: L[q][c] sits at
+// q(q+1)/2 + c, so "column c, all rows" is contiguous across lanes, and "row c" starts at the
+// triangular number c(c+1)/2, which hits sixteen distinct 8-byte banks for sixteen consecutive c.
 template <int NN, int DD>
 __global__ void __launch_bounds__(32)
     kalman_backward_kernel(const float* __restrict__ mask, const int* __restrict__ z,
                            const float* __restrict__ w, KalWs ws, int N, int T, int Lg,
                            int chunk_len, int burn_in, float* __restrict__ x_out) {
   using Y = KL<NN, DD>;
-  constexpr int NS = Y::NS, NTRI = Y::NTRI, OFF = NN - DD;
-  constexpr int PRE = (Y::FW_SIZE + 31) / 32;
+  constexpr int NTRI = Y::NTRI, OFF = NN - DD, FW = Y::FW_SIZE;
+  constexpr int NCP = (FW * 8 + 16 * 32 - 1) / (16 * 32);   // 16-byte pieces per lane and record
   extern __shared__ __align__(16) double sm[];
-  double* Lf = sm;             // NN*NS (lower)
-  double* hs = Lf + NN * NS;   // NN
+  double* rec = sm;            // 2 x FW: packed records, double-buffered
+  double* hs = rec + 2 * FW;   // NN
   double* ys = hs + NN;        // NN
   double* xs = ys + NN;        // NN
-  double* etas = xs + NN;      // NN
-  double* FDs = etas + NN;     // NN*DD
+  double* FDs = xs + NN;       // NN*DD
   double* bs = FDs + NN * DD;  // DD
-  unsigned char* ti = reinterpret_cast<unsigned char*>(bs + DD);
-  unsigned char* tj = ti + NTRI;
   const int lane = threadIdx.x;
   const int Tp = T - Lg + 1, Tt = Tp - 1;
   const int nch = kal_nchunks(Tt, chunk_len);
   const int n = blockIdx.x / nch, c = blockIdx.x % nch;
   const int t0 = (nch == 1) ? 0 : c * chunk_len;
   const int t1 = (nch == 1) ? Tt : min(Tt, t0 + chunk_len);
-  for (int e = lane; e < NTRI; e += 32) {
-    int i = 0;
-    while ((i + 1) * (i + 2) / 2 <= e) i++;
-    ti[e] = (unsigned char)i;
-    tj[e] = (unsigned char)(e - i * (i + 1) / 2);
-  }
-  for (int e = lane; e < NN * NS; e += 32) Lf[e] = 0.0;
   const float* mk = mask + (size_t)n * T + (Lg - 1);
   const int* zn = z + (size_t)n * Tt;
-  const double* fw_n = ws.fw + (size_t)n * Tp * Y::FW_SIZE;
+  const double* fw_n = ws.fw + (size_t)n * Tp * FW;
   const float* w_n = w + (size_t)n * Tt * NN;
   float* xo = x_out + (size_t)n * T * DD;
-  const double* xlast = fw_n + (size_t)(Tp - 1) * Y::FW_SIZE;
+  const double* xlast = fw_n + (size_t)(Tp - 1) * FW;
   int ts = t1;
   bool exact_start = true;
   if (c < nch - 1) {
@@ -956,44 +950,37 @@ __global__ void __launch_bounds__(32)
   }
   if (lane < NN) xs[lane] = exact_start ? xlast[lane] : 0.0;
   if (c == nch - 1 && lane < DD) xo[(size_t)(T - 1) * DD + lane] = (float)xlast[OFF + lane];
+  const unsigned rec_sa = (unsigned)__cvta_generic_to_shared(rec);
+  auto fetch = [&](int tau, int buf) {   // record of step tau -> buffer buf (asynchronous)
+    if (tau >= t0) {
+      const char* src = reinterpret_cast<const char*>(fw_n + (size_t)tau * FW);
+#pragma unroll
+      for (int i = 0; i < NCP; i++) {
+        const int piece = lane + 32 * i;
+        if (piece * 16 < FW * 8)
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(rec_sa + (unsigned)(buf * FW * 8 + piece * 16)),
+                       "l"(src + piece * 16));
+      }
+    }
+    asm volatile("cp.async.commit_group;\n" ::);
+  };
+  fetch(ts - 1, 0);
   __syncwarp();
   int cur_z = -1;
-  double pre[PRE];
-  float wpre = 0.0f;
-  {
-    const int tau = ts - 1;
-    if (tau >= t0) {
-#pragma unroll
-      for (int i = 0; i < PRE; i++) {
-        const int e = lane + 32 * i;
-        pre[i] = (e < Y::FW_SIZE) ? fw_n[(size_t)tau * Y::FW_SIZE + e] : 0.0;
-      }
-      if (lane < NN) wpre = w_n[(size_t)tau * NN + lane];
-    }
-  }
-  for (int tau = ts - 1; tau >= t0; tau--) {
+  float wpre = (ts - 1 >= t0 && lane < NN) ? w_n[(size_t)(ts - 1) * NN + lane] : 0.0f;
+  const int rowbase = lane * (lane + 1) / 2;
+  int buf = 0;
+  for (int tau = ts - 1; tau >= t0; tau--, buf ^= 1) {
     if (tau == t1 - 1 && c < nch - 1 && lane < NN)
       ws.bndx[((size_t)(n * nch + c) * 2 + 0) * NN + lane] = xs[lane];
     const bool live = mk[tau] > 0.0f;
-    // unpack this step's factor, then prefetch the next step's
-    if (live) {
-#pragma unroll
-      for (int i = 0; i < PRE; i++) {
-        const int e = lane + 32 * i;
-        if (e < NTRI) Lf[ti[e] * NS + tj[e]] = pre[i];
-        else if (e < NTRI + NN) etas[e - NTRI] = pre[i];
-      }
-    }
+    fetch(tau - 1, buf ^ 1);          // next step's record, one step ahead
     const float wcur = wpre;
-    if (tau - 1 >= t0) {
-#pragma unroll
-      for (int i = 0; i < PRE; i++) {
-        const int e = lane + 32 * i;
-        pre[i] = (e < Y::FW_SIZE) ? fw_n[(size_t)(tau - 1) * Y::FW_SIZE + e] : 0.0;
-      }
-      if (lane < NN) wpre = w_n[(size_t)(tau - 1) * NN + lane];
-    }
+    if (tau - 1 >= t0 && lane < NN) wpre = w_n[(size_t)(tau - 1) * NN + lane];
+    asm volatile("cp.async.wait_group 1;\n" ::);   // this step's record has landed
+    __syncwarp();
     if (live) {
+      const double* Pk = rec + buf * FW;
       const int zt = zn[tau];
       if (zt != cur_z) {
         const double* tb_ = ws.tab + (size_t)zt * Y::TAB_SIZE;
@@ -1003,7 +990,7 @@ __global__ void __launch_bounds__(32)
       }
       __syncwarp();
       if (lane < NN) {
-        double hh = etas[lane] + ((lane >= DD) ? 100.0 * xs[lane - DD] : 0.0);
+        double hh = Pk[NTRI + lane] + ((lane >= DD) ? 100.0 * xs[lane - DD] : 0.0);
 #pragma unroll
         for (int a = 0; a < DD; a++) hh = fma(FDs[lane * DD + a], xs[OFF + a] - bs[a], hh);
         hs[lane] = hh;
@@ -1013,8 +1000,8 @@ __global__ void __launch_bounds__(32)
         double t0a = 0.0, t1a = 0.0;
 #pragma unroll
         for (int q = 0; q < NN; q += 2) {
-          if (q >= lane) t0a = fma(Lf[q * NS + lane], hs[q], t0a);
-          if (q + 1 < NN && q + 1 >= lane) t1a = fma(Lf[(q + 1) * NS + lane], hs[q + 1], t1a);
+          if (q >= lane) t0a = fma(Pk[q * (q + 1) / 2 + lane], hs[q], t0a);
+          if (q + 1 < NN && q + 1 >= lane) t1a = fma(Pk[(q + 1) * (q + 2) / 2 + lane], hs[q + 1], t1a);
         }
         ys[lane] = (t0a + t1a) + (double)wcur;
       }
@@ -1024,12 +1011,13 @@ __global__ void __launch_bounds__(32)
         double a0 = 0.0, a1 = 0.0;
 #pragma unroll
         for (int q = 0; q < NN; q += 2) {
-          if (q <= lane) a0 = fma(Lf[lane * NS + q], ys[q], a0);
-          if (q + 1 < NN && q + 1 <= lane) a1 = fma(Lf[lane * NS + q + 1], ys[q + 1], a1);
+          if (q <= lane) a0 = fma(Pk[rowbase + q], ys[q], a0);
+          if (q + 1 < NN && q + 1 <= lane) a1 = fma(Pk[rowbase + q + 1], ys[q + 1], a1);
         }
         xn = a0 + a1;
-        xs[lane] = xn;
       }
+      __syncwarp();
+      if (lane < NN) xs[lane] = xn;
       __syncwarp();
     }
     if (tau < t1) {
@@ -1038,6 +1026,7 @@ __global__ void __launch_bounds__(32)
       if (tau == 0 && lane < OFF) xo[lane] = live ? (float)xs[lane] : 0.0f;
     }
   }
+  asm volatile("cp.async.wait_group 0;\n" ::);
   if (nch > 1 && c > 0 && lane < NN) ws.bndx[((size_t)(n * nch + c) * 2 + 1) * NN + lane] = xs[lane];
 }
 
@@ -1144,7 +1133,7 @@ static int launch_latents(const float* Y, const float* mask, const float* v, con
     if (rc) return rc;
   }
   {
-    const size_t smem = (size_t)(NN * YL::NS + 4 * NN + NN * DD + DD) * sizeof(double) + 2 * YL::NTRI;
+    const size_t smem = (size_t)(2 * YL::FW_SIZE + 3 * NN + NN * DD + DD) * sizeof(double);
     auto kern = kalman_backward_kernel<NN, DD>;
     KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<N * nch, 32, smem, st>>>(mask, z, w, ws, N, T, Lg, chunk_len, burn_in, x);
