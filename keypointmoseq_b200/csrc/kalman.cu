@@ -133,9 +133,13 @@ struct KW {  // packed per-state table + per-warp shared-memory layout of the wa
   }
   static constexpr int MSZ = ((moff(NN) > 32 * TS ? moff(NN) : 32 * TS) + 1) & ~1;
   static constexpr int TABS = (SIZE - FD + 1) & ~1;  // shared-memory part of the table (all but G)
+  // Scratch timeline of one step: [M rows] -> [dense T | packed L] -> [Z over both].
   static constexpr int SM_MS = 0;              // M rows (S2/S3), then the dense blocks of T
-  static constexpr int SM_LS = SM_MS + MSZ;    // rows of L, then Z
-  static constexpr int SM_TAB = SM_LS + 32 * RS;
+  static constexpr int SM_LS = SM_MS + MSZ;    // L packed by rows: L[q][r] at q(q+1)/2 + r
+  static constexpr int LPK = (NTRI + 1) & ~1;
+  static constexpr int ZSZ = (NN + 1) * RS;    // Z: rows 0..NN, row stride RS, starts at SM_MS
+  static constexpr int SCR = (MSZ + LPK > ZSZ ? MSZ + LPK : ZSZ);
+  static constexpr int SM_TAB = SM_MS + ((SCR + 1) & ~1);
   static constexpr int SM_DV = SM_TAB + TABS;
   static constexpr int SM_HV = SM_DV + 32;
   static constexpr int SM_TOTAL = SM_HV + 32;
@@ -603,7 +607,8 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 3)
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   double* S = sm + (size_t)wib * Wt::SM_TOTAL;
   double* Ms = S + Wt::SM_MS;   // rows of M, later rows of T
-  double* Ls = S + Wt::SM_LS;   // rows of L
+  double* Lk = S + Wt::SM_LS;   // L packed by rows
+  double* Zs = S + Wt::SM_MS;   // Z (after T and L are dead); scratch of the final section
   double* Tb = S + Wt::SM_TAB - Wt::FD;  // tables of the current state except G (indexed with the KW offsets)
   const double* Gg = ws.tabw;   // G of the current state is read from global memory (L1/L2 resident)
   double* dv = S + Wt::SM_DV;   // 1 / M[i][i]
@@ -727,7 +732,7 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 3)
     // rows of L to shared memory, eta_c - f for the mean column, L and eta_c to the workspace
 #pragma unroll
     for (int i = 0; i < NN; i++)
-      if (col) Ls[i * RS + c] = Lc[i];
+      if (c <= i) Lk[i * (i + 1) / 2 + c] = Lc[i];
     if (col) hv[c] = eta_c - Tb[Wt::F + c];
     if (store) {
       double* fwp = fw_n + (size_t)tau * Y::FW_SIZE;
@@ -774,7 +779,8 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 3)
 #pragma unroll
         for (int rb = 0; rb < RB; rb++) {
           if (kq < 2 * rb) continue;  // L is lower triangular: L[q][r] = 0 for q < r (8 rb <= r)
-          const double av = Ls[q * RS + 8 * rb + g];   // L[q][r]: rows >= NN and columns >= NN are zero
+          const int rr = 8 * rb + g;
+          const double av = (q < NN && rr <= q) ? Lk[q * (q + 1) / 2 + rr] : 0.0;   // L[q][r], lower triangular
 #pragma unroll
           for (int cb = 0; cb < NB - CB0; cb++)
             asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
@@ -799,7 +805,7 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 3)
 #pragma unroll
         for (int b = 0; b < NB; b++) {
           const int cf = 8 * b + g;
-          if (b < CB0) Tk[kq][b] = (kq <= tkmax(b)) ? 100.0 * Ls[(DD + cf) * RS + r] : 0.0;
+          if (b < CB0) Tk[kq][b] = (kq <= tkmax(b) && r <= DD + cf) ? 100.0 * Lk[(DD + cf) * (DD + cf + 1) / 2 + r] : 0.0;
           else Tk[kq][b] = Ms[r * Wt::TS + (cf - 8 * CB0)];
         }
       }
@@ -824,7 +830,8 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 3)
       for (int ib = 0; ib < NB; ib++)
 #pragma unroll
         for (int jb = 0; jb <= ib; jb++)
-          *reinterpret_cast<double2*>(Ls + (8 * ib + g) * RS + 8 * jb + 2 * qd) =
+          if (8 * ib + g <= NN)
+            *reinterpret_cast<double2*>(Zs + (8 * ib + g) * RS + 8 * jb + 2 * qd) =
               make_double2(Zacc[ib * (ib + 1) / 2 + jb][0], Zacc[ib * (ib + 1) / 2 + jb][1]);
       __syncwarp();
     }
@@ -834,16 +841,11 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 3)
       double qv;
       if (c < OFF) qv = (i == c) ? 100.0 : 0.0;
       else qv = (i >= OFF) ? Tb[Wt::QI + (i - OFF) * DD + ca] : 0.0;
-      Lp[i] = qv - ((i >= c && col) ? Ls[i * RS + c] : 0.0);
+      Lp[i] = qv - ((i >= c && col) ? Zs[i * RS + c] : 0.0);
     }
-    eta_p = ((c >= OFF) ? Tb[Wt::QB + ca] : 0.0) + (col ? Ls[NN * RS + c] : 0.0);
-    const double uu_z = Ls[NN * RS + NN];
+    eta_p = ((c >= OFF) ? Tb[Wt::QB + ca] : 0.0) + (col ? Zs[NN * RS + c] : 0.0);
+    const double uu_z = Zs[NN * RS + NN];
     __syncwarp();
-    // the buffer held Z: restore the zero padding the next step's operands rely on (row NN and
-    // column NN; rows / columns beyond are zero in Z already, and the rest is rewritten when L is
-    // published)
-    Ls[NN * RS + lane] = 0.0;
-    Ls[lane * RS + NN] = 0.0;
     if (want_ll && store) llacc += ct - 0.5 * Tb[Wt::SC + 1] + log(pd) + 0.5 * (uu_z - Tb[Wt::SC + 0]);
     __syncwarp();
   }
@@ -869,19 +871,19 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 3)
       const double piv = __shfl_sync(FULL, Wc[k], k);
       const double rs = rsqrt_pos(piv);
       const double m = Wc[k] * rs;
-      if (c <= k) Ls[k * RS + c] = m;
+      if (c <= k) Zs[k * RS + c] = m;
       if (c == 0) dv[k] = rs;
       pd *= rs;
       __syncwarp();
 #pragma unroll
-      for (int i = 0; i < k; i++) Wc[i] = fma(-Ls[k * RS + i], m, Wc[i]);
+      for (int i = 0; i < k; i++) Wc[i] = fma(-Zs[k * RS + i], m, Wc[i]);
     }
     double Lc[NN];
 #pragma unroll
     for (int i = 0; i < NN; i++) {
       double a0 = (i == c) ? 1.0 : 0.0;
 #pragma unroll
-      for (int q = 0; q < i; q++) a0 = fma(-Ls[i * RS + q], Lc[q], a0);
+      for (int q = 0; q < i; q++) a0 = fma(-Zs[i * RS + q], Lc[q], a0);
       Lc[i] = a0 * dv[i];
     }
     if (col) hv[c] = eta_c;
