@@ -14,7 +14,7 @@
 //
 // UMMA K-major no-swizzle layout (16-byte units): element (row r, k) lives at
 //   (r / 8) * SBO + (k / 4) * LBO + (r % 8) * 16 + (k % 4) * 4   bytes,  LBO = 128, SBO = (KD/4)*128.
-#include "common.cuh"
+#include "tc_common.cuh"
 #include "dispatch.cuh"
 
 #define TC_STATES 16   // states per weight tile
@@ -35,21 +35,6 @@ struct TC {
                                     ((uint32_t)(TC_M >> 4) << 24);  // F32 accum, TF32 x TF32, K-major both
   static_assert(N % 16 == 0 && N <= 256, "invalid UMMA N");
 };
-
-__device__ __forceinline__ uint32_t tf32_rna(float v) {
-  uint32_t u;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v));
-  return u;
-}
-
-__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
-  uint64_t d = 0;
-  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
-  d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
-  d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
-  d |= (uint64_t)1 << 46;  // descriptor version (Blackwell)
-  return d;                 // base offset 0, layout type 0 = no swizzle
-}
 
 // Pack the fp32 whitened weights into per-tile hi / lo TF32 operands in the UMMA layout.
 template <int DD, int LL>

@@ -6,11 +6,13 @@
 // session into chunks with a warm-up (hmm_ffbs.cu) yields thousands of independent chains, and 128
 // chains stepping in lock-step make the per-frame work a real GEMM:
 //     T (128 chains x K) = A (128 x K: the chains' current messages a) @ pi (K x K)
-// Kernel hmm_forward_tc: one CTA = 128 chains, one thread = one chain.  pi (hi / lo TF32 parts)
-// stays resident in shared memory in the UMMA K-major layout; per frame the thread reads T of its
-// chain from TMEM, multiplies by exp(ll - rowmax), accumulates the normaliser and the marginal
-// log-likelihood, writes the message (global, for the backward sampler) and its hi / lo split
-// (shared, next A operand), then one elected thread issues 3 x KD/8 tcgen05.mma.
+// Kernel hmm_forward_tc: one CTA = 128 chains, 512 threads: thread = (chain, quarter of the states).
+// pi (hi / lo TF32 parts) stays resident in shared memory in the UMMA K-major layout; per frame a
+// thread reads its part of T from TMEM, multiplies by exp(ll - row max) (row max and normaliser are
+// exchanged between the four parts through shared memory), accumulates the marginal log-likelihood,
+// writes the message (global, interleaved layout, for the sampler) and its hi / lo split (shared,
+// next A operand), then one elected thread issues 3 x KD/8 tcgen05.mma.  ll is prefetched two
+// frames ahead, while the tensor core works.
 // Kernel hmm_stay_tc (frame-parallel): P = a @ pi_su (pi_su[i][j] = pi[i][j] for i < j) and the
 // "stay" bits  P_j <= u T_j < P_j + a_j pi[j][j]  that let the backward sampler skip runs.
 // Messages are stored unnormalised (a, and T = a @ pi in the same units): every consumer only
@@ -21,7 +23,6 @@
 
 struct HmmTcArgs {
   const float* ll;
-  const float* rowmax;
   const double* pi;
   const float* u;
   const int* tv;
@@ -43,18 +44,6 @@ struct HTC {
   static constexpr uint32_t IDESC = umma_idesc_tf32_m128(NP);
   static constexpr size_t SMEM = 1024 + 2 * A_BYTES + 2 * B_BYTES + 256;
 };
-
-// max_j ll[row][j] for every frame row (one warp per row)
-__global__ void hmm_rowmax_kernel(const float* __restrict__ ll, long long rows, int K,
-                                  float* __restrict__ rowmax) {
-  const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (row >= rows) return;
-  const int lane = threadIdx.x & 31;
-  float m = -INFINITY;
-  for (int j = lane; j < K; j += 32) m = fmaxf(m, ll[row * K + j]);
-  m = warp_max_f(m);
-  if (lane == 0) rowmax[row] = m;
-}
 
 // flag (as +1e30 in err[0]) sessions whose mask is not of the form  t < tv[n]
 __global__ void hmm_mask_check_kernel(const float* __restrict__ mask, long long mask_stride, int Tm,
@@ -572,7 +561,7 @@ int kpms_hmm_forward_tc(const float* ll, int ll_tiled, float* ll_scratch, const 
     if (rc) return rc;
     ll = ll_scratch;
   }
-  HmmTcArgs a{ll, nullptr, pi, u, tv, a_out, T_out, stay, llpart, bnd, N, Tm, K, chunk_len, burn_in, nch};
+  HmmTcArgs a{ll, pi, u, tv, a_out, T_out, stay, llpart, bnd, N, Tm, K, chunk_len, burn_in, nch};
   if (K <= 32) return launch_hmm_tc<32, 32>(a, st);
   if (K <= 64) return launch_hmm_tc<64, 64>(a, st);
   return launch_hmm_tc<104, 112>(a, st);

@@ -493,3 +493,29 @@ def test_hmm_backward_chunks_are_repaired(G, monkeypatch):
     zo, lo = O._hmm_batch(ll, mask, pi, u)
     valid = mask > 0
     assert (N_(z_rep)[valid] == zo[valid]).mean() >= 0.999
+
+
+def test_alternative_kernel_paths_agree(G, monkeypatch):
+    """The kernels kept behind environment switches stay correct: KPMS_KALMAN_IMPL=0 (CTA-per-chunk
+    shared-memory Kalman filter) and KPMS_HMM_TC=0 (CUDA-core chunked HMM filter)."""
+    import torch
+    d, s, p, Gm = H.problem(seed=61, N=3, T=700, k=8, dk=2, D=10, L=3, K=8, ragged=True)
+    rng = np.random.default_rng(3)
+    w, wl = H.f32r(rng.standard_normal((3, 697, 30))), H.f32r(rng.standard_normal((3, 30)))
+    kw = dict(Y=T_(d['Y']), mask=T_(d['mask']), v=T_(s['v']), h=T_(s['h']), z=T_(s['z']), s=T_(s['s']),
+              Cd=T_(p['Cd']), sigmasq=T_(p['sigmasq']), Ab=T_(p['Ab']), Q=T_(p['Q']), Gamma=T_(Gm),
+              draws={'w': T_(w), 'w_last': T_(wl)}, chunk_len=128, burn_in=160, strict=False)
+    x0 = G.resample_latents(0, **kw)
+    monkeypatch.setenv("KPMS_KALMAN_IMPL", "0")
+    x1 = G.resample_latents(0, **kw)
+    monkeypatch.delenv("KPMS_KALMAN_IMPL")
+    assert float((x0 - x1).abs().max()) < 1e-5 * max(1.0, float(x0.abs().max()))
+    ll, mask, pi, u = _hmm_case(31, N=4, T=2400, K=40, ragged=True)
+    hk = dict(ll=T_(ll), mask=T_(mask), pi=T_(pi), u=T_(u), chunk_len=300, burn_in=256, strict=False, return_info=True)
+    z0, l0, _ = G.sample_hmm_stateseqs(**hk)
+    monkeypatch.setenv("KPMS_HMM_TC", "0")
+    z1, l1, i1 = G.sample_hmm_stateseqs(**hk)
+    torch.cuda.synchronize()
+    assert float(i1['boundary_err']) < 1e-5
+    assert float((z0 != z1).float().mean()) < 1e-3
+    assert np.all(np.abs(N_(l0) - N_(l1)) <= 1e-5 * np.abs(N_(l0)))
