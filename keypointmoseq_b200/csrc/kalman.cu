@@ -581,7 +581,8 @@ __global__ void __launch_bounds__(KAL_NT, 1)
 //   T = L^T [F | eta_c - f]                  (lane c: column c of F; lane NN: the mean column)
 //   Lam_p' = Qinv_ - T^T T, eta_p' = qb_ + T^T u      (rows of T published, broadcast back)
 // ~4.2 k warp instructions per step, of which ~2.1 k are DFMA; eight such warps per SM.
-#define KW_WARPS 4
+#define KW_WARPS 12
+#define KW_LOCKSTEP 1
 
 // 1/sqrt(x) for the pivots of an SPD matrix (x > 0, normal): hardware seed (2^-22) and one
 // third-order correction, without rsqrt()'s special-case handling.
@@ -594,7 +595,7 @@ __device__ __forceinline__ double rsqrt_pos(double x) {
 }
 
 template <int NN, int DD>
-__global__ void __launch_bounds__(KW_WARPS * 32, 3)
+__global__ void __launch_bounds__(KW_WARPS * 32, 1)
     kalman_forward_warp_kernel(const float* __restrict__ mask, const int* __restrict__ z,
                                const float* __restrict__ w_last, KalWs ws, int N, int T, int Lg,
                                int chunk_len, int burn_in, int want_ll) {
@@ -615,13 +616,15 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 3)
   double* hv = S + Wt::SM_HV;   // eta_c - f  (then scratch)
   const int Tp = T - Lg + 1, Tt = Tp - 1;
   const int nch = kal_nchunks(Tt, chunk_len);
-  const int unit = blockIdx.x * KW_WARPS + wib;
-  if (unit >= N * nch) return;  // whole warp leaves; the kernel has no block-wide barrier
+  const int unit0 = blockIdx.x * KW_WARPS + wib;
+  const bool has_unit = unit0 < N * nch;
+  const int unit = has_unit ? unit0 : 0;
   const int n = unit / nch, cc = unit % nch;
   const int t0 = (nch == 1) ? 0 : cc * chunk_len;
-  const int t1 = (nch == 1) ? Tt : min(Tt, t0 + chunk_len);
+  int t1 = (nch == 1) ? Tt : min(Tt, t0 + chunk_len);
   int tb = 0;
   if (cc > 0) tb = max(0, min(t0, ws.tv[n]) - burn_in);
+  if (!has_unit) t1 = tb;
   const int c = lane;
   const bool col = c < NN;
   const int ca = min(max(c - OFF, 0), DD - 1);  // clamped index into the D-blocks
@@ -652,7 +655,17 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 3)
   float mk_next = mk[tb];
   int z_next = (tb < Tt) ? zn[tb] : 0;
 
-  for (int tau = tb; tau < t1; tau++) {
+  // every warp of the CTA takes the same number of trips (the longest chain's)
+  __shared__ int maxit_s;
+  if (threadIdx.x == 0) maxit_s = 0;
+  __syncthreads();
+  if (lane == 0) atomicMax(&maxit_s, t1 - tb);
+  __syncthreads();
+  const int maxit = maxit_s;
+  for (int it = 0; it < maxit; it++) {
+    __syncthreads();   // keeps the warps that share a scheduler on the same code (instruction cache)
+    const int tau = tb + it;
+    if (tau >= t1) continue;
     if (tau == t0 && cc > 0) {
       double* bd = ws.bndf + ((size_t)(n * nch + cc) * 2 + 0) * Y::BND;
 #pragma unroll
@@ -849,6 +862,7 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 3)
     if (want_ll && store) llacc += ct - 0.5 * Tb[Wt::SC + 1] + log(pd) + 0.5 * (uu_z - Tb[Wt::SC + 0]);
     __syncwarp();
   }
+  if (!has_unit) return;
   if (nch > 1) {
     double* bd = ws.bndf + ((size_t)(n * nch + cc) * 2 + 1) * Y::BND;
 #pragma unroll
