@@ -19,6 +19,7 @@
 
 #define TC_STATES 16   // states per weight tile
 #define TC_M 128       // frames per block (UMMA M)
+#define TC_THREADS 256 // thread = (frame row, half of the K chunks / half of the states)
 
 template <int DD, int LL>
 struct TC {
@@ -55,7 +56,7 @@ __global__ void ar_tc_pack_kernel(const float* __restrict__ Wf, int K, unsigned 
 }
 
 template <int DD, int LL>
-__global__ void __launch_bounds__(TC_M, 1)
+__global__ void __launch_bounds__(TC_THREADS)
     ar_loglik_tc_kernel(const float* __restrict__ x, const unsigned char* __restrict__ tiles,
                         const float* __restrict__ cst, int N, int T, int K, int nstripes,
                         int tile_cl, int tile_nch, float* __restrict__ ll) {
@@ -69,6 +70,7 @@ __global__ void __launch_bounds__(TC_M, 1)
   uint64_t* mbar = reinterpret_cast<uint64_t*>(s_cst + TC_STATES);                // 8-byte aligned
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mbar + 1);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int row = tid & (TC_M - 1), half = tid >> 7;
   const int tile = blockIdx.x, stripe = blockIdx.y;
   const int k0 = tile * TC_STATES;
   const int Tm = T - LL;
@@ -82,7 +84,7 @@ __global__ void __launch_bounds__(TC_M, 1)
   {
     const uint4* src = reinterpret_cast<const uint4*>(tiles + (size_t)tile * 2 * C::B_BYTES);
     uint4* dst = reinterpret_cast<uint4*>(sB_hi);
-    for (int i = tid; i < 2 * C::B_BYTES / 16; i += TC_M) dst[i] = src[i];
+    for (int i = tid; i < 2 * C::B_BYTES / 16; i += TC_THREADS) dst[i] = src[i];
     if (tid < TC_STATES) s_cst[tid] = (k0 + tid < K) ? cst[k0 + tid] : 0.0f;
   }
   const uint32_t mbar_sa = (uint32_t)__cvta_generic_to_shared(mbar);
@@ -108,14 +110,14 @@ __global__ void __launch_bounds__(TC_M, 1)
 
   for (long long blk = stripe; blk < nblk; blk += nstripes) {
     // ---- A tile: thread r builds row r = frame blk*128 + r (hi and lo parts)
-    long long g = blk * TC_M + tid;
+    long long g = blk * TC_M + row;
     bool live = g < frames;
     {
       const float* xp = x;
       if (tile_cl > 0) {
         const long long b = blk / tile_cl;
         const int r = (int)(blk - b * tile_cl);
-        const long long uu = b * 128 + tid;
+        const long long uu = b * 128 + row;
         live = false;
         if (uu < units) {
           const int n = (int)(uu / tile_nch), cc = (int)(uu % tile_nch);
@@ -129,18 +131,29 @@ __global__ void __launch_bounds__(TC_M, 1)
         const int n = (int)(g / Tm), tp = (int)(g % Tm);
         xp = x + ((size_t)n * T + tp) * DD;  // lag window x[tp .. tp+L]: DL+DD contiguous floats
       }
-      const size_t rowoff = (size_t)(tid / 8) * C::SBO + (tid % 8) * 16;
+      const size_t rowoff = (size_t)(row / 8) * C::SBO + (row % 8) * 16;
 #pragma unroll
       for (int kc = 0; kc < C::KC; kc++) {
+        if ((kc & 1) != half) continue;   // the two threads of a row share the chunks
         uint32_t hi[4], lo[4];
+        float v4[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        if (live) {
+          if ((DD & 1) == 0 && kc * 4 + 3 < DD * LL + DD) {   // windows start on 8-byte boundaries when D is even
+            const float2 a = __ldg(reinterpret_cast<const float2*>(xp + kc * 4));
+            const float2 b = __ldg(reinterpret_cast<const float2*>(xp + kc * 4 + 2));
+            v4[0] = a.x; v4[1] = a.y; v4[2] = b.x; v4[3] = b.y;
+          } else {
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+              const int p = kc * 4 + q;
+              if (p < DD * LL + DD) v4[q] = xp[p];
+              else if (p == C::P - 1) v4[q] = 1.0f;
+            }
+          }
+        }
 #pragma unroll
         for (int q = 0; q < 4; q++) {
-          const int p = kc * 4 + q;
-          float v = 0.0f;
-          if (live) {
-            if (p < DD * LL + DD) v = xp[p];
-            else if (p == C::P - 1) v = 1.0f;
-          }
+          const float v = v4[q];
           hi[q] = tf32_rna(v);
           lo[q] = tf32_rna(v - __uint_as_float(hi[q]));
         }
@@ -188,47 +201,47 @@ __global__ void __launch_bounds__(TC_M, 1)
     asm volatile("tcgen05.fence::after_thread_sync;\n" ::);
     // ---- epilogue: thread = frame row; warp w reads TMEM lanes 32w..32w+31
     {
-      float q[TC_STATES];
+      // epilogue: thread = (frame row, half): states 8*half .. 8*half+7 of the tile, i.e. TMEM
+      // columns [8*half*DD, 8*(half+1)*DD); warp w reads TMEM lanes 32*(w%4) .. +31
+      constexpr int HS = TC_STATES / 2, HC = HS * DD, W = (HC % 16 == 0) ? 16 : 8;
+      float q[HS];
 #pragma unroll
-      for (int sidx = 0; sidx < TC_STATES; sidx++) q[sidx] = 0.0f;
-      const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16);
+      for (int sidx = 0; sidx < HS; sidx++) q[sidx] = 0.0f;
+      const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(half * HC);
 #pragma unroll
-      for (int c0 = 0; c0 < C::N; c0 += 16) {
+      for (int c0 = 0; c0 < HC; c0 += W) {
         uint32_t r[16];
-        asm volatile(
-            "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, "
-            "%13, %14, %15}, [%16];\n"
-            : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-              "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-            : "r"(taddr + (uint32_t)c0));
-        asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::);
+        if (W == 16) tmem_ld16(taddr + (uint32_t)c0, r);
+        else tmem_ld8(taddr + (uint32_t)c0, r);
 #pragma unroll
-        for (int i = 0; i < 16; i++) {
+        for (int i = 0; i < W; i++) {
           const float v = __uint_as_float(r[i]);
           q[(c0 + i) / DD] = fmaf(v, v, q[(c0 + i) / DD]);
         }
       }
+      const int ks = k0 + half * HS;
+      const float* cs = s_cst + half * HS;
       if (live && tile_cl > 0) {
         // interleaved layout: float4 index (blk * K/4 + kc) * 128 + row  (K % 4 == 0 guaranteed by the caller)
-        float4* out4 = reinterpret_cast<float4*>(ll) + ((size_t)blk * (K >> 2) + (k0 >> 2)) * 128 + tid;
+        float4* out4 = reinterpret_cast<float4*>(ll) + ((size_t)blk * (K >> 2) + (ks >> 2)) * 128 + row;
 #pragma unroll
-        for (int s4 = 0; s4 < TC_STATES; s4 += 4)
-          if (k0 + s4 < K)
+        for (int s4 = 0; s4 < HS; s4 += 4)
+          if (ks + s4 < K)
             out4[(size_t)(s4 >> 2) * 128] =
-                make_float4(s_cst[s4] - 0.5f * q[s4], s_cst[s4 + 1] - 0.5f * q[s4 + 1],
-                            s_cst[s4 + 2] - 0.5f * q[s4 + 2], s_cst[s4 + 3] - 0.5f * q[s4 + 3]);
+                make_float4(cs[s4] - 0.5f * q[s4], cs[s4 + 1] - 0.5f * q[s4 + 1],
+                            cs[s4 + 2] - 0.5f * q[s4 + 2], cs[s4 + 3] - 0.5f * q[s4 + 3]);
       } else if (live) {
-        float* out = ll + g * K + k0;
-        if ((K & 3) == 0 && k0 + TC_STATES <= K) {
+        float* out = ll + g * K + ks;
+        if ((K & 3) == 0 && ks + HS <= K) {
 #pragma unroll
-          for (int s4 = 0; s4 < TC_STATES; s4 += 4)
+          for (int s4 = 0; s4 < HS; s4 += 4)
             *reinterpret_cast<float4*>(out + s4) =
-                make_float4(s_cst[s4] - 0.5f * q[s4], s_cst[s4 + 1] - 0.5f * q[s4 + 1],
-                            s_cst[s4 + 2] - 0.5f * q[s4 + 2], s_cst[s4 + 3] - 0.5f * q[s4 + 3]);
+                make_float4(cs[s4] - 0.5f * q[s4], cs[s4 + 1] - 0.5f * q[s4 + 1],
+                            cs[s4 + 2] - 0.5f * q[s4 + 2], cs[s4 + 3] - 0.5f * q[s4 + 3]);
         } else {
 #pragma unroll
-          for (int sidx = 0; sidx < TC_STATES; sidx++)
-            if (k0 + sidx < K) out[sidx] = s_cst[sidx] - 0.5f * q[sidx];
+          for (int sidx = 0; sidx < HS; sidx++)
+            if (ks + sidx < K) out[sidx] = cs[sidx] - 0.5f * q[sidx];
         }
       }
     }
@@ -265,7 +278,7 @@ static int launch_tc(const float* x, const float* Wf, const float* cst, int N, i
   if (stripes < 1) stripes = 1;
   if (stripes > nblk) stripes = nblk;
   if (ntiles > 65535) return KPMS_ERR_UNSUPPORTED;
-  kern<<<dim3(ntiles, (unsigned)stripes), TC_M, smem, st>>>(x, tiles, cst, N, T, K, (int)stripes, tile_cl, tile_nch, ll);
+  kern<<<dim3(ntiles, (unsigned)stripes), TC_THREADS, smem, st>>>(x, tiles, cst, N, T, K, (int)stripes, tile_cl, tile_nch, ll);
   return kpms_last_launch();
 }
 
