@@ -96,13 +96,51 @@ def ar_log_likelihood(*, x, Ab, Q, impl=0, **kwargs):
     return ll
 
 
+# Adaptive warm-up of the chunked HMM passes: how fast the filter forgets depends on the current
+# parameters (slowly early in a fit, when the states are hardly distinguishable).  A failed boundary
+# check doubles the warm-up for this and the following calls; a run of comfortable passes halves it
+# again.  `boost` multiplies the configured burn_in.
+_HMM_ADAPT = {"boost": 1, "streak": 0}
+HMM_MAX_BOOST = 16
+
+
+def _run_hmm_adaptive(run, berr, chunk_len, burn_in, strict, adaptive):
+    """run(chunk_len, burn_in) launches one chunked pass and fills `berr`."""
+    tol = STATESEQ_CHUNKING["tol"]
+    if chunk_len <= 0 or not strict:
+        run(chunk_len, burn_in if chunk_len > 0 else 0)
+        return
+    boost = _HMM_ADAPT["boost"] if adaptive else 1
+    while True:
+        run(chunk_len, burn_in if boost == 1 else max(burn_in, 32) * boost)
+        b = float(berr)
+        if b <= tol:
+            if adaptive:
+                _HMM_ADAPT["streak"] = _HMM_ADAPT["streak"] + 1 if b <= 0.03 * tol else 0
+                if _HMM_ADAPT["streak"] >= 8 and _HMM_ADAPT["boost"] > 1:
+                    _HMM_ADAPT["boost"] //= 2
+                    _HMM_ADAPT["streak"] = 0
+            return
+        FALLBACKS["stateseqs"] += 1
+        FALLBACKS.setdefault("stateseqs_berr", []).append(b)
+        del FALLBACKS["stateseqs_berr"][:-8]
+        boost *= 2
+        if b > 1e29 or boost > HMM_MAX_BOOST:     # 1e30 flags a mask that is not trailing padding
+            FALLBACKS["stateseqs_exact"] = FALLBACKS.get("stateseqs_exact", 0) + 1
+            run(0, 0)
+            return
+        if adaptive:
+            _HMM_ADAPT["boost"], _HMM_ADAPT["streak"] = boost, 0
+
+
 def _hmm_chunking(N, Tm, K, chunk_len, burn_in, strict, dev):
     chunk_len = STATESEQ_CHUNKING["chunk_len"] if chunk_len is None else chunk_len
     burn_in = STATESEQ_CHUNKING["burn_in"] if burn_in is None else burn_in
     strict = STATESEQ_CHUNKING["strict"] if strict is None else strict
-    if chunk_len == "auto":
+    auto = chunk_len == "auto"
+    if auto:
         chunk_len = auto_hmm_chunk_len(N, Tm, K, int(burn_in), dev) if K <= 128 else 0
-    return int(chunk_len), int(burn_in), bool(strict)
+    return int(chunk_len), int(burn_in), bool(strict), auto
 
 
 def sample_hmm_stateseqs(*, ll, mask, pi, u, chunk_len=None, burn_in=None, strict=None, return_info=False):
@@ -113,7 +151,7 @@ def sample_hmm_stateseqs(*, ll, mask, pi, u, chunk_len=None, burn_in=None, stric
     dev = ll.device
     N, Tm, K = ll.shape
     mask, pi, u = f32(mask, dev), f64(pi, dev), f32(u, dev)
-    chunk_len, burn_in, strict = _hmm_chunking(N, Tm, K, chunk_len, burn_in, strict, dev)
+    chunk_len, burn_in, strict, auto = _hmm_chunking(N, Tm, K, chunk_len, burn_in, strict, dev)
     z = torch.empty((N, Tm), dtype=torch.int32, device=dev)
     loglik = torch.empty((N,), dtype=torch.float64, device=dev)
     berr = torch.zeros((1,), dtype=torch.float32, device=dev)
@@ -124,21 +162,7 @@ def sample_hmm_stateseqs(*, ll, mask, pi, u, chunk_len=None, burn_in=None, stric
                                      bi, _lib.ptr(z), _lib.ptr(loglik), _lib.ptr(berr), _lib.ptr(ws),
                                      ws.numel(), _lib.stream_ptr(dev)), "kpms_hmm_ffbs")
 
-    run(chunk_len, burn_in)
-    if chunk_len > 0 and strict and float(berr) > STATESEQ_CHUNKING["tol"]:
-        # warm-up too short for this model: once more with four times the warm-up, then exactly
-        FALLBACKS["stateseqs"] += 1
-        FALLBACKS.setdefault("stateseqs_berr", []).append(float(berr))
-        del FALLBACKS["stateseqs_berr"][:-8]
-        burn2 = 4 * max(burn_in, 64)
-        cl2 = auto_hmm_chunk_len(N, Tm, K, burn2, dev)
-        ok = False
-        if cl2 > 0 and float(berr) < 1e29:    # 1e30 flags a mask that is not trailing padding
-            run(cl2, burn2)
-            ok = float(berr) <= STATESEQ_CHUNKING["tol"]
-        if not ok:
-            FALLBACKS["stateseqs_exact"] = FALLBACKS.get("stateseqs_exact", 0) + 1
-            run(0, 0)
+    _run_hmm_adaptive(run, berr, chunk_len, burn_in, strict, auto)
     last_stateseq_boundary_err = berr
     if return_info:
         return z, loglik, {"boundary_err": berr}
@@ -159,7 +183,7 @@ def resample_stateseqs(key, *, x, mask, Ab, Q, pi, draws=None, impl=0, chunk_len
         u = f32(draws["u"], dev)
     else:
         u = dist.fill_uniform((N, T - L), dist.seed_of(key), dist.STREAM_Z, dev)
-    chunk_len, burn_in, strict = _hmm_chunking(N, T - L, K, chunk_len, burn_in, strict, dev)
+    chunk_len, burn_in, strict, auto = _hmm_chunking(N, T - L, K, chunk_len, burn_in, strict, dev)
     z = torch.empty((N, T - L), dtype=torch.int32, device=dev)
     loglik = torch.empty((N,), dtype=torch.float64, device=dev)
     berr = torch.zeros((1,), dtype=torch.float32, device=dev)
@@ -173,21 +197,7 @@ def resample_stateseqs(key, *, x, mask, Ab, Q, pi, draws=None, impl=0, chunk_len
             cl, bi, _lib.ptr(z), _lib.ptr(loglik), _lib.ptr(berr), _lib.ptr(ws), ws.numel(), int(impl),
             _lib.stream_ptr(dev)), "kpms_resample_stateseqs")
 
-    run(chunk_len, burn_in)
-    if chunk_len > 0 and strict and float(berr) > STATESEQ_CHUNKING["tol"]:
-        # warm-up too short for this model: once more with four times the warm-up, then exactly
-        FALLBACKS["stateseqs"] += 1
-        FALLBACKS.setdefault("stateseqs_berr", []).append(float(berr))
-        del FALLBACKS["stateseqs_berr"][:-8]
-        burn2 = 4 * max(burn_in, 64)
-        cl2 = auto_hmm_chunk_len(N, Tm, K, burn2, dev)
-        ok = False
-        if cl2 > 0 and float(berr) < 1e29:    # 1e30 flags a mask that is not trailing padding
-            run(cl2, burn2)
-            ok = float(berr) <= STATESEQ_CHUNKING["tol"]
-        if not ok:
-            FALLBACKS["stateseqs_exact"] = FALLBACKS.get("stateseqs_exact", 0) + 1
-            run(0, 0)
+    _run_hmm_adaptive(run, berr, chunk_len, burn_in, strict, auto)
     last_stateseq_boundary_err = berr
     return z, loglik
 
