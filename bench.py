@@ -66,16 +66,37 @@ class ClockSampler:
         self.index, self.rows, self._stop, self._th = index, [], threading.Event(), None
 
     def _run(self):
+        # NVML in-process (one init, cheap queries); the nvidia-smi subprocess is only the fallback:
+        # spawning it several times a second from every rank stalls CUDA calls of all processes.
+        nv = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            hd = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            nv = pynvml
+        except Exception:
+            nv = None
         while not self._stop.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True,
-                                     timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([c.strip() for c in out.split(",")])
+                if nv is not None:
+                    sm = nv.nvmlDeviceGetClockInfo(hd, nv.NVML_CLOCK_SM)
+                    mx = nv.nvmlDeviceGetMaxClockInfo(hd, nv.NVML_CLOCK_SM)
+                    rs = nv.nvmlDeviceGetCurrentClocksEventReasons(hd) if hasattr(
+                        nv, "nvmlDeviceGetCurrentClocksEventReasons") else nv.nvmlDeviceGetCurrentClocksThrottleReasons(hd)
+                    bit = lambda name: "Active" if rs & getattr(nv, name, 0) else "Not Active"
+                    self.rows.append([str(sm), str(mx), bit("nvmlClocksThrottleReasonHwSlowdown"),
+                                      bit("nvmlClocksThrottleReasonHwThermalSlowdown"),
+                                      bit("nvmlClocksThrottleReasonSwThermalSlowdown"),
+                                      bit("nvmlClocksThrottleReasonSwPowerCap")])
+                else:
+                    out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits"], capture_output=True, text=True,
+                                         timeout=5).stdout.strip()
+                    if out:
+                        self.rows.append([c.strip() for c in out.split(",")])
             except Exception:
                 pass
-            self._stop.wait(0.2)
+            self._stop.wait(0.05 if nv is not None else 0.5)
 
     def __enter__(self):
         self._th = threading.Thread(target=self._run, daemon=True)
@@ -245,8 +266,15 @@ def main():
         ev1.record()
         barrier()
     launches = int(lib.kpms_launch_count() - l0)
+    my_ms = ev0.elapsed_time(ev1) / args.steps
     ms = max_over_ranks(ev0.elapsed_time(ev1)) / args.steps
     value = frames_total / (ms * 1e-3)
+    per_rank = None
+    if world > 1:   # diagnostics: every rank's own time and chunk retries during the timed sweeps
+        per_rank = [None] * world
+        td.all_gather_object(per_rank, {"ms": round(my_ms, 2), "fallbacks": {a: b for a, b in G.FALLBACKS.items()
+                                                                             if not a.endswith("_berr")},
+                                        "hmm_burn_boost": G._HMM_ADAPT["boost"]})
     clocks = clk.summary()
 
     # ---- per-step breakdown and the roofline of the dominant entry point (rank-local)
@@ -355,7 +383,8 @@ def main():
                                                 if G.LATENTS_CHUNKING["chunk_len"] == "auto" else G.LATENTS_CHUNKING["chunk_len"]),
                            "kalman_burn_in": G.LATENTS_CHUNKING["burn_in"],
                            "kalman_boundary_err": boundary_err,
-                           "chunk_fallbacks": dict(G.FALLBACKS),
+                           "chunk_fallbacks": dict(G.FALLBACKS), "hmm_burn_boost": G._HMM_ADAPT["boost"],
+                           "per_rank": per_rank,
                            "l2": "per-step working set (>= 20 GB of filter workspace + ll/alphan) far exceeds the 126 MB L2"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline,
                 "cpu_baseline": cpu, "breakdown_ms": bd}
