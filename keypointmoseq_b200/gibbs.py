@@ -68,6 +68,16 @@ def auto_chunk_len(N, T, L, burn_in, device):
     return 0 if cl >= Tt else cl
 
 
+def spd_inv(A):
+    """Inverse of symmetric positive definite matrices through their Cholesky factor.  (torch.linalg.inv
+    goes through MAGMA's batched LU for small batches, which synchronises the whole DEVICE and so
+    stalls behind copies running on other streams; potrf / trsm stay on the current stream.)"""
+    L = torch.linalg.cholesky(A)
+    eye = torch.eye(A.shape[-1], dtype=A.dtype, device=A.device).expand(A.shape)
+    Li = torch.linalg.solve_triangular(L, eye, upper=False)
+    return Li.transpose(-1, -2) @ Li
+
+
 def _dims(Ab):
     K, D = Ab.shape[0], Ab.shape[1]
     L = Ab.shape[2] // Ab.shape[1]          # gibbs.py:12,102,109
@@ -353,7 +363,7 @@ def log_joint_likelihood(*, Y, mask, x, s, v, h, z, pi, Ab, Q, Cd, sigmasq, sigm
     pi, Ab, Q, sigmasq = f64(pi, dev), f64(Ab, dev), f64(Q, dev), f64(sigmasq, dev)
     K, D, L = _dims(Ab)
     Cdfull = expand_Cd(f64(Cd, dev), _gamma(Gamma, k, dev), dk)
-    Qinv = torch.linalg.inv(Q).contiguous()                     # util.py:237-238
+    Qinv = spd_inv(Q).contiguous()                              # util.py:237-238
     logdet = torch.linalg.slogdet(Q)[1].contiguous()
     out = torch.empty((5,), dtype=torch.float64, device=dev)
     ws = _lib.WORKSPACE.get("logjoint", lib.kpms_log_joint_workspace_bytes(), dev)
@@ -406,7 +416,7 @@ def sample_obs_params(key, W, V, Gamma, *, sigmasq_C, draws=None):
                       torch.eye(dk, dtype=torch.float64, device=dev))
     S_yx = torch.einsum('ji,jac->aic', Gamma, V).reshape(-1)                    # gibbs.py:77-80
     n = dk * D1 * (k - 1)
-    Sigma_n = torch.linalg.inv(torch.eye(n, dtype=torch.float64, device=dev) / sigmasq_C + S_xx)
+    Sigma_n = spd_inv(torch.eye(n, dtype=torch.float64, device=dev) / sigmasq_C + S_xx)
     Sigma_n = 0.5 * (Sigma_n + Sigma_n.T)
     mu_n = Sigma_n @ S_yx
     if draws is not None:
@@ -490,10 +500,11 @@ def sample_ar_params(key, F, *, nlags, nu_0, S_0, M_0, K_0, draws=None):
     S_0, M_0, K_0 = f64(S_0, dev), f64(M_0, dev), f64(K_0, dev)
     S_in_in, S_out_in, S_out_out = F[:, :P1, :P1], F[:, P1:, :P1], F[:, P1:, P1:]
     count = F[:, P1 - 1, P1 - 1]
-    K_0_inv = torch.linalg.inv(K_0)
-    K_n = torch.linalg.inv(K_0_inv + S_in_in)
+    K_0_inv = spd_inv(K_0)
+    K_n_inv = K_0_inv + S_in_in                     # gibbs.py:133 inverts this and :135 inverts it back
+    K_n = spd_inv(K_n_inv)
     M_n = (M_0 @ K_0_inv + S_out_in) @ K_n
-    S_n = S_0 + S_out_out + (M_0 @ K_0_inv @ M_0.T - M_n @ torch.linalg.inv(K_n) @ M_n.transpose(-1, -2))
+    S_n = S_0 + S_out_out + (M_0 @ K_0_inv @ M_0.T - M_n @ K_n_inv @ M_n.transpose(-1, -2))
     nu = nu_0 + count
     if draws is not None:
         chi2, normals, G = f64(draws["chi2"], dev), f64(draws["normals"], dev), f64(draws["G"], dev)

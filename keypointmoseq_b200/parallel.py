@@ -9,6 +9,8 @@ identical parameters from the same seed (no broadcast).
 Sweep order = examples/keypoint_slds.ipynb cell 12 (steps 1-8):
   ar_params, obs_variance, hdp_transitions, stateseqs, latents, heading, location, scales.
 """
+import os
+
 import torch
 
 from . import gibbs as G
@@ -54,7 +56,7 @@ def sufficient_stats(data, states, hyp, Gamma, params):
 
 
 def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessions_global=None,
-                _wait=None, _done=None):
+                _wait=None, _done=None, _mark=None):
     """One full sweep.  `data`/`states` hold this rank's shard; `params` are replicated.
     Returns new (states, params) dicts; inputs are not mutated.
 
@@ -67,6 +69,7 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
     rank, world = _world(group)
     wait = _wait or (lambda g: None)
     done = _done or (lambda name, t: None)
+    mark = _mark or (lambda label: None)
     defer_obs = _wait is not None
     st, pr = dict(states), dict(params)
     K = int(hyp["num_states"])
@@ -74,7 +77,9 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
     N, Tm = st["z"].shape
     wait("xz")
     F = G.ar_sufficient_stats(nlags=hyp["nlags"], num_states=K, mask=data["mask"], x=st["x"], z=st["z"])
+    mark("ar_stats")
     counts = G.transition_counts(z=st["z"], mask=data["mask"], num_states=K)
+    mark("counts")
 
     def obs_stats():
         return G.obs_variance_stats(Y=data["Y"], mask=data["mask"], Cd=pr["Cd"], v=st["v"], h=st["h"],
@@ -98,6 +103,7 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
     n_glob = n_sessions_global if n_sessions_global is not None else N * world
     pr["betas"], pr["pi"] = G.sample_hdp_transitions(key, counts, pr["betas"], hyp["alpha"], hyp["kappa"],
                                                      hyp["gamma"], max_customers=n_glob * max(Tm - 1, 1))
+    mark("params")
     # 4-8: per-session steps on the local shard; the Philox key is salted with the rank
     lkey = (key, "rank", rank)
     z_new = G.resample_stateseqs(lkey, x=st["x"], mask=data["mask"], Ab=pr["Ab"], Q=pr["Q"], pi=pr["pi"])[0]
@@ -139,7 +145,7 @@ def _copy_streams(dev):
 
 
 def gibbs_sweep_host(key, host_data, host_states, params, hyp, Gamma=None, group=None,
-                     n_sessions_global=None, out=None, device=None):
+                     n_sessions_global=None, out=None, device=None, timeline=None):
     """One sweep driven from HOST arrays (the drop-in situation: the caller keeps data and states
     in host memory, e.g. as NumPy / JAX-CPU arrays).
 
@@ -174,12 +180,26 @@ def gibbs_sweep_host(key, host_data, host_states, params, hyp, Gamma=None, group
     if out is None:
         out = {}
 
+    marks = []   # (label, event on the main stream) when a `timeline` dict is requested
+    ev_start = torch.cuda.Event(enable_timing=True)
+    if timeline is not None:
+        ev_start.record(main)
+
+    def mark(label):
+        if timeline is not None:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record(main)
+            marks.append((label, e))
+
     def wait(g):
-        main.wait_event(ev_xz if g == "xz" else ev_all)
+        mark("before_wait_" + g)
+        main.wait_event(ev_xz if (g == "xz" and os.environ.get("KPMS_E2E_NO_OVERLAP") != "1") else ev_all)
+        mark("after_wait_" + g)
 
     def done(name, t):
         if name not in out:
             out[name] = torch.empty(t.shape, dtype=t.dtype).pin_memory()
+        mark("done_" + name)
         ev = torch.cuda.Event()
         ev.record(main)
         cs_out.wait_event(ev)
@@ -191,6 +211,10 @@ def gibbs_sweep_host(key, host_data, host_states, params, hyp, Gamma=None, group
         t.record_stream(cs_out)
 
     st, pr = gibbs_sweep(key, dd, ds, params, hyp, Gamma=Gamma, group=group,
-                         n_sessions_global=n_sessions_global, _wait=wait, _done=done)
+                         n_sessions_global=n_sessions_global, _wait=wait, _done=done, _mark=mark)
     cs_out.synchronize()
+    if timeline is not None:
+        main.synchronize()
+        for label, e in marks:
+            timeline[label] = ev_start.elapsed_time(e)
     return out, pr, st
