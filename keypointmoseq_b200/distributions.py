@@ -80,7 +80,7 @@ def sample_invwishart(S, nu, chi2, normals):
     chi2(nu - arange(n)); `normals` (...,n(n-1)/2) fill the strict upper triangle in
     row-major order."""
     n = S.shape[-1]
-    chol = torch.linalg.cholesky(S)
+    chol = torch.linalg.cholesky_ex(S)[0]
     x = torch.diag_embed(torch.sqrt(chi2))
     iu = torch.triu_indices(n, n, 1, device=S.device)
     x[..., iu[0], iu[1]] = normals
@@ -92,7 +92,7 @@ def sample_invwishart(S, nu, chi2, normals):
 
 def sample_mn(M, U, V, G):
     """distributions.py:23-27."""
-    return M + torch.linalg.cholesky(U) @ G @ torch.linalg.cholesky(V).transpose(-1, -2)
+    return M + torch.linalg.cholesky_ex(U)[0] @ G @ torch.linalg.cholesky_ex(V)[0].transpose(-1, -2)
 
 
 def sample_mniw(nu, S, M, K, chi2, normals, G):

@@ -71,8 +71,10 @@ def auto_chunk_len(N, T, L, burn_in, device):
 def spd_inv(A):
     """Inverse of symmetric positive definite matrices through their Cholesky factor.  (torch.linalg.inv
     goes through MAGMA's batched LU for small batches, which synchronises the whole DEVICE and so
-    stalls behind copies running on other streams; potrf / trsm stay on the current stream.)"""
-    L = torch.linalg.cholesky(A)
+    stalls behind copies running on other streams; potrf / trsm stay on the current stream.
+    cholesky_ex does not read the status back, so nothing here synchronises with the host: like the
+    reference, a non-PD input yields NaNs rather than an exception.)"""
+    L = torch.linalg.cholesky_ex(A)[0]
     eye = torch.eye(A.shape[-1], dtype=A.dtype, device=A.device).expand(A.shape)
     Li = torch.linalg.solve_triangular(L, eye, upper=False)
     return Li.transpose(-1, -2) @ Li
@@ -423,7 +425,7 @@ def sample_obs_params(key, W, V, Gamma, *, sigmasq_C, draws=None):
         w = f64(draws["w"], dev)
     else:
         w = torch.randn((n,), dtype=torch.float64, device=dev, generator=dist.torch_generator(dist.seed_of(key), 13, dev))
-    draw = mu_n + torch.linalg.cholesky(Sigma_n) @ w                            # jr.multivariate_normal
+    draw = mu_n + torch.linalg.cholesky_ex(Sigma_n)[0] @ w                            # jr.multivariate_normal
     return draw.reshape(D1, dk * (k - 1)).T.contiguous()
 
 
