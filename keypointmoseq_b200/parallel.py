@@ -45,6 +45,27 @@ def unpack_stats(buf, K, P, k):
     return F, S_y, msum, counts
 
 
+def all_reduce_stats(F, S_y, msum, counts, group=None):
+    """Sum the per-shard statistics over the ranks with ONE all-reduce of the packed buffer.
+    S_y / msum may be None (they are then reduced later by `all_reduce_obs_stats`)."""
+    import torch.distributed as td
+    K, P, k = counts.shape[0], F.shape[1], (S_y.numel() if S_y is not None else 1)
+    buf = pack_stats(F, S_y if S_y is not None else F.new_zeros(k), msum if msum is not None else F.new_zeros(1),
+                     counts)
+    td.all_reduce(buf, op=td.ReduceOp.SUM, group=group)
+    F, S2, m2, counts = unpack_stats(buf, K, P, k)
+    return F, (S2 if S_y is not None else None), (m2 if msum is not None else None), counts
+
+
+def all_reduce_obs_stats(S_y, msum, group=None):
+    """The deferred observation-noise statistics of `gibbs_sweep_host`: k + 1 doubles."""
+    import torch.distributed as td
+    k = S_y.numel()
+    buf = torch.cat([S_y.reshape(-1), msum.reshape(-1)])
+    td.all_reduce(buf, op=td.ReduceOp.SUM, group=group)
+    return buf[:k], buf[k:k + 1]
+
+
 def sufficient_stats(data, states, hyp, Gamma, params):
     """Local (per-shard) statistics feeding the three parameter updates."""
     F = G.ar_sufficient_stats(nlags=hyp["nlags"], num_states=hyp["num_states"], mask=data["mask"],
@@ -88,13 +109,9 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
     if not defer_obs:
         S_y, msum = obs_stats()
         if world > 1:
-            buf = pack_stats(F, S_y, msum, counts)
-            td.all_reduce(buf, op=td.ReduceOp.SUM, group=group)
-            F, S_y, msum, counts = unpack_stats(buf, K, F.shape[1], k)
+            F, S_y, msum, counts = all_reduce_stats(F, S_y, msum, counts, group)
     elif world > 1:
-        buf = pack_stats(F, F.new_zeros(k), F.new_zeros(1), counts)
-        td.all_reduce(buf, op=td.ReduceOp.SUM, group=group)
-        F, _, _, counts = unpack_stats(buf, K, F.shape[1], k)
+        F, _, _, counts = all_reduce_stats(F, None, None, counts, group)
     # 1-3: replicated parameter draws (same key on every rank)
     pr["Ab"], pr["Q"] = G.sample_ar_params(key, F, nlags=hyp["nlags"], nu_0=hyp["nu_0"], S_0=hyp["S_0"],
                                            M_0=hyp["M_0"], K_0=hyp["K_0"])
@@ -112,9 +129,7 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
         wait("all")
         S_y, msum = obs_stats()     # uses the OLD x (st["x"]), exactly as step 2 of the sweep does
         if world > 1:
-            buf = torch.cat([S_y.reshape(-1), msum.reshape(-1)])
-            td.all_reduce(buf, op=td.ReduceOp.SUM, group=group)
-            S_y, msum = buf[:k], buf[k:k + 1]
+            S_y, msum = all_reduce_obs_stats(S_y, msum, group)
         pr["sigmasq"] = G.sample_obs_variance(key, S_y, msum, nu_sigma=hyp["nu_sigma"], sigmasq_0=hyp["sigmasq_0"])
     st["z"] = z_new
     st["x"] = G.resample_latents(lkey, Y=data["Y"], mask=data["mask"], v=st["v"], h=st["h"], z=st["z"],

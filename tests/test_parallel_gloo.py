@@ -45,6 +45,13 @@ def _worker(rank, world, port, out):
         buf = parallel.pack_stats(F, S_y, msum, counts)
         td.all_reduce(buf, op=td.ReduceOp.SUM)
         F2, S2, m2, c2 = parallel.unpack_stats(buf, K, F.shape[1], k)
+        # the two-stage reduction of the host-driven sweep must give the same sums
+        F3, _, _, c3 = parallel.all_reduce_stats(F, None, None, counts)
+        S3, m3 = parallel.all_reduce_obs_stats(S_y, msum)
+        F4, S4, m4, c4 = parallel.all_reduce_stats(F, S_y, msum, counts)
+        two_stage_ok = bool(torch.equal(F3, F2) and torch.equal(c3, c2) and torch.equal(S3, S2) and
+                            torch.equal(m3.reshape(-1), m2.reshape(-1)) and torch.equal(F4, F2) and
+                            torch.equal(S4, S2) and torch.equal(c4, c2))
         Ab, Q = G.sample_ar_params((3, 1), F2, nlags=L, nu_0=hp['nu_0'], S_0=torch.as_tensor(hp['S_0']),
                                    M_0=torch.as_tensor(hp['M_0']), K_0=torch.as_tensor(hp['K_0']))
         sig = G.sample_obs_variance((3, 1), S2, m2, nu_sigma=hp['nu_sigma'], sigmasq_0=hp['sigmasq_0'])
@@ -53,7 +60,7 @@ def _worker(rank, world, port, out):
         if rank == 0:
             Ff, Sf, mf, cf = _local_stats(d, s, p, Gm, L, K, 0, N)
             out.put(dict(F_err=float((F2 - Ff).abs().max() / Ff.abs().max()), S_err=float((S2 - Sf).abs().max()),
-                         m_ok=bool(torch.equal(m2, mf)), c_ok=bool(torch.equal(c2, cf)),
+                         m_ok=bool(torch.equal(m2, mf)), c_ok=bool(torch.equal(c2, cf)), two_stage_ok=two_stage_ok,
                          same_params=bool(all(torch.equal(g, Ab) for g in gathered)),
                          finite=bool(torch.isfinite(Ab).all() and torch.isfinite(Q).all() and (sig > 0).all())))
     finally:
@@ -82,4 +89,4 @@ def test_packed_allreduce_and_replicated_draws_gloo():
         p.join(timeout=120)
         assert p.exitcode == 0
     assert res["F_err"] < 1e-13 and res["S_err"] < 1e-9
-    assert res["m_ok"] and res["c_ok"] and res["same_params"] and res["finite"]
+    assert res["m_ok"] and res["c_ok"] and res["same_params"] and res["finite"] and res["two_stage_ok"]
