@@ -21,6 +21,11 @@ SIGNATURES = {
     "kpms_version": (c_int, []),
     "kpms_status_string": (ctypes.c_char_p, [c_int]),
     "kpms_launch_count": (c_uint64, []),
+    "kpms_set_option": (c_int, [ctypes.c_char_p, c_int]),
+    "kpms_get_option": (c_int, [ctypes.c_char_p, ctypes.POINTER(c_int)]),
+    "kpms_fill_uniform_at": (c_int, [P, c_size_t, c_uint64, c_uint64, c_uint64, P]),
+    "kpms_fill_normal_at": (c_int, [P, c_size_t, c_uint64, c_uint64, c_uint64, P]),
+    "kpms_fill_gamma_at": (c_int, [P, c_size_t, c_uint64, c_double, c_uint64, c_uint64, P]),
     "kpms_fill_uniform": (c_int, [P, c_size_t, c_uint64, c_uint64, P]),
     "kpms_fill_normal": (c_int, [P, c_size_t, c_uint64, c_uint64, P]),
     "kpms_fill_gamma": (c_int, [P, c_size_t, c_double, c_uint64, c_uint64, P]),
@@ -36,7 +41,9 @@ SIGNATURES = {
     "kpms_ar_stats_workspace_bytes": (c_size_t, [c_int] * 5),
     "kpms_ar_stats": (c_int, [P, P, P, c_int, c_int, c_int, c_int, c_int, P, P, c_size_t, P]),
     "kpms_count_transitions": (c_int, [P, P, c_int64, c_int, c_int, c_int, P, P]),
-    "kpms_crp_tablecounts": (c_int, [P, P, P, c_double, c_double, P, P, c_int, c_int, P, P, P, P]),
+    "kpms_crp_tablecounts": (c_int, [P, P, P, c_double, c_double, P, c_int64, P, c_int, c_int, P, P, P, P]),
+    "kpms_crp_tablecounts_philox": (c_int, [P, P, P, c_double, c_double, c_uint64, c_uint64, c_uint64, c_int,
+                                            P, P, P]),
     "kpms_obs_variance_stats_workspace_bytes": (c_size_t, [c_int] * 3),
     "kpms_obs_variance_stats": (c_int, [P] * 7 + [c_int] * 5 + [P, P, P, c_size_t, P]),
     "kpms_obs_params_stats_workspace_bytes": (c_size_t, [c_int] * 5),
@@ -72,6 +79,17 @@ def load():
         fn.argtypes = args
     _lib = lib
     return lib
+
+
+def set_option(name, value):
+    """Debugging / cross-check switch of the library (see include/kpms_b200.h: kpms_set_option)."""
+    check(load().kpms_set_option(name.encode(), int(value)), "kpms_set_option(%s)" % name)
+
+
+def get_option(name):
+    v = c_int(0)
+    check(load().kpms_get_option(name.encode(), ctypes.byref(v)), "kpms_get_option(%s)" % name)
+    return v.value
 
 
 def check(status, what):

@@ -1,9 +1,43 @@
 // Version / status strings and the Philox fill kernels of libkpms_b200.
 #include "common.cuh"
 
+#include <stdlib.h>
+#include <string.h>
+
 unsigned long long kpms_launch_counter = 0;
 
-extern "C" int kpms_version(void) { return 100; }
+// Debugging / cross-check switches.  The environment is read ONCE, when the library is loaded;
+// afterwards only kpms_set_option changes them (no getenv on any launch path).
+static int env_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return (e && e[0]) ? atoi(e) : dflt;
+}
+KpmsOptions kpms_opts = {env_int("KPMS_KALMAN_IMPL", 1), env_int("KPMS_HMM_TC", 1), env_int("KPMS_HMM_BWD_BURN", -1),
+                         env_int("KPMS_LL_TILED", 0), env_int("KPMS_HMM_FLAGS", 0)};
+
+static int* option_slot(const char* name) {
+  if (!name) return nullptr;
+  if (!strcmp(name, "kalman_impl")) return &kpms_opts.kalman_impl;
+  if (!strcmp(name, "hmm_tc")) return &kpms_opts.hmm_tc;
+  if (!strcmp(name, "hmm_bwd_burn")) return &kpms_opts.hmm_bwd_burn;
+  if (!strcmp(name, "ll_tiled")) return &kpms_opts.ll_tiled;
+  if (!strcmp(name, "hmm_flags")) return &kpms_opts.hmm_flags;
+  return nullptr;
+}
+extern "C" int kpms_set_option(const char* name, int value) {
+  int* slot = option_slot(name);
+  KPMS_REQUIRE(slot != nullptr, KPMS_ERR_UNSUPPORTED);
+  *slot = value;
+  return KPMS_OK;
+}
+extern "C" int kpms_get_option(const char* name, int* value) {
+  int* slot = option_slot(name);
+  KPMS_REQUIRE(slot != nullptr && value != nullptr, KPMS_ERR_UNSUPPORTED);
+  *value = *slot;
+  return KPMS_OK;
+}
+
+extern "C" int kpms_version(void) { return 200; }
 extern "C" uint64_t kpms_launch_count(void) { return kpms_launch_counter; }
 
 extern "C" const char* kpms_status_string(int status) {
@@ -23,89 +57,77 @@ extern "C" const char* kpms_status_string(int status) {
 }
 
 // counter = (element-group index lo, hi, round, stream_id); key = seed.  One Philox call
-// yields 4 uniforms / 4 normals, so thread g fills elements 4g..4g+3.
-__global__ void fill_uniform_kernel(float* __restrict__ out, size_t n, uint2 key, uint32_t sid) {
-  size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  size_t i = g * 4;
-  if (i >= n) return;
-  uint4 r = philox4x32_10(make_uint4((uint32_t)g, (uint32_t)(g >> 32), 0u, sid), key);
-  float v[4] = {u01(r.x), u01(r.y), u01(r.z), u01(r.w)};
-  if (i + 3 < n && ((uintptr_t)(out + i) % 16 == 0)) {
-    *reinterpret_cast<float4*>(out + i) = make_float4(v[0], v[1], v[2], v[3]);
+// yields 4 uniforms / 4 normals: group G holds the elements 4G..4G+3 of the GLOBAL index space
+// (global index = offset + local index), so a shard that fills only its own sessions gets exactly
+// the values a single process filling the whole array would have put there.
+template <int NORMAL>
+__global__ void fill4_kernel(float* __restrict__ out, size_t n, unsigned long long offset, uint2 key,
+                             uint32_t sid) {
+  const unsigned long long G = (offset >> 2) + (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long i = (long long)(G * 4ULL - offset);   // local index of the group's first element (may be < 0)
+  if (i >= (long long)n) return;
+  uint4 r = philox4x32_10(make_uint4((uint32_t)G, (uint32_t)(G >> 32), NORMAL ? 1u : 0u, sid), key);
+  float v[4];
+  if (NORMAL) {
+    float2 a = box_muller(r.x, r.y), b = box_muller(r.z, r.w);
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
   } else {
-    for (int j = 0; j < 4 && i + j < n; j++) out[i + j] = v[j];
+    v[0] = u01(r.x); v[1] = u01(r.y); v[2] = u01(r.z); v[3] = u01(r.w);
   }
-}
-
-__global__ void fill_normal_kernel(float* __restrict__ out, size_t n, uint2 key, uint32_t sid) {
-  size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  size_t i = g * 4;
-  if (i >= n) return;
-  uint4 r = philox4x32_10(make_uint4((uint32_t)g, (uint32_t)(g >> 32), 1u, sid), key);
-  float2 a = box_muller(r.x, r.y), b = box_muller(r.z, r.w);
-  float v[4] = {a.x, a.y, b.x, b.y};
-  if (i + 3 < n && ((uintptr_t)(out + i) % 16 == 0)) {
+  if (i >= 0 && i + 3 < (long long)n && ((uintptr_t)(out + i) % 16 == 0)) {
     *reinterpret_cast<float4*>(out + i) = make_float4(v[0], v[1], v[2], v[3]);
   } else {
-    for (int j = 0; j < 4 && i + j < n; j++) out[i + j] = v[j];
+    for (int j = 0; j < 4; j++)
+      if (i + j >= 0 && i + j < (long long)n) out[i + j] = v[j];
   }
 }
 
 // Marsaglia & Tsang (2000) for shape >= 1; one element per thread, rejection rounds
 // advance the third counter word.
-__global__ void fill_gamma_kernel(float* __restrict__ out, size_t n, float shape, uint2 key,
-                                  uint32_t sid) {
+__global__ void fill_gamma_kernel(float* __restrict__ out, size_t n, unsigned long long offset, float shape,
+                                  uint2 key, uint32_t sid) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const float d = shape - 1.0f / 3.0f;
-  const float c = rsqrtf(9.0f * d);
-  float res = d;
-  for (uint32_t round = 0; round < 64u; round++) {
-    uint4 r = philox4x32_10(make_uint4((uint32_t)i, (uint32_t)(i >> 32), 2u + round, sid), key);
-    float2 nn = box_muller(r.x, r.y);
-    float xx = nn.x;
-    float v = 1.0f + c * xx;
-    if (v <= 0.0f) continue;
-    v = v * v * v;
-    float u = u01_open0(r.z);
-    if (logf(u) < 0.5f * xx * xx + d - d * v + d * logf(v)) {
-      res = d * v;
-      break;
-    }
-  }
-  out[i] = res;
+  out[i] = philox_gamma(offset + i, shape, key, sid);
 }
 
-static inline uint2 split_seed(uint64_t seed) {
-  return make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
-}
 
-extern "C" int kpms_fill_uniform(float* out, size_t n, uint64_t seed, uint64_t stream_id,
-                                 void* stream) {
+static int fill4(int normal, float* out, size_t n, uint64_t offset, uint64_t seed, uint64_t stream_id, void* stream) {
   KPMS_REQUIRE(out != nullptr || n == 0, KPMS_ERR_NULL);
   if (n == 0) return KPMS_OK;
-  size_t groups = (n + 3) / 4;
-  fill_uniform_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-      out, n, split_seed(seed), (uint32_t)stream_id);
+  const size_t groups = (size_t)(((offset + n + 3) >> 2) - (offset >> 2));
+  const unsigned blocks = (unsigned)((groups + 255) / 256);
+  if (normal)
+    fill4_kernel<1><<<blocks, 256, 0, (cudaStream_t)stream>>>(out, n, offset, split_seed(seed), (uint32_t)stream_id);
+  else
+    fill4_kernel<0><<<blocks, 256, 0, (cudaStream_t)stream>>>(out, n, offset, split_seed(seed), (uint32_t)stream_id);
   return kpms_last_launch();
 }
 
-extern "C" int kpms_fill_normal(float* out, size_t n, uint64_t seed, uint64_t stream_id,
-                                void* stream) {
-  KPMS_REQUIRE(out != nullptr || n == 0, KPMS_ERR_NULL);
-  if (n == 0) return KPMS_OK;
-  size_t groups = (n + 3) / 4;
-  fill_normal_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-      out, n, split_seed(seed), (uint32_t)stream_id);
-  return kpms_last_launch();
+extern "C" int kpms_fill_uniform_at(float* out, size_t n, uint64_t offset, uint64_t seed, uint64_t stream_id,
+                                    void* stream) {
+  return fill4(0, out, n, offset, seed, stream_id, stream);
 }
-
-extern "C" int kpms_fill_gamma(float* out, size_t n, double shape, uint64_t seed,
-                               uint64_t stream_id, void* stream) {
+extern "C" int kpms_fill_normal_at(float* out, size_t n, uint64_t offset, uint64_t seed, uint64_t stream_id,
+                                   void* stream) {
+  return fill4(1, out, n, offset, seed, stream_id, stream);
+}
+extern "C" int kpms_fill_gamma_at(float* out, size_t n, uint64_t offset, double shape, uint64_t seed,
+                                  uint64_t stream_id, void* stream) {
   KPMS_REQUIRE(out != nullptr || n == 0, KPMS_ERR_NULL);
   KPMS_REQUIRE(shape >= 1.0, KPMS_ERR_UNSUPPORTED);
   if (n == 0) return KPMS_OK;
   fill_gamma_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-      out, n, (float)shape, split_seed(seed), (uint32_t)stream_id);
+      out, n, offset, (float)shape, split_seed(seed), (uint32_t)stream_id);
   return kpms_last_launch();
+}
+extern "C" int kpms_fill_uniform(float* out, size_t n, uint64_t seed, uint64_t stream_id, void* stream) {
+  return fill4(0, out, n, 0, seed, stream_id, stream);
+}
+extern "C" int kpms_fill_normal(float* out, size_t n, uint64_t seed, uint64_t stream_id, void* stream) {
+  return fill4(1, out, n, 0, seed, stream_id, stream);
+}
+extern "C" int kpms_fill_gamma(float* out, size_t n, double shape, uint64_t seed, uint64_t stream_id,
+                               void* stream) {
+  return kpms_fill_gamma_at(out, n, 0, shape, seed, stream_id, stream);
 }

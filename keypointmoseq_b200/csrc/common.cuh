@@ -17,6 +17,17 @@
     if (e__ != cudaSuccess) return (int)e__; \
   } while (0)
 
+// debugging / cross-check switches (api.cu): read from the environment once at load time,
+// changed afterwards only through kpms_set_option
+struct KpmsOptions {
+  int kalman_impl;   // 0: CTA-per-chunk shared-memory Kalman filter instead of the warp kernel
+  int hmm_tc;        // 0: CUDA-core chunked HMM filter instead of the tcgen05 one
+  int hmm_bwd_burn;  // >= 0: warm-up of the HMM sampler only (0 forces every chunk through the repair pass)
+  int ll_tiled;      // 1: the emission kernel writes the interleaved HMM layout directly
+  int hmm_flags;     // bit 0: forward pass only (timing)
+};
+extern KpmsOptions kpms_opts;
+
 // host-side count of kernel launches issued by this library (one bump per launch site)
 extern unsigned long long kpms_launch_counter;
 static inline int kpms_last_launch() {
@@ -59,6 +70,7 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
   }
   return ctr;
 }
+static inline uint2 split_seed(uint64_t seed) { return make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)); }
 // [0,1) with 24 random bits (exactly representable in fp32)
 __device__ __forceinline__ float u01(uint32_t r) { return (float)(r >> 8) * (1.0f / 16777216.0f); }
 // (0,1]
@@ -70,6 +82,35 @@ __device__ __forceinline__ float2 box_muller(uint32_t a, uint32_t b) {
   float s, c;
   sincospif(2.0f * u01(b), &s, &c);
   return make_float2(r * c, r * s);
+}
+
+// Gamma(shape, 1), shape >= 1 (Marsaglia & Tsang 2000) for GLOBAL element index e: rejection
+// rounds advance the third counter word, so the value depends on (seed, stream id, e) only.
+__device__ __forceinline__ float philox_gamma(unsigned long long e, float shape, uint2 key, uint32_t sid) {
+  const float d = shape - 1.0f / 3.0f;
+  const float c = rsqrtf(9.0f * d);
+  float res = d;
+  for (uint32_t round = 0; round < 64u; round++) {
+    uint4 r = philox4x32_10(make_uint4((uint32_t)e, (uint32_t)(e >> 32), 2u + round, sid), key);
+    float2 nn = box_muller(r.x, r.y);
+    float xx = nn.x;
+    float v = 1.0f + c * xx;
+    if (v <= 0.0f) continue;
+    v = v * v * v;
+    float u = u01_open0(r.z);
+    if (logf(u) < 0.5f * xx * xx + d - d * v + d * logf(v)) {
+      res = d * v;
+      break;
+    }
+  }
+  return res;
+}
+// uniform [0,1) number `e` of the stream a kpms_fill_uniform(seed, sid) call would have produced
+__device__ __forceinline__ float philox_uniform_at(unsigned long long e, uint2 key, uint32_t sid) {
+  const unsigned long long G = e >> 2;
+  const uint4 r = philox4x32_10(make_uint4((uint32_t)G, (uint32_t)(G >> 32), 0u, sid), key);
+  const uint32_t w = (e & 3) == 0 ? r.x : ((e & 3) == 1 ? r.y : ((e & 3) == 2 ? r.z : r.w));
+  return u01(w);
 }
 
 // R(-h)(y - v) in the first two coordinates (reference util.py:140-166)

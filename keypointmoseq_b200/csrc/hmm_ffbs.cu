@@ -112,6 +112,8 @@ __global__ void hmm_tv_kernel(const float* __restrict__ mask, long long mask_str
 }
 
 bool kpms_hmm_tc_supported(int Tm, int K, int chunk_len);  // hmm_tc.cu
+int kpms_hmm_mask_check(const float* mask, long long mask_stride, int Tm, const int* tv, int N,
+                        unsigned* err_bits, cudaStream_t st);  // hmm_tc.cu
 int kpms_hmm_forward_tc(const float* ll, int ll_tiled, float* ll_scratch, const float* mask,
                         long long mask_stride, const double* pi, const float* u, const int* tv, int N,
                         int Tm, int K, int chunk_len, int burn_in, int nch, float* a_out, float* T_out,
@@ -282,7 +284,10 @@ __global__ void hmm_finish_kernel(HmmWs ws, int nch, int K, int chunk_len, doubl
     if ((c + 1) * chunk_len >= tvn) break;  // the next chunk starts inside the trailing padding
     const float* a = ws.bnd + ((size_t)(n * nch + c) * 2 + 1) * K;
     const float* b = ws.bnd + ((size_t)(n * nch + c + 1) * 2 + 0) * K;
-    for (int e = threadIdx.x; e < K; e += blockDim.x) worst = fmaxf(worst, fabsf(a[e] - b[e]));
+    for (int e = threadIdx.x; e < K; e += blockDim.x) {
+      const float d = fabsf(a[e] - b[e]);
+      worst = (d != d) ? INFINITY : fmaxf(worst, d);  // a NaN boundary must fail the check, not vanish in fmax
+    }
   }
   for (int o = 16; o > 0; o >>= 1) worst = fmaxf(worst, __shfl_xor_sync(0xffffffffu, worst, o));
   if ((threadIdx.x & 31) == 0) atomicMax(err_bits, __float_as_uint(worst));
@@ -590,6 +595,11 @@ static int launch_reg(const float* ll, int ll_tiled, const float* mask, long lon
   }
   if (boundary_err) KPMS_CUDA(cudaMemsetAsync(boundary_err, 0, sizeof(float), st));
   int rc = KPMS_ERR_UNSUPPORTED;
+  if (nch > 1) {  // both chunked filters assume trailing padding; anything else is flagged as 1e30
+    rc = kpms_hmm_mask_check(mask, ms, Tm, ws.tv, N, (unsigned*)boundary_err, st);
+    if (rc) return rc;
+    rc = KPMS_ERR_UNSUPPORTED;
+  }
   if (nch > 1)
     rc = kpms_hmm_forward_tc(ll, ll_tiled, ws.lltile, mask, ms, pi, u, ws.tv, N, Tm, K, chunk_len, burn_in, nch,
                              ws.alphan, ws.Tbuf, ws.stay, ws.llpart, ws.bnd, (unsigned*)boundary_err, st);
@@ -604,15 +614,14 @@ static int launch_reg(const float* ll, int ll_tiled, const float* mask, long lon
   hmm_finish_kernel<<<N, 128, 0, st>>>(ws, nch, K, chunk_len, loglik, (unsigned*)boundary_err);
   rc = kpms_last_launch();
   if (rc) return rc;
-  const char* env = getenv("KPMS_HMM_FLAGS");  // debugging: bit 0 = forward pass only
-  if (env && (atoi(env) & 1)) return KPMS_OK;
+  if (kpms_opts.hmm_flags & 1) return KPMS_OK;  // debugging: forward pass only
   auto kern = hmm_backward_kernel<KP>;
   const size_t smem = (size_t)(KP * KP + HMM_BWARPS * (HMM_BRING * 8 + 32)) * sizeof(float);
   KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const long long units = (long long)N * nch;
-  const char* eb = getenv("KPMS_HMM_BWD_BURN");  // testing: warm-up of the sampler only (0 = every chunk repaired)
+  const int bwd_burn = kpms_opts.hmm_bwd_burn;  // testing: warm-up of the sampler only (0 = every chunk repaired)
   kern<<<(unsigned)((units + HMM_BWARPS - 1) / HMM_BWARPS), HMM_BWARPS * 32, smem, st>>>(
-      mask, ms, pi, u, N, Tm, K, chunk_len, eb ? atoi(eb) : burn_in, z, ws);
+      mask, ms, pi, u, N, Tm, K, chunk_len, bwd_burn >= 0 ? bwd_burn : burn_in, z, ws);
   rc = kpms_last_launch();
   if (rc || nch == 1) return rc;
   auto rep = hmm_brepair_kernel<KP>;
@@ -633,6 +642,8 @@ int kpms_hmm_ffbs_impl(const float* ll, int ll_tiled, const float* mask, int64_t
   KPMS_REQUIRE(K <= 1024, KPMS_ERR_UNSUPPORTED);
   KPMS_REQUIRE(chunk_len <= 0 || burn_in >= 0, KPMS_ERR_SHAPE);
   if (K > 128) chunk_len = 0;  // the generic kernel walks whole sessions
+  // chunked mode reports what it could not verify through boundary_err: it is not optional there
+  KPMS_REQUIRE(hmm_nchunks(Tm, chunk_len) == 1 || boundary_err != nullptr, KPMS_ERR_NULL);
   HmmWs ws;
   const size_t need = hmm_layout(N, Tm, K, chunk_len, workspace, &ws);
   KPMS_REQUIRE(kpms_aligned(workspace, 256) && workspace_bytes >= need, KPMS_ERR_WORKSPACE);

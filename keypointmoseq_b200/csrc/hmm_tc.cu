@@ -532,9 +532,15 @@ __global__ void __launch_bounds__(256) hmm_ll_tile_kernel(const float* __restric
   }
 }
 
+// Chunked passes assume trailing padding: flags anything else as 1e30 in *err_bits.
+int kpms_hmm_mask_check(const float* mask, long long mask_stride, int Tm, const int* tv, int N,
+                        unsigned* err_bits, cudaStream_t st) {
+  hmm_mask_check_kernel<<<N, 256, 0, st>>>(mask, mask_stride, Tm, tv, err_bits);
+  return kpms_last_launch();
+}
+
 bool kpms_hmm_tc_supported(int Tm, int K, int chunk_len) {
-  const char* tcenv = getenv("KPMS_HMM_TC");  // "0" forces the CUDA-core forward kernel in chunked mode
-  if (tcenv && tcenv[0] == '0') return false;
+  if (kpms_opts.hmm_tc == 0) return false;  // option: CUDA-core forward kernel in chunked mode
   return chunk_len > 0 && chunk_len < Tm && K <= 104 && (K & 3) == 0;
 }
 
@@ -547,11 +553,7 @@ int kpms_hmm_forward_tc(const float* ll, int ll_tiled, float* ll_scratch, const 
                         unsigned* stay, double* llpart, float* bnd, unsigned* err_bits, cudaStream_t st) {
   if (!kpms_hmm_tc_supported(Tm, K, chunk_len)) return KPMS_ERR_UNSUPPORTED;
   int rc = 0;
-  if (err_bits) {
-    hmm_mask_check_kernel<<<N, 256, 0, st>>>(mask, mask_stride, Tm, tv, err_bits);
-    rc = kpms_last_launch();
-    if (rc) return rc;
-  }
+  (void)mask; (void)mask_stride; (void)err_bits;  // the caller has run kpms_hmm_mask_check
   if (!ll_tiled) {
     const long long tiles = (((long long)N * nch + 127) / 128) * chunk_len;
     const size_t smem = (size_t)(K >> 2) * 129 * sizeof(float4);

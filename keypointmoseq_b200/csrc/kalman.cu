@@ -1073,7 +1073,8 @@ __global__ void kalman_finish_kernel(KalWs ws, int nch, int BND, int NN, double*
       }
       double md = 0.0, ma = 0.0;
       for (int e = tid; e < len; e += blockDim.x) {
-        md = fmax(md, fabs(a[e] - b[e]));
+        const double d = fabs(a[e] - b[e]);
+        md = (d != d) ? INFINITY : fmax(md, d);  // a NaN boundary must fail the check, not vanish in fmax
         ma = fmax(ma, fabs(a[e]));
       }
       for (int o = 16; o > 0; o >>= 1) {
@@ -1130,8 +1131,7 @@ static int launch_latents(const float* Y, const float* mask, const float* v, con
   {
     const size_t smem = (size_t)(2 * NN * YL::NS + NN * YL::NV + 3 * NN + NN * NN + NN * DD + DD * DD +
                                  NN + DD + 2 + YL::OBS_SIZE) * sizeof(double) + 2 * YL::NTRI;
-    const char* env = getenv("KPMS_KALMAN_IMPL");
-    if (env && env[0] == '0') {  // CTA-per-chunk shared-memory kernel (kept for cross-checks)
+    if (kpms_opts.kalman_impl == 0 || NN > 30) {  // CTA-per-chunk shared-memory kernel (cross-checks; n > 30)
       auto kern = kalman_forward_kernel<NN, DD>;
       KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       kern<<<N * nch, KAL_NT, smem, st>>>(mask, z, w_last, ws, N, T, Lg, chunk_len, burn_in,

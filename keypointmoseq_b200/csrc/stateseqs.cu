@@ -51,9 +51,8 @@ extern "C" int kpms_resample_stateseqs(const float* x, const float* mask, const 
   int tile_cl = 0, tile_nch = 0, tiled = 0;
   // Writing ll straight into the filter's interleaved layout makes the emission kernel gather its
   // lag windows from scattered frames, which costs more (6.5 vs 3.3 ms on the bench shard) than the
-  // filter's own transposition pass (0.65 ms); opt in with KPMS_LL_TILED=1.
-  const char* env = getenv("KPMS_LL_TILED");
-  if (env && env[0] == '1' && kpms_hmm_tc_supported(Tm, K, chunk_len)) {
+  // filter's own transposition pass (0.65 ms); opt in with kpms_set_option("ll_tiled", 1).
+  if (kpms_opts.ll_tiled == 1 && kpms_hmm_tc_supported(Tm, K, chunk_len)) {
     tile_cl = chunk_len;
     tile_nch = (Tm + chunk_len - 1) / chunk_len;
   }

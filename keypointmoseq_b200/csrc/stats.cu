@@ -219,7 +219,7 @@ extern "C" int kpms_count_transitions(const int32_t* z, const float* mask, int64
 __global__ void crp_tablecounts_kernel(const long long* __restrict__ counts,
                                        const long long* __restrict__ starts,
                                        const double* __restrict__ betas, double alpha, double kappa,
-                                       const float* __restrict__ randseq,
+                                       const float* __restrict__ randseq, long long randseq_len,
                                        const float* __restrict__ u_thin, int thin_cap, int K,
                                        long long* __restrict__ ms, long long* __restrict__ ms_raw,
                                        int* __restrict__ overflow) {
@@ -229,7 +229,9 @@ __global__ void crp_tablecounts_kernel(const long long* __restrict__ counts,
   __shared__ long long m_sh;
   const long long c = counts[cell];
   long long m = 0;
-  if (c > 0) {
+  if (c > 0 && starts[cell] + c > randseq_len) {  // the caller's uniforms do not cover this cell
+    if (tid == 0 && overflow) atomicOr(overflow, 2);
+  } else if (c > 0) {
     const double cw = alpha * betas[j];
     const float* rs = randseq + starts[cell];
     for (long long q = tid; q < c; q += blockDim.x)
@@ -252,7 +254,7 @@ __global__ void crp_tablecounts_kernel(const long long* __restrict__ counts,
   long long lim = mraw;
   if (lim > thin_cap) {
     lim = thin_cap;
-    if (tid == 0 && overflow) *overflow = 1;
+    if (tid == 0 && overflow) atomicOr(overflow, 1);
   }
   long long kept = 0;
   for (long long q = tid; q < lim; q += blockDim.x)
@@ -270,14 +272,93 @@ __global__ void crp_tablecounts_kernel(const long long* __restrict__ counts,
 
 extern "C" int kpms_crp_tablecounts(const int64_t* counts, const int64_t* starts,
                                     const double* betas, double alpha, double kappa,
-                                    const float* randseq, const float* u_thin, int thin_cap, int K,
-                                    int64_t* ms, int64_t* ms_raw, int32_t* overflow, void* stream) {
+                                    const float* randseq, int64_t randseq_len, const float* u_thin,
+                                    int thin_cap, int K, int64_t* ms, int64_t* ms_raw, int32_t* overflow,
+                                    void* stream) {
   KPMS_REQUIRE(counts && starts && betas && randseq && u_thin && ms, KPMS_ERR_NULL);
-  KPMS_REQUIRE(K > 0 && thin_cap > 0, KPMS_ERR_SHAPE);
+  KPMS_REQUIRE(K > 0 && thin_cap > 0 && randseq_len >= 0, KPMS_ERR_SHAPE);
   cudaStream_t st = (cudaStream_t)stream;
   if (overflow) KPMS_CUDA(cudaMemsetAsync(overflow, 0, sizeof(int32_t), st));
   crp_tablecounts_kernel<<<K * K, 256, 0, st>>>((const long long*)counts, (const long long*)starts,
-                                                betas, alpha, kappa, randseq, u_thin, thin_cap, K,
+                                                betas, alpha, kappa, randseq, (long long)randseq_len, u_thin,
+                                                thin_cap, K,
                                                 (long long*)ms, (long long*)ms_raw, overflow);
+  return kpms_last_launch();
+}
+
+// Same table counts with the uniforms generated in the kernel: customer c of cell (i,j) uses
+// uniform number starts[i,j]+c of the Philox stream (seed, stream_crp) — exactly the value
+// kpms_fill_uniform would have written to randseq[starts[i,j]+c] — and thinning draw q of state i
+// uses uniform number (i << 32) + q of stream (seed, stream_thin).  Nothing of the size of the data
+// is materialised, the thinning has no capacity limit, and every rank of a sharded job computes
+// identical counts from the all-reduced `counts` without exchanging anything.
+__global__ void crp_tablecounts_philox_kernel(const long long* __restrict__ counts,
+                                              const long long* __restrict__ starts,
+                                              const double* __restrict__ betas, double alpha, double kappa,
+                                              uint2 key, uint32_t sid_crp, uint32_t sid_thin, int K,
+                                              long long* __restrict__ ms, long long* __restrict__ ms_raw) {
+  const int cell = blockIdx.x, i = cell / K, j = cell % K;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  __shared__ long long red[8];
+  __shared__ long long m_sh;
+  const long long c = counts[cell];
+  long long m = 0;
+  if (c > 0) {
+    const double cw = alpha * betas[j];
+    const unsigned long long e0 = (unsigned long long)starts[cell], e1 = e0 + (unsigned long long)c;
+    for (unsigned long long G = (e0 >> 2) + tid; G <= ((e1 - 1) >> 2); G += blockDim.x) {
+      const uint4 r = philox4x32_10(make_uint4((uint32_t)G, (uint32_t)(G >> 32), 0u, sid_crp), key);
+      const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+      for (int q4 = 0; q4 < 4; q4++) {
+        const unsigned long long e = G * 4ULL + q4;
+        if (e >= e0 && e < e1) m += ((double)u01(w[q4]) < cw / ((double)(e - e0) + cw)) ? 1 : 0;
+      }
+    }
+  }
+  m = warp_sum_ll(m);
+  if (lane == 0) red[warp] = m;
+  __syncthreads();
+  if (tid == 0) {
+    long long s = 0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); w++) s += red[w];
+    m_sh = s;
+    if (ms_raw) ms_raw[cell] = s;
+    if (i != j) ms[cell] = s;
+  }
+  if (i != j) return;
+  __syncthreads();
+  const long long mraw = m_sh;
+  const double rho = betas[i] * alpha / (betas[i] * alpha + kappa);
+  long long kept = 0;
+  const unsigned long long base = (unsigned long long)i << 32;
+  for (unsigned long long G = tid; G * 4ULL < (unsigned long long)mraw; G += blockDim.x) {
+    const unsigned long long GG = (base >> 2) + G;
+    const uint4 r = philox4x32_10(make_uint4((uint32_t)GG, (uint32_t)(GG >> 32), 0u, sid_thin), key);
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int q4 = 0; q4 < 4; q4++)
+      if ((long long)(G * 4ULL + q4) < mraw) kept += ((double)u01(w[q4]) < rho) ? 1 : 0;
+  }
+  kept = warp_sum_ll(kept);
+  __syncthreads();
+  if (lane == 0) red[warp] = kept;
+  __syncthreads();
+  if (tid == 0) {
+    long long s = 0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); w++) s += red[w];
+    ms[cell] = s;
+  }
+}
+
+extern "C" int kpms_crp_tablecounts_philox(const int64_t* counts, const int64_t* starts,
+                                           const double* betas, double alpha, double kappa, uint64_t seed,
+                                           uint64_t stream_crp, uint64_t stream_thin, int K, int64_t* ms,
+                                           int64_t* ms_raw, void* stream) {
+  KPMS_REQUIRE(counts && starts && betas && ms, KPMS_ERR_NULL);
+  KPMS_REQUIRE(K > 0, KPMS_ERR_SHAPE);
+  crp_tablecounts_philox_kernel<<<K * K, 256, 0, (cudaStream_t)stream>>>(
+      (const long long*)counts, (const long long*)starts, betas, alpha, kappa, split_seed(seed),
+      (uint32_t)stream_crp, (uint32_t)stream_thin, K, (long long*)ms, (long long*)ms_raw);
   return kpms_last_launch();
 }

@@ -37,24 +37,35 @@ def torch_generator(seed, salt, device):
     return g
 
 
-def fill_uniform(shape, seed, stream_id, device):
+def _row_offset(shape, first_row):
+    """Global element index of this shard's first element: the draws of row (session) n depend on
+    its GLOBAL index first_row + n only, so results do not depend on how sessions are sharded
+    (the reference splits one key per session: gibbs.py:20,54,112,145)."""
+    per_row = 1
+    for d in shape[1:]:
+        per_row *= int(d)
+    return int(first_row) * per_row
+
+
+def fill_uniform(shape, seed, stream_id, device, first_row=0):
     out = torch.empty(shape, dtype=torch.float32, device=device)
-    _lib.check(_lib.load().kpms_fill_uniform(_lib.ptr(out), out.numel(), seed, stream_id,
-                                             _lib.stream_ptr(device)), "kpms_fill_uniform")
+    _lib.check(_lib.load().kpms_fill_uniform_at(_lib.ptr(out), out.numel(), _row_offset(shape, first_row), seed,
+                                                stream_id, _lib.stream_ptr(device)), "kpms_fill_uniform_at")
     return out
 
 
-def fill_normal(shape, seed, stream_id, device):
+def fill_normal(shape, seed, stream_id, device, first_row=0):
     out = torch.empty(shape, dtype=torch.float32, device=device)
-    _lib.check(_lib.load().kpms_fill_normal(_lib.ptr(out), out.numel(), seed, stream_id,
-                                            _lib.stream_ptr(device)), "kpms_fill_normal")
+    _lib.check(_lib.load().kpms_fill_normal_at(_lib.ptr(out), out.numel(), _row_offset(shape, first_row), seed,
+                                               stream_id, _lib.stream_ptr(device)), "kpms_fill_normal_at")
     return out
 
 
-def fill_gamma(shape, conc, seed, stream_id, device):
+def fill_gamma(shape, conc, seed, stream_id, device, first_row=0):
     out = torch.empty(shape, dtype=torch.float32, device=device)
-    _lib.check(_lib.load().kpms_fill_gamma(_lib.ptr(out), out.numel(), float(conc), seed, stream_id,
-                                           _lib.stream_ptr(device)), "kpms_fill_gamma")
+    _lib.check(_lib.load().kpms_fill_gamma_at(_lib.ptr(out), out.numel(), _row_offset(shape, first_row),
+                                              float(conc), seed, stream_id, _lib.stream_ptr(device)),
+               "kpms_fill_gamma_at")
     return out
 
 

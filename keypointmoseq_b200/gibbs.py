@@ -19,7 +19,6 @@ from . import distributions as dist
 from .util import center_embedding, expand_Cd, f32, f64, i32
 
 VONMISES_ROUNDS = 8          # Best-Fisher rejection rounds pre-drawn per frame
-THIN_CAP = 16384             # max tables per state handled by the sticky thinning
 # Kalman time-chunking: "auto" cuts every session into chunks sized so that one wave of warps
 # covers the shard; each chunk is warmed up over `burn_in` earlier steps.  With strict=True the
 # reported chunk-boundary mismatch is read back and the call is repeated in the exact sequential
@@ -66,6 +65,12 @@ def auto_chunk_len(N, T, L, burn_in, device):
     if nch == 1 or cl < 4 * max(burn_in, 1):
         cl = max(4 * max(burn_in, 1), 256)
     return 0 if cl >= Tt else cl
+
+
+def latents_check_ok(berr):
+    """Reads the Kalman chunk-boundary mismatch back (synchronises); NaN counts as a failure."""
+    b = float(berr.max()) if torch.is_tensor(berr) else float(berr)
+    return b == b and b <= LATENTS_CHUNKING["tol"]
 
 
 def spd_inv(A):
@@ -116,26 +121,47 @@ _HMM_ADAPT = {"boost": 1, "streak": 0}
 HMM_MAX_BOOST = 16
 
 
-def _run_hmm_adaptive(run, berr, chunk_len, burn_in, strict, adaptive):
-    """run(chunk_len, burn_in) launches one chunked pass and fills `berr`."""
+def _hmm_burn(burn_in, boost):
+    return burn_in if boost == 1 else max(burn_in, 32) * boost
+
+
+def note_hmm_check(b, adaptive=True):
+    """Book-keeping of the adaptive warm-up after a chunked pass whose boundary mismatch was `b`.
+    Returns True when the pass is acceptable."""
     tol = STATESEQ_CHUNKING["tol"]
+    if b <= tol:
+        if adaptive:
+            _HMM_ADAPT["streak"] = _HMM_ADAPT["streak"] + 1 if b <= 0.03 * tol else 0
+            if _HMM_ADAPT["streak"] >= 8 and _HMM_ADAPT["boost"] > 1:
+                _HMM_ADAPT["boost"] //= 2
+                _HMM_ADAPT["streak"] = 0
+        return True
+    FALLBACKS["stateseqs"] += 1
+    FALLBACKS.setdefault("stateseqs_berr", []).append(b)
+    del FALLBACKS["stateseqs_berr"][:-8]
+    return False
+
+
+def _run_hmm_adaptive(run, berr, chunk_len, burn_in, strict, adaptive):
+    """run(chunk_len, burn_in) launches one chunked pass and fills `berr`.
+    strict=True reads the mismatch back (one host synchronisation) and repeats the pass with a longer
+    warm-up, finally with the sequential kernels, until it is within tolerance.  strict="defer"
+    launches once with the current adaptive warm-up and leaves the check to the caller
+    (`parallel.gibbs_sweep` reads all boundary errors of a sweep back together, once)."""
     if chunk_len <= 0 or not strict:
         run(chunk_len, burn_in if chunk_len > 0 else 0)
         return
     boost = _HMM_ADAPT["boost"] if adaptive else 1
+    if strict == "defer":
+        run(chunk_len, _hmm_burn(burn_in, boost))
+        return
     while True:
-        run(chunk_len, burn_in if boost == 1 else max(burn_in, 32) * boost)
+        run(chunk_len, _hmm_burn(burn_in, boost))
         b = float(berr)
-        if b <= tol:
-            if adaptive:
-                _HMM_ADAPT["streak"] = _HMM_ADAPT["streak"] + 1 if b <= 0.03 * tol else 0
-                if _HMM_ADAPT["streak"] >= 8 and _HMM_ADAPT["boost"] > 1:
-                    _HMM_ADAPT["boost"] //= 2
-                    _HMM_ADAPT["streak"] = 0
+        if b != b:
+            b = float("inf")
+        if note_hmm_check(b, adaptive):
             return
-        FALLBACKS["stateseqs"] += 1
-        FALLBACKS.setdefault("stateseqs_berr", []).append(b)
-        del FALLBACKS["stateseqs_berr"][:-8]
         boost *= 2
         if b > 1e29 or boost > HMM_MAX_BOOST:     # 1e30 flags a mask that is not trailing padding
             FALLBACKS["stateseqs_exact"] = FALLBACKS.get("stateseqs_exact", 0) + 1
@@ -152,7 +178,7 @@ def _hmm_chunking(N, Tm, K, chunk_len, burn_in, strict, dev):
     auto = chunk_len == "auto"
     if auto:
         chunk_len = auto_hmm_chunk_len(N, Tm, K, int(burn_in), dev) if K <= 128 else 0
-    return int(chunk_len), int(burn_in), bool(strict), auto
+    return int(chunk_len), int(burn_in), (strict if strict == "defer" else bool(strict)), auto
 
 
 def sample_hmm_stateseqs(*, ll, mask, pi, u, chunk_len=None, burn_in=None, strict=None, return_info=False):
@@ -182,8 +208,10 @@ def sample_hmm_stateseqs(*, ll, mask, pi, u, chunk_len=None, burn_in=None, stric
 
 
 def resample_stateseqs(key, *, x, mask, Ab, Q, pi, draws=None, impl=0, chunk_len=None, burn_in=None,
-                       strict=None, **kwargs):
-    """gibbs.py:107-115 -> (z (N,T-L) int32, marginal log-likelihood (N,) float64)."""
+                       strict=None, session_offset=0, return_info=False, **kwargs):
+    """gibbs.py:107-115 -> (z (N,T-L) int32, marginal log-likelihood (N,) float64).
+    `session_offset`: global index of this shard's first session (keys the Philox draws, so that
+    the samples do not depend on the sharding)."""
     global last_stateseq_boundary_err
     lib = _lib.load()
     x = f32(x)
@@ -194,7 +222,7 @@ def resample_stateseqs(key, *, x, mask, Ab, Q, pi, draws=None, impl=0, chunk_len
     if draws is not None:
         u = f32(draws["u"], dev)
     else:
-        u = dist.fill_uniform((N, T - L), dist.seed_of(key), dist.STREAM_Z, dev)
+        u = dist.fill_uniform((N, T - L), dist.seed_of(key), dist.STREAM_Z, dev, session_offset)
     chunk_len, burn_in, strict, auto = _hmm_chunking(N, T - L, K, chunk_len, burn_in, strict, dev)
     z = torch.empty((N, T - L), dtype=torch.int32, device=dev)
     loglik = torch.empty((N,), dtype=torch.float64, device=dev)
@@ -211,12 +239,15 @@ def resample_stateseqs(key, *, x, mask, Ab, Q, pi, draws=None, impl=0, chunk_len
 
     _run_hmm_adaptive(run, berr, chunk_len, burn_in, strict, auto)
     last_stateseq_boundary_err = berr
+    if return_info:
+        return z, loglik, {"boundary_err": berr, "chunk_len": chunk_len}
     return z, loglik
 
 
 # ------------------------------------------------------------------------ a5-a7
 def resample_latents(key, *, Y, mask, v, h, z, s, Cd, sigmasq, Ab, Q, Gamma=None, draws=None,
-                     chunk_len=None, burn_in=None, strict=None, return_info=False, **kwargs):
+                     chunk_len=None, burn_in=None, strict=None, return_info=False, session_offset=0,
+                     **kwargs):
     """gibbs.py:10-23 -> x (N,T,D) float32.  With `return_info=True` also returns a dict with
     the innovation-form marginal log-likelihood (N,) and the chunk-boundary mismatch (2,)."""
     lib = _lib.load()
@@ -233,8 +264,8 @@ def resample_latents(key, *, Y, mask, v, h, z, s, Cd, sigmasq, Ab, Q, Gamma=None
         w, w_last = f32(draws["w"], dev), f32(draws["w_last"], dev)
     else:
         seed = dist.seed_of(key)
-        w = dist.fill_normal((N, T - L, n), seed, dist.STREAM_X, dev)
-        w_last = dist.fill_normal((N, n), seed, dist.STREAM_X_LAST, dev)
+        w = dist.fill_normal((N, T - L, n), seed, dist.STREAM_X, dev, session_offset)
+        w_last = dist.fill_normal((N, n), seed, dist.STREAM_X_LAST, dev, session_offset)
     global last_latents_boundary_err
     chunk_len = LATENTS_CHUNKING["chunk_len"] if chunk_len is None else chunk_len
     burn_in = LATENTS_CHUNKING["burn_in"] if burn_in is None else burn_in
@@ -255,7 +286,7 @@ def resample_latents(key, *, Y, mask, v, h, z, s, Cd, sigmasq, Ab, Q, Gamma=None
             ws.numel(), _lib.stream_ptr(dev)), "kpms_resample_latents")
 
     run(chunk_len, burn_in)
-    if chunk_len > 0 and strict and float(berr.max()) > LATENTS_CHUNKING["tol"]:
+    if chunk_len > 0 and strict and strict != "defer" and not latents_check_ok(berr):
         # warm-up too short for this model: once more with four times the warm-up, then exactly
         # (one warp per session)
         FALLBACKS["latents"] += 1
@@ -264,19 +295,19 @@ def resample_latents(key, *, Y, mask, v, h, z, s, Cd, sigmasq, Ab, Q, Gamma=None
         ok = False
         if cl2 > 0:
             run(cl2, burn2)
-            ok = float(berr.max()) <= LATENTS_CHUNKING["tol"]
+            ok = latents_check_ok(berr)
         if not ok:
             FALLBACKS["latents_exact"] = FALLBACKS.get("latents_exact", 0) + 1
             run(0, 0)
     last_latents_boundary_err = berr
     if return_info:
-        return x, {"loglik": loglik, "boundary_err": berr}
+        return x, {"loglik": loglik, "boundary_err": berr, "chunk_len": chunk_len}
     return x
 
 
 # ------------------------------------------------------------------------ a15
 def resample_heading(key, *, Y, v, x, s, Cd, sigmasq, Gamma=None, draws=None, return_info=False,
-                     **kwargs):
+                     session_offset=0, **kwargs):
     """gibbs.py:25-35 -> h (N,T) float32 in [-pi, pi]."""
     lib = _lib.load()
     Y = f32(Y)
@@ -288,7 +319,7 @@ def resample_heading(key, *, Y, v, x, s, Cd, sigmasq, Gamma=None, draws=None, re
     if draws is not None:
         u = f32(draws["u"], dev)
     else:
-        u = dist.fill_uniform((N, T, VONMISES_ROUNDS, 3), dist.seed_of(key), dist.STREAM_H, dev)
+        u = dist.fill_uniform((N, T, VONMISES_ROUNDS, 3), dist.seed_of(key), dist.STREAM_H, dev, session_offset)
     rounds = u.shape[2]
     hout = torch.empty((N, T), dtype=torch.float32, device=dev)
     theta = torch.empty((N, T), dtype=torch.float64, device=dev) if return_info else None
@@ -304,7 +335,7 @@ def resample_heading(key, *, Y, v, x, s, Cd, sigmasq, Gamma=None, draws=None, re
 
 # ------------------------------------------------------------------------ a16
 def resample_location(key, *, mask, Y, h, x, s, Cd, sigmasq, sigmasq_loc, Gamma=None, draws=None,
-                      return_info=False, **kwargs):
+                      return_info=False, session_offset=0, **kwargs):
     """gibbs.py:38-54 -> v (N,T,dk) float32."""
     lib = _lib.load()
     Y = f32(Y)
@@ -317,8 +348,8 @@ def resample_location(key, *, mask, Y, h, x, s, Cd, sigmasq, sigmasq_loc, Gamma=
         w, w_last = f32(draws["w"], dev), f32(draws["w_last"], dev)
     else:
         seed = dist.seed_of(key)
-        w = dist.fill_normal((N, T - 1, dk), seed, dist.STREAM_V, dev)
-        w_last = dist.fill_normal((N, dk), seed, dist.STREAM_V_LAST, dev)
+        w = dist.fill_normal((N, T - 1, dk), seed, dist.STREAM_V, dev, session_offset)
+        w_last = dist.fill_normal((N, dk), seed, dist.STREAM_V_LAST, dev, session_offset)
     vout = torch.empty((N, T, dk), dtype=torch.float32, device=dev)
     loglik = torch.empty((N,), dtype=torch.float64, device=dev) if return_info else None
     ws = _lib.WORKSPACE.get("location", lib.kpms_resample_location_workspace_bytes(N, T, dk), dev)
@@ -455,7 +486,8 @@ def resample_obs_variance(key, *, Y, mask, Cd, v, h, x, s, nu_sigma, sigmasq_0, 
 
 
 # ------------------------------------------------------------------------ a14
-def resample_scales(key, *, x, v, h, Y, Cd, sigmasq, nu_s, s_0, Gamma=None, draws=None, **kwargs):
+def resample_scales(key, *, x, v, h, Y, Cd, sigmasq, nu_s, s_0, Gamma=None, draws=None, session_offset=0,
+                    **kwargs):
     """gibbs.py:117-125 -> s (N,T,k) float32 (no mask, as the reference)."""
     lib = _lib.load()
     Y = f32(Y)
@@ -467,7 +499,7 @@ def resample_scales(key, *, x, v, h, Y, Cd, sigmasq, nu_s, s_0, Gamma=None, draw
     if draws is not None:
         g = f32(draws["g"], dev)
     else:
-        g = dist.fill_gamma((N, T, k), (nu_s + 3) / 2, dist.seed_of(key), dist.STREAM_S, dev)
+        g = dist.fill_gamma((N, T, k), (nu_s + 3) / 2, dist.seed_of(key), dist.STREAM_S, dev, session_offset)
     sout = torch.empty((N, T, k), dtype=torch.float32, device=dev)
     _lib.check(lib.kpms_resample_scales(
         _lib.ptr(Y), _lib.ptr(v), _lib.ptr(h), _lib.ptr(x), _lib.ptr(Cdfull), _lib.ptr(sigmasq),
@@ -557,8 +589,17 @@ def transition_counts(*, z, mask, num_states, **kwargs):
     return counts
 
 
-def sample_ms(key, counts, betas, alpha, kappa, draws=None, max_customers=None):
-    """transitions.py:23-33 -> ms (K,K) int64 (CRP table counts, sticky diagonal thinned)."""
+def sample_ms(key, counts, betas, alpha, kappa, draws=None, max_customers=None, thin=False):
+    """transitions.py:23-33 -> (ms (K,K) int64, ms_raw (K,K) int64 = the CRP table counts).
+    thin=False (default): ms = ms_raw, which is what the reference returns — its binomial thinning of
+    the sticky diagonal (transitions.py:28-31) is assigned to a temporary copy (`newms.flat[::K+1]`
+    slices a flat iterator) and never reaches the result; pinned by
+    tests/golden/reference_sweep_bench.npz.  thin=True: the thinning the code intends, as the
+    Bernoulli sum over uniforms.  Without `draws` the uniforms are generated inside the kernel (Philox,
+    customer c of cell (i,j) = number starts[i,j]+c of the stream): nothing of the size of the data
+    is materialised and every rank of a sharded job gets the same counts.  With injected `draws`
+    (`randseq`, `u_thin`) a capacity overflow raises.  `max_customers` is accepted for
+    compatibility and ignored."""
     lib = _lib.load()
     dev = counts.device
     K = counts.shape[0]
@@ -566,31 +607,40 @@ def sample_ms(key, counts, betas, alpha, kappa, draws=None, max_customers=None):
     betas = f64(betas, dev)
     flat = counts.flatten()
     starts = (torch.cumsum(flat, 0) - flat).reshape(K, K).contiguous()   # transitions.py:12-15
-    if draws is not None:
-        randseq, u_thin = f32(draws["randseq"], dev), f32(draws["u_thin"], dev)
-        if randseq.numel() == 0:
-            randseq = torch.zeros(1, dtype=torch.float32, device=dev)
-    else:
-        if max_customers is None:
-            max_customers = int(flat.sum().item())
-        seed = dist.seed_of(key)
-        randseq = dist.fill_uniform((max(int(max_customers), 1),), seed, dist.STREAM_CRP, dev)
-        u_thin = dist.fill_uniform((K, THIN_CAP), seed, dist.STREAM_THIN, dev)
     ms = torch.empty((K, K), dtype=torch.int64, device=dev)
     ms_raw = torch.empty((K, K), dtype=torch.int64, device=dev)
+    if draws is None or "randseq" not in draws:
+        seed = dist.seed_of(key)
+        _lib.check(lib.kpms_crp_tablecounts_philox(
+            _lib.ptr(counts), _lib.ptr(starts), _lib.ptr(betas), float(alpha), float(kappa), seed,
+            dist.STREAM_CRP, dist.STREAM_THIN, K, _lib.ptr(ms), _lib.ptr(ms_raw), _lib.stream_ptr(dev)),
+            "kpms_crp_tablecounts_philox")
+        return (ms if thin else ms_raw), ms_raw
+    randseq = f32(draws["randseq"], dev)
+    u_thin = f32(draws["u_thin"], dev) if thin else torch.zeros((K, 1), dtype=torch.float32, device=dev)
+    nrand = randseq.numel()
+    if nrand == 0:
+        randseq = torch.zeros(1, dtype=torch.float32, device=dev)
     overflow = torch.zeros((1,), dtype=torch.int32, device=dev)
     _lib.check(lib.kpms_crp_tablecounts(
         _lib.ptr(counts), _lib.ptr(starts), _lib.ptr(betas), float(alpha), float(kappa), _lib.ptr(randseq),
-        _lib.ptr(u_thin), int(u_thin.shape[1]), K, _lib.ptr(ms), _lib.ptr(ms_raw), _lib.ptr(overflow),
+        nrand, _lib.ptr(u_thin), int(u_thin.shape[1]), K, _lib.ptr(ms), _lib.ptr(ms_raw), _lib.ptr(overflow),
         _lib.stream_ptr(dev)), "kpms_crp_tablecounts")
-    return ms, ms_raw, overflow
+    flag = int(overflow.item()) & (3 if thin else 2)
+    if flag:
+        raise _lib.KpmsError("sample_ms: injected draws too short (%s)" % ", ".join(
+            n for b, n in ((1, "u_thin has fewer columns than tables to thin"),
+                           (2, "randseq shorter than the number of transitions")) if flag & b))
+    return (ms if thin else ms_raw), ms_raw
 
 
-def sample_hdp_transitions(key, counts, betas, alpha, kappa, gamma, draws=None, max_customers=None):
-    """transitions.py:35-40 -> (betas (K,), pi (K,K)) float64."""
+def sample_hdp_transitions(key, counts, betas, alpha, kappa, gamma, draws=None, max_customers=None, thin=False,
+                           return_info=False):
+    """transitions.py:35-40 -> (betas (K,), pi (K,K)) float64.  With `return_info=True` also a dict
+    with the table counts `ms` and the two Dirichlet concentrations."""
     dev = counts.device
     K = counts.shape[0]
-    ms, _, _ = sample_ms(key, counts, betas, alpha, kappa, draws=draws, max_customers=max_customers)
+    ms, _ = sample_ms(key, counts, betas, alpha, kappa, draws=draws, thin=thin)
     gen = dist.torch_generator(dist.seed_of(key), 12, dev)
     if draws is not None and "betas_g" in draws:
         gb = f64(draws["betas_g"], dev)
@@ -604,27 +654,32 @@ def sample_hdp_transitions(key, counts, betas, alpha, kappa, gamma, draws=None, 
         pi = gp / gp.sum(-1, keepdim=True)
     else:
         pi = dist.sample_dirichlet(gen, conc)
+    if return_info:
+        return betas_new, pi, {"ms": ms, "betas_conc": ms.sum(0).to(torch.float64) + gamma / K, "pi_conc": conc}
     return betas_new, pi
 
 
-def sample_transitions(key, counts, alpha, kappa):
-    """transitions.py:42-44."""
+def sample_transitions(key, counts, alpha, kappa, draws=None):
+    """transitions.py:42-44 -> pi (K,K) float64; `draws={'pi_g': Gamma(conc) variates}` injects the draw."""
     dev = counts.device
     K = counts.shape[0]
     conc = counts.to(torch.float64) + alpha + kappa * torch.eye(K, dtype=torch.float64, device=dev)
+    if draws is not None and "pi_g" in draws:
+        gp = f64(draws["pi_g"], dev)
+        return gp / gp.sum(-1, keepdim=True)
     return dist.sample_dirichlet(dist.torch_generator(dist.seed_of(key), 14, dev), conc)
 
 
-def resample_hdp_transitions(key, *, z, mask, betas, alpha, kappa, gamma, num_states, draws=None, **kwargs):
+def resample_hdp_transitions(key, *, z, mask, betas, alpha, kappa, gamma, num_states, draws=None, thin=False,
+                             return_info=False, **kwargs):
     """gibbs.py:148-151 -> (betas, pi).  No device->host copy of z / mask: the histogram and
     the CRP table counts run on the GPU (the reference round-trips through numba)."""
     counts = transition_counts(z=z, mask=mask, num_states=num_states)
-    N, Tm = z.shape
-    return sample_hdp_transitions(key, counts, betas, alpha, kappa, gamma, draws=draws,
-                                  max_customers=N * max(Tm - 1, 1))
+    return sample_hdp_transitions(key, counts, betas, alpha, kappa, gamma, draws=draws, thin=thin,
+                                  return_info=return_info)
 
 
-def resample_transitions(key, *, z, mask, alpha, kappa, num_states, **kwargs):
+def resample_transitions(key, *, z, mask, alpha, kappa, num_states, draws=None, **kwargs):
     """gibbs.py:153-156 -> pi."""
     counts = transition_counts(z=z, mask=mask, num_states=num_states)
-    return sample_transitions(key, counts, alpha, kappa)
+    return sample_transitions(key, counts, alpha, kappa, draws=draws)

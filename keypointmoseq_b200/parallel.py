@@ -1,19 +1,33 @@
-"""One blocked Gibbs sweep over session shards (one process per GPU).
+"""Blocked Gibbs sweeps over session shards (one process per GPU).
 
 Sessions are conditionally independent given the parameters, so every per-frame /
 per-session step runs on its own shard with no communication.  The three parameter steps
 consume only sufficient statistics of the previous sweep's state, which are packed into
 one float64 buffer and combined with ONE all-reduce per sweep; every rank then draws
-identical parameters from the same seed (no broadcast).
+identical parameters from the same key (no broadcast).
 
-Sweep order = examples/keypoint_slds.ipynb cell 12 (steps 1-8):
-  ar_params, obs_variance, hdp_transitions, stateseqs, latents, heading, location, scales.
+`gibbs_sweep`  : the full keypoint-SLDS sweep, examples/keypoint_slds.ipynb cell 12 (steps 1-8):
+                 ar_params, obs_variance, hdp_transitions, stateseqs, latents, heading, location, scales.
+`arhmm_sweep`  : the AR-HMM sweep with x fixed, keypoint_slds.ipynb cell 9 / depth_ar_hmm.ipynb cell 8:
+                 hdp_transitions, ar_params, stateseqs.
+
+Random draws of session n depend on its GLOBAL index (`session_offset` + local index), never on
+the rank, so z, x, h, v, s do not depend on how the sessions are sharded (the reference splits one
+key per session: gibbs.py:20,54,112,145).
+
+The chunk-parallel passes (HMM, Kalman) report a boundary mismatch.  A sweep launches all of its
+steps optimistically and reads the mismatches back ONCE, at its end; a step that failed is redone
+(with a longer warm-up, finally sequentially) together with the steps after it.  The warm-up
+multiplier of the HMM passes is shared by all ranks: each rank's verdict on its last pass travels
+in the packed all-reduce, so every rank changes it at the same sweep.
 """
 import os
 
 import torch
 
 from . import gibbs as G
+
+_N_FLAGS = 3   # [passes that failed, passes that were comfortable, passes reported] of the previous sweep
 
 
 def _world(group):
@@ -30,31 +44,56 @@ def shard_range(n_sessions, rank, world):
     return lo, lo + base + (1 if rank < rem else 0)
 
 
-def pack_stats(F, S_y, msum, counts):
-    """-> flat float64 buffer [F | S_y | mask_sum | counts]."""
-    return torch.cat([F.reshape(-1), S_y.reshape(-1), msum.reshape(-1),
-                      counts.to(torch.float64).reshape(-1)])
+_OFFSETS = {}
 
 
-def unpack_stats(buf, K, P, k):
+def session_offset_of(n_local, group=None):
+    """Global index of this rank's first session when shards are contiguous in rank order.
+    Gathered once per (group, shard size) and cached: sharding is static during a fit."""
+    import torch.distributed as td
+    rank, world = _world(group)
+    if world == 1:
+        return 0
+    key = (id(group), int(n_local))
+    if key not in _OFFSETS:
+        sizes = [None] * world
+        td.all_gather_object(sizes, int(n_local), group=group)
+        _OFFSETS[key] = sum(sizes[:rank])
+    return _OFFSETS[key]
+
+
+def pack_stats(F, S_y, msum, counts, flags=None):
+    """-> flat float64 buffer [F | S_y | mask_sum | counts | flags]."""
+    parts = [F.reshape(-1), S_y.reshape(-1), msum.reshape(-1), counts.to(torch.float64).reshape(-1)]
+    if flags is not None:
+        parts.append(flags.to(torch.float64).reshape(-1))
+    return torch.cat(parts)
+
+
+def unpack_stats(buf, K, P, k, n_flags=0):
     o = 0
     F = buf[o:o + K * P * P].reshape(K, P, P); o += K * P * P
     S_y = buf[o:o + k]; o += k
     msum = buf[o:o + 1]; o += 1
-    counts = buf[o:o + K * K].reshape(K, K).round().to(torch.int64)
+    counts = buf[o:o + K * K].reshape(K, K).round().to(torch.int64); o += K * K
+    if n_flags:
+        return F, S_y, msum, counts, buf[o:o + n_flags]
     return F, S_y, msum, counts
 
 
-def all_reduce_stats(F, S_y, msum, counts, group=None):
+def all_reduce_stats(F, S_y, msum, counts, group=None, flags=None):
     """Sum the per-shard statistics over the ranks with ONE all-reduce of the packed buffer.
-    S_y / msum may be None (they are then reduced later by `all_reduce_obs_stats`)."""
+    S_y / msum may be None (they are then reduced later by `all_reduce_obs_stats`).  With `flags`
+    (a small float64 vector) the summed flags are returned as a fifth value."""
     import torch.distributed as td
     K, P, k = counts.shape[0], F.shape[1], (S_y.numel() if S_y is not None else 1)
     buf = pack_stats(F, S_y if S_y is not None else F.new_zeros(k), msum if msum is not None else F.new_zeros(1),
-                     counts)
+                     counts, flags)
     td.all_reduce(buf, op=td.ReduceOp.SUM, group=group)
-    F, S2, m2, counts = unpack_stats(buf, K, P, k)
-    return F, (S2 if S_y is not None else None), (m2 if msum is not None else None), counts
+    out = unpack_stats(buf, K, P, k, 0 if flags is None else flags.numel())
+    F, S2, m2, counts = out[:4]
+    res = (F, (S2 if S_y is not None else None), (m2 if msum is not None else None), counts)
+    return res if flags is None else res + (out[4],)
 
 
 def all_reduce_obs_stats(S_y, msum, group=None):
@@ -76,17 +115,96 @@ def sufficient_stats(data, states, hyp, Gamma, params):
     return F, S_y, msum, counts
 
 
+# ---------------------------------------------------------------------------------------------
+# Shared warm-up multiplier of the chunked HMM passes.  `verdict` = what this rank saw in its last
+# sweep (travels in the next all-reduce); `pending` = the summed verdicts of all ranks, a device
+# tensor that is read back together with the boundary errors at the end of the sweep.
+_HMM_SHARED = {"verdict": None}
+
+
+def _local_verdict(dev):
+    v = _HMM_SHARED["verdict"]
+    if v is None:
+        return torch.zeros(_N_FLAGS, dtype=torch.float64, device=dev)
+    # built from Python scalars by fill kernels: no host->device copy that could wait for the stream
+    return torch.stack([torch.full((), float(x), dtype=torch.float64, device=dev) for x in v])
+
+
+def _apply_verdicts(failed, comfortable, reported):
+    """Identical on every rank (the inputs are all-reduced sums)."""
+    A = G._HMM_ADAPT
+    if reported <= 0:
+        return
+    if failed > 0:
+        A["boost"], A["streak"] = min(A["boost"] * 2, G.HMM_MAX_BOOST), 0
+    elif comfortable >= reported:
+        A["streak"] += 1
+        if A["streak"] >= 8 and A["boost"] > 1:
+            A["boost"] //= 2
+            A["streak"] = 0
+    else:
+        A["streak"] = 0
+
+
+def _verify_and_repair(checks, flags_dev, run_from, world):
+    """ONE device->host read of everything a sweep left to verify; redo what failed."""
+    parts, names = [], []
+    for name in ("z", "x"):
+        if name in checks and checks[name] is not None:
+            parts.append(checks[name].reshape(-1).to(torch.float64))
+            names.append((name, checks[name].numel()))
+    if flags_dev is not None:
+        parts.append(flags_dev.reshape(-1))
+    if not parts:
+        return
+    host = torch.cat(parts).cpu().tolist()      # the sweep's only synchronisation
+    o, vals = 0, {}
+    for name, cnt in names:
+        vals[name] = max(float("inf") if v != v else v for v in host[o:o + cnt])
+        o += cnt
+    if flags_dev is not None:                    # verdicts of the PREVIOUS sweep, summed over the ranks
+        _apply_verdicts(*host[o:o + _N_FLAGS])
+    tolz = G.STATESEQ_CHUNKING["tol"]
+    verdict = [0.0, 0.0, 0.0]
+    z_failed = False
+    if "z" in vals:
+        b = vals["z"]
+        verdict = [float(b > tolz), float(b <= 0.03 * tolz), 1.0]
+        if b > tolz:
+            z_failed = True
+            G.FALLBACKS["stateseqs"] += 1
+            G.FALLBACKS.setdefault("stateseqs_berr", []).append(b)
+            del G.FALLBACKS["stateseqs_berr"][:-8]
+    if world > 1:
+        _HMM_SHARED["verdict"] = verdict
+    else:
+        _apply_verdicts(*verdict)
+    if z_failed:
+        # redo the state sequences with verification on (longer warm-up, finally sequential) and
+        # everything that consumed them; the shared multiplier itself moves through _apply_verdicts
+        saved = dict(G._HMM_ADAPT)
+        G._HMM_ADAPT["boost"] = min(saved["boost"] * 2, G.HMM_MAX_BOOST) if world > 1 else saved["boost"]
+        run_from("z", True)
+        if world > 1:
+            G._HMM_ADAPT.update(saved)
+    elif "x" in vals and not (vals["x"] <= G.LATENTS_CHUNKING["tol"]):
+        G.FALLBACKS["latents"] += 1
+        run_from("x", True)
+
+
 def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessions_global=None,
-                _wait=None, _done=None, _mark=None):
+                session_offset=None, _wait=None, _done=None, _mark=None):
     """One full sweep.  `data`/`states` hold this rank's shard; `params` are replicated.
     Returns new (states, params) dicts; inputs are not mutated.
+
+    `session_offset`: global index of this shard's first session (default: gathered once from the
+    shard sizes, contiguous in rank order).  `n_sessions_global` is accepted for compatibility.
 
     `_wait(group)` / `_done(name, tensor)` are the hooks of `gibbs_sweep_host`: `_wait("xz")` is
     called before x, z and mask are first read, `_wait("all")` before Y, v, h and s are, and
     `_done` as soon as a state is final.  With hooks the observation-noise statistics are taken
     after the state sequences (they do not depend on z, so the sweep is unchanged) — by then
     the large arrays have arrived."""
-    import torch.distributed as td
     rank, world = _world(group)
     wait = _wait or (lambda g: None)
     done = _done or (lambda name, t: None)
@@ -94,8 +212,9 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
     defer_obs = _wait is not None
     st, pr = dict(states), dict(params)
     K = int(hyp["num_states"])
-    k = data["Y"].shape[2]
-    N, Tm = st["z"].shape
+    N = st["z"].shape[0]
+    off = session_offset_of(N, group) if session_offset is None else int(session_offset)
+    dev = st["z"].device if torch.is_tensor(st["z"]) else None
     wait("xz")
     F = G.ar_sufficient_stats(nlags=hyp["nlags"], num_states=K, mask=data["mask"], x=st["x"], z=st["z"])
     mark("ar_stats")
@@ -106,46 +225,92 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
         return G.obs_variance_stats(Y=data["Y"], mask=data["mask"], Cd=pr["Cd"], v=st["v"], h=st["h"],
                                     x=st["x"], s=st["s"], Gamma=Gamma)
     S_y = msum = None
+    flags_dev = None
     if not defer_obs:
         S_y, msum = obs_stats()
         if world > 1:
-            F, S_y, msum, counts = all_reduce_stats(F, S_y, msum, counts, group)
+            F, S_y, msum, counts, flags_dev = all_reduce_stats(F, S_y, msum, counts, group, _local_verdict(F.device))
     elif world > 1:
-        F, _, _, counts = all_reduce_stats(F, None, None, counts, group)
+        F, _, _, counts, flags_dev = all_reduce_stats(F, None, None, counts, group, _local_verdict(F.device))
     # 1-3: replicated parameter draws (same key on every rank)
     pr["Ab"], pr["Q"] = G.sample_ar_params(key, F, nlags=hyp["nlags"], nu_0=hyp["nu_0"], S_0=hyp["S_0"],
                                            M_0=hyp["M_0"], K_0=hyp["K_0"])
     if not defer_obs:
         pr["sigmasq"] = G.sample_obs_variance(key, S_y, msum, nu_sigma=hyp["nu_sigma"], sigmasq_0=hyp["sigmasq_0"])
-    n_glob = n_sessions_global if n_sessions_global is not None else N * world
     pr["betas"], pr["pi"] = G.sample_hdp_transitions(key, counts, pr["betas"], hyp["alpha"], hyp["kappa"],
-                                                     hyp["gamma"], max_customers=n_glob * max(Tm - 1, 1))
+                                                     hyp["gamma"])
     mark("params")
-    # 4-8: per-session steps on the local shard; the Philox key is salted with the rank
-    lkey = (key, "rank", rank)
-    z_new = G.resample_stateseqs(lkey, x=st["x"], mask=data["mask"], Ab=pr["Ab"], Q=pr["Q"], pi=pr["pi"])[0]
-    done("z", z_new)
-    if defer_obs:
-        wait("all")
-        S_y, msum = obs_stats()     # uses the OLD x (st["x"]), exactly as step 2 of the sweep does
-        if world > 1:
-            S_y, msum = all_reduce_obs_stats(S_y, msum, group)
-        pr["sigmasq"] = G.sample_obs_variance(key, S_y, msum, nu_sigma=hyp["nu_sigma"], sigmasq_0=hyp["sigmasq_0"])
-    st["z"] = z_new
-    st["x"] = G.resample_latents(lkey, Y=data["Y"], mask=data["mask"], v=st["v"], h=st["h"], z=st["z"],
-                                 s=st["s"], Cd=pr["Cd"], sigmasq=pr["sigmasq"], Ab=pr["Ab"], Q=pr["Q"],
-                                 Gamma=Gamma)
-    done("x", st["x"])
-    st["h"] = G.resample_heading(lkey, Y=data["Y"], v=st["v"], x=st["x"], s=st["s"], Cd=pr["Cd"],
-                                 sigmasq=pr["sigmasq"], Gamma=Gamma)
-    done("h", st["h"])
-    st["v"] = G.resample_location(lkey, mask=data["mask"], Y=data["Y"], h=st["h"], x=st["x"], s=st["s"],
-                                  Cd=pr["Cd"], sigmasq=pr["sigmasq"], sigmasq_loc=hyp["sigmasq_loc"],
-                                  Gamma=Gamma)
-    done("v", st["v"])
-    st["s"] = G.resample_scales(lkey, x=st["x"], v=st["v"], h=st["h"], Y=data["Y"], Cd=pr["Cd"],
-                                sigmasq=pr["sigmasq"], nu_s=hyp["nu_s"], s_0=hyp["s_0"], Gamma=Gamma)
-    done("s", st["s"])
+    # 4-8: per-session steps on the local shard, launched without waiting for their verification
+    x_old = st["x"]
+    checks = {}
+
+    def run_from(step, strict):
+        if step == "z":
+            z_new, _, info = G.resample_stateseqs(key, x=x_old, mask=data["mask"], Ab=pr["Ab"], Q=pr["Q"],
+                                                  pi=pr["pi"], strict=strict, session_offset=off, return_info=True)
+            checks["z"] = info["boundary_err"] if (strict == "defer" and info["chunk_len"] > 0) else None
+            done("z", z_new)
+            if defer_obs and "sigmasq_done" not in checks:
+                wait("all")
+                S_y, msum = obs_stats()     # uses the OLD x (st["x"]), exactly as step 2 of the sweep does
+                if world > 1:
+                    S_y, msum = all_reduce_obs_stats(S_y, msum, group)
+                pr["sigmasq"] = G.sample_obs_variance(key, S_y, msum, nu_sigma=hyp["nu_sigma"],
+                                                      sigmasq_0=hyp["sigmasq_0"])
+                checks["sigmasq_done"] = None
+            st["z"] = z_new
+        st["x"], info = G.resample_latents(key, Y=data["Y"], mask=data["mask"], v=states["v"], h=states["h"],
+                                           z=st["z"], s=states["s"], Cd=pr["Cd"], sigmasq=pr["sigmasq"],
+                                           Ab=pr["Ab"], Q=pr["Q"], Gamma=Gamma, strict=strict,
+                                           session_offset=off, return_info=True)
+        checks["x"] = info["boundary_err"] if (strict == "defer" and info["chunk_len"] > 0) else None
+        done("x", st["x"])
+        st["h"] = G.resample_heading(key, Y=data["Y"], v=states["v"], x=st["x"], s=states["s"], Cd=pr["Cd"],
+                                     sigmasq=pr["sigmasq"], Gamma=Gamma, session_offset=off)
+        done("h", st["h"])
+        st["v"] = G.resample_location(key, mask=data["mask"], Y=data["Y"], h=st["h"], x=st["x"], s=states["s"],
+                                      Cd=pr["Cd"], sigmasq=pr["sigmasq"], sigmasq_loc=hyp["sigmasq_loc"],
+                                      Gamma=Gamma, session_offset=off)
+        done("v", st["v"])
+        st["s"] = G.resample_scales(key, x=st["x"], v=st["v"], h=st["h"], Y=data["Y"], Cd=pr["Cd"],
+                                    sigmasq=pr["sigmasq"], nu_s=hyp["nu_s"], s_0=hyp["s_0"], Gamma=Gamma,
+                                    session_offset=off)
+        done("s", st["s"])
+
+    run_from("z", "defer")
+    _verify_and_repair(checks, flags_dev, run_from, world)
+    return st, pr
+
+
+def arhmm_sweep(key, data, states, params, hyp, group=None, session_offset=None):
+    """One sweep of the AR-HMM with the continuous states fixed: resample_hdp_transitions,
+    resample_ar_params, resample_stateseqs (keypoint_slds.ipynb cell 9; depth_ar_hmm.ipynb cell 8 —
+    there `states['x']` is the data itself).  Sharded like `gibbs_sweep`: one packed all-reduce of
+    the AR statistics and the transition counts."""
+    rank, world = _world(group)
+    st, pr = dict(states), dict(params)
+    K = int(hyp["num_states"])
+    N = st["z"].shape[0]
+    off = session_offset_of(N, group) if session_offset is None else int(session_offset)
+    F = G.ar_sufficient_stats(nlags=hyp["nlags"], num_states=K, mask=data["mask"], x=st["x"], z=st["z"])
+    counts = G.transition_counts(z=st["z"], mask=data["mask"], num_states=K)
+    flags_dev = None
+    if world > 1:
+        F, _, _, counts, flags_dev = all_reduce_stats(F, None, None, counts, group, _local_verdict(F.device))
+    pr["betas"], pr["pi"] = G.sample_hdp_transitions(key, counts, pr["betas"], hyp["alpha"], hyp["kappa"],
+                                                     hyp["gamma"])
+    pr["Ab"], pr["Q"] = G.sample_ar_params(key, F, nlags=hyp["nlags"], nu_0=hyp["nu_0"], S_0=hyp["S_0"],
+                                           M_0=hyp["M_0"], K_0=hyp["K_0"])
+    checks = {}
+
+    def run_from(step, strict):
+        z_new, _, info = G.resample_stateseqs(key, x=st["x"], mask=data["mask"], Ab=pr["Ab"], Q=pr["Q"],
+                                              pi=pr["pi"], strict=strict, session_offset=off, return_info=True)
+        checks["z"] = info["boundary_err"] if (strict == "defer" and info["chunk_len"] > 0) else None
+        st["z"] = z_new
+
+    run_from("z", "defer")
+    _verify_and_repair(checks, flags_dev, run_from, world)
     return st, pr
 
 
@@ -160,7 +325,8 @@ def _copy_streams(dev):
 
 
 def gibbs_sweep_host(key, host_data, host_states, params, hyp, Gamma=None, group=None,
-                     n_sessions_global=None, out=None, device=None, timeline=None):
+                     n_sessions_global=None, session_offset=None, out=None, device=None, timeline=None,
+                     resident=None):
     """One sweep driven from HOST arrays (the drop-in situation: the caller keeps data and states
     in host memory, e.g. as NumPy / JAX-CPU arrays).
 
@@ -169,18 +335,24 @@ def gibbs_sweep_host(key, host_data, host_states, params, hyp, Gamma=None, group
     arrive while those steps compute — and every new state is sent back on a second copy stream
     the moment it is final, overlapping the steps that follow.  Host tensors should be pinned;
     `out` (dict of pinned host tensors, allocated when None) receives z, x, h, v, s.
+    `resident`: optional dict of DEVICE tensors (e.g. {'Y': ..., 'mask': ...}) that the caller keeps
+    on the GPU across sweeps; those arrays are not uploaded again.
     Returns (out, params_on_device, states_on_device); the host copies are complete on return."""
     dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
     main = torch.cuda.current_stream(dev)
     cs_in, cs_out = _copy_streams(dev)
-    hd = {a: torch.as_tensor(b) for a, b in host_data.items()}
+    resident = resident or {}
+    hd = {a: torch.as_tensor(b) for a, b in host_data.items() if a not in resident}
     hs = {a: torch.as_tensor(b) for a, b in host_states.items()}
     dd = {a: torch.empty(b.shape, dtype=b.dtype, device=dev) for a, b in hd.items()}
+    dd.update(resident)
     ds = {a: torch.empty(b.shape, dtype=b.dtype, device=dev) for a, b in hs.items()}
     cs_in.wait_stream(main)     # the fresh buffers may alias memory that queued kernels still use
     first = [("s", "x"), ("s", "z"), ("d", "mask")]
     with torch.cuda.stream(cs_in):
         for kind, a in first:
+            if kind == "d" and a not in hd:
+                continue
             (ds if kind == "s" else dd)[a].copy_((hs if kind == "s" else hd)[a], non_blocking=True)
         ev_xz = torch.cuda.Event()
         ev_xz.record(cs_in)
@@ -226,7 +398,8 @@ def gibbs_sweep_host(key, host_data, host_states, params, hyp, Gamma=None, group
         t.record_stream(cs_out)
 
     st, pr = gibbs_sweep(key, dd, ds, params, hyp, Gamma=Gamma, group=group,
-                         n_sessions_global=n_sessions_global, _wait=wait, _done=done, _mark=mark)
+                         n_sessions_global=n_sessions_global, session_offset=session_offset,
+                         _wait=wait, _done=done, _mark=mark)
     cs_out.synchronize()
     if timeline is not None:
         main.synchronize()

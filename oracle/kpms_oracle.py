@@ -671,12 +671,21 @@ def sample_crp_tablecounts(concentration, customers, colweights, randseq):
     return m
 
 
-def sample_ms(counts, betas, alpha, kappa, randseq, u_thin):
-    """transitions.py:23-33.  The host `np.random.binomial(ms_ii, rho_i)` is
-    realised as an explicit Bernoulli sum over injected uniforms
-    `u_thin[i, :ms_ii] < rho_i` (identical in distribution)."""
+def sample_ms(counts, betas, alpha, kappa, randseq, u_thin=None, thin=False):
+    """transitions.py:23-33.
+
+    thin=False (default) is what the reference RETURNS: its binomial thinning of the sticky diagonal
+    (transitions.py:28-31) is assigned through `newms.flat[::K+1][indices] = ...`, and slicing a
+    `flat` iterator yields a copy, so the assignment lands in a temporary and `newms` leaves the
+    function equal to the raw CRP table counts (pinned by tests/golden/reference_sweep_bench.npz,
+    where the reference's own sample_ms return value is recorded).
+    thin=True applies the thinning the code intends (the override correction of the sticky HDP-HMM
+    sampler): the host `np.random.binomial(ms_ii, rho_i)` realised as the Bernoulli sum
+    `u_thin[i, :ms_ii] < rho_i` over injected uniforms (identical in distribution)."""
     ms = sample_crp_tablecounts(alpha, np.array(counts, dtype=np.int64), np.array(betas), randseq)
     newms = ms.copy()
+    if not thin:
+        return newms
     K = ms.shape[0]
     for i in range(K):
         rho = betas[i] * alpha / (betas[i] * alpha + kappa)
@@ -696,7 +705,87 @@ def dirichlet_from_gammas(g):
     return g / g.sum(-1, keepdims=True)
 
 
+def resample_hdp_transitions(*, z, mask, betas, alpha, kappa, gamma, num_states, randseq, betas_g, pi_g,
+                             u_thin=None, thin=False):
+    """gibbs.py:148-151 -> transitions.py:35-40 with every draw injected: `randseq` for the CRP
+    (numba's np.random.random stream), `betas_g` (K,) and `pi_g` (K,K) the Gamma variates behind
+    the two jr.dirichlet calls (`u_thin`, `thin`: see sample_ms)."""
+    counts = count_transitions(num_states, mask[..., -z.shape[-1]:], z)
+    ms = sample_ms(counts, betas, alpha, kappa, randseq, u_thin, thin)
+    betas_new = dirichlet_from_gammas(np.asarray(betas_g, dtype=np.float64))
+    return betas_new, dirichlet_from_gammas(np.asarray(pi_g, dtype=np.float64)), counts, ms
+
+
+def sample_transitions(counts, alpha, kappa, pi_g):
+    """transitions.py:42-44: pi ~ Dir(counts + alpha + kappa I); returns (pi, concentration)."""
+    conc = counts + alpha + kappa * np.eye(counts.shape[0])
+    return dirichlet_from_gammas(np.asarray(pi_g, dtype=np.float64)), conc
+
+
+# ---- initialize.py ------------------------------------------------------------------
+
+def initial_location(Y):
+    """initialize.py:39-40."""
+    v = Y.mean(-2).copy()
+    v[..., 2:] = 0
+    return v
+
+
+def initial_heading(posterior_keypoints, anterior_keypoints, Y):
+    """initialize.py:42-45."""
+    post = Y[..., posterior_keypoints, :2].mean(-2)
+    ante = Y[..., anterior_keypoints, :2].mean(-2)
+    return vector_to_angle(ante - post)
+
+
+def initial_latents(*, Y, mask, v, h, latent_dim, sample_index, Gamma, whiten=True):
+    """initialize.py:20-37 with the frame sample injected (`np.random.choice(t*n, num_samples)`)
+    and the PCA restated from its definition (sklearn.decomposition.PCA, third-party: principal
+    axes of the sample covariance, largest-magnitude entry of each axis positive)."""
+    n, t, k, d = Y.shape
+    y = np.einsum('ji,ntjd->ntid', Gamma, inverse_affine_transform(Y, v, h))
+    yflat = y.reshape(n * t, (k - 1) * d)
+    ys = yflat[sample_index]
+    mean = ys.mean(0)
+    ev, evec = np.linalg.eigh(np.cov(ys.T))
+    comps = evec[:, ::-1].T[:latent_dim]
+    comps = comps * np.sign(comps[np.arange(latent_dim), np.abs(comps).argmax(1)])[:, None]
+    lat = (yflat - mean) @ comps.T
+    Cd = np.hstack([comps.T, mean[:, None]])
+    if whiten:
+        cov = np.cov(lat[mask.reshape(-1) > 0].T)
+        Lc = np.linalg.cholesky(cov)
+        lat = lat @ np.linalg.inv(Lc).T
+        Cd[:, :-1] = Cd[:, :-1] @ Lc
+    return lat.reshape(n, t, latent_dim), Cd
+
+
+def initial_ar_params(*, num_states, nu_0, S_0, M_0, K_0, chi2, normals, G):
+    """initialize.py:48-51: one sample_mniw draw from the prior per state."""
+    out = [sample_mniw(nu_0, S_0, M_0, K_0, chi2[k], normals[k], G[k]) for k in range(num_states)]
+    return np.stack([o[0] for o in out]), np.stack([o[1] for o in out])
+
+
 # ---- full-sweep convenience used by the CPU baseline ---------------------------
+
+def arhmm_sweep(data, states, params, hyp, draws):
+    """One AR-HMM sweep with x fixed: examples/keypoint_slds.ipynb cell 9 and
+    examples/depth_ar_hmm.ipynb cell 8 (resample_hdp_transitions, resample_ar_params,
+    resample_stateseqs)."""
+    L, K, mask = hyp['nlags'], hyp['num_states'], data['mask']
+    st, pr = dict(states), dict(params)
+    counts = count_transitions(K, mask[..., -st['z'].shape[-1]:], st['z'])
+    ms = sample_ms(counts, pr['betas'], hyp['alpha'], hyp['kappa'], draws['crp_u'])
+    pr['betas'] = dirichlet_from_gammas(draws['betas_g'](ms.sum(0) + hyp['gamma'] / K))
+    pr['pi'] = dirichlet_from_gammas(draws['pi_g'](hyp['alpha'] * pr['betas'][None, :] + counts
+                                                   + hyp['kappa'] * np.eye(K)))
+    pr['Ab'], pr['Q'] = resample_ar_params(nlags=L, num_states=K, mask=mask, x=st['x'], z=st['z'],
+                                           nu_0=hyp['nu_0'], S_0=hyp['S_0'], M_0=hyp['M_0'], K_0=hyp['K_0'],
+                                           chi2=draws['ar_chi2'], normals=draws['ar_normals'], G=draws['ar_G'])
+    st['z'], _ = resample_stateseqs(x=st['x'], mask=mask, Ab=pr['Ab'], Q=pr['Q'], pi=pr['pi'], u=draws['z_u'])
+    return st, pr
+
+
 
 def sweep(data, states, params, hyp, draws, Gamma):
     """One blocked Gibbs sweep in the order of examples/keypoint_slds.ipynb cell 12
@@ -714,7 +803,7 @@ def sweep(data, states, params, hyp, draws, Gamma):
                                           nu_sigma=hyp['nu_sigma'], sigmasq_0=hyp['sigmasq_0'], Gamma=Gamma,
                                           g=draws['sigmasq_g'])
     counts = count_transitions(K, mask[..., -st['z'].shape[-1]:], st['z'])
-    ms = sample_ms(counts, pr['betas'], hyp['alpha'], hyp['kappa'], draws['crp_u'], draws['thin_u'])
+    ms = sample_ms(counts, pr['betas'], hyp['alpha'], hyp['kappa'], draws['crp_u'])
     pr['betas'] = dirichlet_from_gammas(draws['betas_g'](ms.sum(0) + hyp['gamma'] / K))
     pr['pi'] = dirichlet_from_gammas(draws['pi_g'](hyp['alpha'] * pr['betas'][None, :] + counts
                                                    + hyp['kappa'] * np.eye(K)))

@@ -11,6 +11,10 @@ What is the reference's and what is not:
     inverse CDF of one pre-drawn uniform, jr.multivariate_normal is mean + cholesky(cov) @ normal
     (JAX's default method), tfd.VonMises.sample is Best-Fisher rejection on pre-drawn uniforms --
     the same conventions the oracle states for these third-party samplers;
+  * jr.dirichlet is the normalisation of pre-drawn gammas; the host-side np.random.binomial of
+    transitions.py:29 is replaced (by the generator script) with a Bernoulli sum over pre-drawn
+    uniforms; numba's private np.random.random stream inside sample_crp_tablecounts is the
+    reference's own (seeded, and replayed as the injected uniforms);
   * tfd.MultivariateNormalFullCovariance.log_prob is restated from its definition.
 """
 import sys
@@ -116,6 +120,25 @@ def gamma(key, a, dtype=None):
     return sa(np.array(g, dtype=np.float64))
 
 
+def dirichlet(key, alpha):
+    """jr.dirichlet = normalised Gamma(alpha, 1) variates; the injected gammas are consumed in call order."""
+    g = np.asarray(Ctx.draws["dirichlet_g"].pop(0), dtype=np.float64)
+    assert g.shape == np.asarray(alpha).shape, (g.shape, np.asarray(alpha).shape)
+    return sa(g / g.sum(-1, keepdims=True))
+
+
+def bernoulli_sum_binomial(u_thin, rho_all):
+    """Stand-in for the host-side np.random.binomial(n, p) of transitions.py:29 (called once, on the
+    non-empty diagonal cells): the entry for state i is the Bernoulli sum over the injected uniforms
+    u_thin[i, :n] — the convention the oracle and the CUDA kernel state for this draw.  The state
+    of an entry is recovered from its success probability (rho_all[i], distinct per state)."""
+    def binomial(n, p, size=None):
+        n, p = np.atleast_1d(np.asarray(n)), np.atleast_1d(np.asarray(p))
+        rows = [int(np.argmin(np.abs(rho_all - pp))) for pp in p]
+        return np.array([(u_thin[r, :int(nn)] < pp).sum() for r, nn, pp in zip(rows, n, p)], dtype=np.int64)
+    return binomial
+
+
 def categorical(key, logits):
     u = _take("uniform")[Ctx.scan_t]
     w = np.exp(np.asarray(logits, dtype=np.float64))
@@ -206,12 +229,35 @@ class VonMises:
         return sa(VonMises.sampler(self.loc, self.k, _take("vonmises")))
 
 
+def import_reference(*modules, ref="/root/reference"):
+    """Import modules of the REFERENCE's `keypoint_moseq` (a namespace package: it has no
+    __init__.py) although this repository ships a regular package of the same name (the drop-in
+    shim), which would otherwise win: the repository root and the working directory are taken off
+    sys.path while the reference is imported, and cached modules of that name are dropped."""
+    import importlib
+    import os
+    here = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    saved = list(sys.path)
+    sys.path[:] = [ref] + [p for p in saved if p not in ("", ".", ref) and os.path.abspath(p) != here
+                           and os.path.abspath(p) != os.getcwd()]
+    for name in [m for m in sys.modules if m == "keypoint_moseq" or m.startswith("keypoint_moseq.")]:
+        del sys.modules[name]
+    try:
+        out = [importlib.import_module("keypoint_moseq." + m) for m in modules]
+        for mod in out:
+            assert mod.__file__.startswith(ref), mod.__file__
+    finally:
+        sys.path[:] = saved
+    return out if len(out) > 1 else out[0]
+
+
 def install():
     """Register the stand-ins as `jax`, `jax.numpy`, ... in sys.modules."""
     jnp = _NpProxy(np)
     lax = types.SimpleNamespace(scan=scan, cond=cond, map=lax_map)
     jr = types.SimpleNamespace(split=split, normal=normal, multivariate_normal=multivariate_normal,
-                               gamma=gamma, categorical=categorical)
+                               gamma=gamma, categorical=categorical, dirichlet=dirichlet,
+                               PRNGKey=lambda seed: Key())
     jscipy = types.SimpleNamespace(linalg=types.SimpleNamespace(
         solve_triangular=lambda a, b, lower=False, **k: sa(scipy.linalg.solve_triangular(a, b, lower=lower))))
     config = types.SimpleNamespace(update=lambda *a, **k: None)

@@ -48,9 +48,9 @@ def _load_reference():
                  "tensorflow_probability.substrates.jax",
                  "tensorflow_probability.substrates.jax.distributions"]:
         sys.modules[name] = inert
-    sys.path.insert(0, REF)
-    T = importlib.import_module("keypoint_moseq.transitions")
-    U = importlib.import_module("keypoint_moseq.util")
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from jax_numpy_shim import import_reference   # the repository's own `keypoint_moseq` shim must not win
+    T, U = import_reference("transitions", "util", ref=REF)
     return T.sample_crp_tablecounts, U.count_transitions
 
 

@@ -2,9 +2,14 @@
 executed in the build container under tests/golden/jax_numpy_shim.py (JAX itself is not
 installed; see the shim's header for exactly what is and is not the reference's code).
 
-Every resample_* step of keypoint_slds.ipynb cell 12 except resample_hdp_transitions (whose
-numba part is pinned separately by make_reference_pins.py) is run ONCE on the same small problem,
-with injected draws; inputs, draws and the reference's outputs go to reference_sweep.npz.
+Every resample_* step of keypoint_slds.ipynb cell 12 is run ONCE on the same problem, with injected
+draws; inputs, draws and the reference's outputs go to
+  reference_sweep.npz        small shapes (N=3, T=48, k=5, D=4, L=2, K=5), without resample_hdp_transitions
+                             (its numba part is pinned separately by make_reference_pins.py);
+  reference_sweep_bench.npz  the shapes the benchmark dispatches to (D=10, L=3 -> n=30 Kalman, 48-wide
+                             emission tile; k=16; K=8; T=400, ragged), including resample_hdp_transitions
+                             (numba's seeded stream replayed as the injected uniforms, the host-side
+                             binomial thinning and the two Dirichlet draws injected, see the shim).
 
     python tests/golden/make_reference_sweep.py
 """
@@ -25,16 +30,15 @@ from keypointmoseq_b200.synthetic import simulate, default_hypparams   # noqa: E
 from oracle import kpms_oracle as O                    # noqa: E402  (only its von Mises restatement)
 
 
-def main():
+def main(shape=(3, 48, 5, 2, 4, 2, 5, 6), fname="reference_sweep.npz", sim_seed=77, draw_seed=4242, with_hdp=False):
     shim.install()
     shim.VonMises.sampler = O.sample_vonmises
-    sys.path.insert(0, "/root/reference")
-    G = importlib.import_module("keypoint_moseq.gibbs")
+    G, U, TR = shim.import_reference("gibbs", "util", "transitions")
 
-    N, T, k, dk, D, L, K, R = 3, 48, 5, 2, 4, 2, 5, 6
-    data, st, pr, Gamma = simulate(77, N, T, k=k, dk=dk, D=D, L=L, K=K, ragged=True, dtype=np.float64)
+    N, T, k, dk, D, L, K, R = shape
+    data, st, pr, Gamma = simulate(sim_seed, N, T, k=k, dk=dk, D=D, L=L, K=K, ragged=True, dtype=np.float64)
     trans, ar, obs, loc = default_hypparams(D, L, K)
-    rng = np.random.default_rng(4242)
+    rng = np.random.default_rng(draw_seed)
     n = D * L
     f = lambda a: shim.sa(np.array(a, dtype=np.float64))
     r32 = lambda a: np.asarray(a, dtype=np.float32).astype(np.float64)   # float32-representable: the CUDA path stores these in fp32
@@ -98,7 +102,6 @@ def main():
     out.update(d_obsparams_w=wc, r_obsparams_Cd=np.asarray(Cdr))
 
     # (f)2: diagnostics (util.py:232-275, 41-45)
-    U = importlib.import_module("keypoint_moseq.util")
     shim.Ctx.draws, shim.Ctx.vmap, shim.Ctx.scan_t = {}, [], None
     lj = U.log_joint_likelihood(Y=Y, mask=mask, x=x, s=s, v=v, h=h, z=z, pi=pi, Ab=Ab, Q=Q, Cd=Cd, sigmasq=sigmasq,
                                 sigmasq_loc=float(loc["sigmasq_loc"]), nu_s=float(obs["nu_s"]), s_0=float(obs["s_0"]))
@@ -106,10 +109,54 @@ def main():
     usage, durations = U.stateseq_stats(np.asarray(z), np.asarray(mask))
     out.update(r_usage=np.asarray(usage, dtype=np.int64), r_durations=np.asarray(durations, dtype=np.int64))
 
-    path = os.path.join(HERE, "reference_sweep.npz")
+    if with_hdp:
+        # 3: resample_hdp_transitions (gibbs.py:148-151 -> util.count_transitions (numba),
+        # transitions.sample_hdp_transitions: numba CRP with its private seeded stream, host binomial
+        # thinning, two jr.dirichlet draws)
+        from numba import njit
+
+        @njit
+        def seed_numba(sd):
+            np.random.seed(sd)
+
+        # kappa chosen so that the binomial thinning of the diagonal keeps a real fraction of the tables
+        alpha, kappa, gamma = float(trans["alpha"]), 50.0, float(trans["gamma"])
+        betas = f(pr["betas"])
+        crp_seed = 9091
+        counts_ref = np.asarray(U.count_transitions(K, np.array(mask[..., -z.shape[-1]:]), np.array(z)))
+        tot = int(counts_ref.sum())
+        randseq = np.random.RandomState(crp_seed).random_sample(tot)       # = numba's stream after seed_numba(crp_seed)
+        u_thin = rng.random((K, 4096))
+        rho_all = np.asarray(betas) * alpha / (np.asarray(betas) * alpha + kappa)
+        # what the reference's sample_ms returns: the raw CRP counts (its thinning writes to a temporary)
+        ms_expected = O.sample_ms(counts_ref.astype(np.int64), np.asarray(betas), alpha, kappa, randseq)
+        gb = rng.gamma(ms_expected.sum(0) + gamma / K)
+        gp = rng.gamma(alpha * (gb / gb.sum())[None, :] + counts_ref + kappa * np.eye(K))
+        real_binomial, real_sample_ms, seen = np.random.binomial, TR.sample_ms, {}
+
+        def recording_sample_ms(*a, **kw):       # the reference's own sample_ms; its return value is recorded
+            seen["ms"] = np.asarray(real_sample_ms(*a, **kw)).copy()
+            return seen["ms"]
+        TR.sample_ms = recording_sample_ms
+        np.random.binomial = shim.bernoulli_sum_binomial(u_thin, rho_all)
+        try:
+            seed_numba(crp_seed)
+            shim.Ctx.draws, shim.Ctx.vmap, shim.Ctx.scan_t = {"dirichlet_g": [gb, gp]}, [], None
+            betas_r, pi_r = G.resample_hdp_transitions(key, z=z, mask=mask, betas=betas, alpha=alpha, kappa=kappa,
+                                                       gamma=gamma, num_states=K)
+        finally:
+            np.random.binomial, TR.sample_ms = real_binomial, real_sample_ms
+        assert np.array_equal(seen["ms"], ms_expected), "the injected Dirichlet gammas were drawn for other table counts"
+        out.update(hyp_alpha=np.float64(alpha), hyp_kappa=np.float64(kappa), hyp_gamma=np.float64(gamma),
+                   betas=np.asarray(betas), d_hdp_randseq=randseq, d_hdp_u_thin=u_thin, d_hdp_betas_g=gb,
+                   d_hdp_pi_g=gp, r_hdp_counts=counts_ref, r_hdp_ms=seen["ms"], r_hdp_betas=np.asarray(betas_r), r_hdp_pi=np.asarray(pi_r))
+
+    path = os.path.join(HERE, fname)
     np.savez_compressed(path, **{a: np.asarray(b) for a, b in out.items()})
     print("wrote", path, os.path.getsize(path), "bytes")
 
 
 if __name__ == "__main__":
     main()
+    main(shape=(3, 400, 16, 2, 10, 3, 8, 8), fname="reference_sweep_bench.npz", sim_seed=78, draw_seed=4343,
+         with_hdp=True)

@@ -237,19 +237,58 @@ def test_crp_tablecounts_exact(G):
     randseq = H.f32r(rng.random(int(counts.sum())))
     u_thin = H.f32r(rng.random((K, 4096)))
     want_raw = O.sample_crp_tablecounts(alpha, counts, betas, randseq)
-    want = O.sample_ms(counts, betas, alpha, kappa, randseq, u_thin)
-    ms, ms_raw, ovf = G.sample_ms(0, T_(counts), T_(betas), alpha, kappa,
-                                  draws={'randseq': T_(randseq), 'u_thin': T_(u_thin)})
-    assert np.array_equal(N_(ms_raw), want_raw) and np.array_equal(N_(ms), want) and int(ovf) == 0
+    # default = what the reference returns (its thinning is lost in a temporary): the raw counts
+    ms0, ms_raw0 = G.sample_ms(0, T_(counts), T_(betas), alpha, kappa, draws={'randseq': T_(randseq)})
+    assert np.array_equal(N_(ms0), want_raw) and np.array_equal(N_(ms_raw0), want_raw)
+    assert np.array_equal(O.sample_ms(counts, betas, alpha, kappa, randseq), want_raw)
+    # thin=True: the intended binomial thinning of the sticky diagonal, as Bernoulli sums
+    want = O.sample_ms(counts, betas, alpha, kappa, randseq, u_thin, thin=True)
+    ms, ms_raw = G.sample_ms(0, T_(counts), T_(betas), alpha, kappa,
+                             draws={'randseq': T_(randseq), 'u_thin': T_(u_thin)}, thin=True)
+    assert np.array_equal(N_(ms_raw), want_raw) and np.array_equal(N_(ms), want)
+    assert (want.diagonal() < want_raw.diagonal()).any()
+    # injected draws that are too short are refused loudly, not silently capped
+    from keypointmoseq_b200._lib import KpmsError
+    with pytest.raises(KpmsError):
+        G.sample_ms(0, T_(counts), T_(betas), alpha, kappa, draws={'randseq': T_(randseq[:-5]), 'u_thin': T_(u_thin)})
+    with pytest.raises(KpmsError):
+        G.sample_ms(0, T_(counts), T_(betas), alpha, kappa, draws={'randseq': T_(randseq), 'u_thin': T_(u_thin[:, :2])},
+                    thin=True)
     # Dirichlet concentrations of transitions.py:38-39 from the same statistics
     gb = rng.gamma(want.sum(0) + 1e3 / K)
     betas_new = gb / gb.sum()
     conc = alpha * betas_new[None] + counts + kappa * np.eye(K)
     gp = rng.gamma(conc)
-    b, pi = G.sample_hdp_transitions(0, T_(counts), T_(betas), alpha, kappa, 1e3,
+    b, pi = G.sample_hdp_transitions(0, T_(counts), T_(betas), alpha, kappa, 1e3, thin=True,
                                      draws={'randseq': T_(randseq), 'u_thin': T_(u_thin), 'betas_g': T_(gb),
                                             'pi_g': T_(gp)})
     assert np.allclose(N_(b), betas_new, rtol=1e-13) and np.allclose(N_(pi), gp / gp.sum(1, keepdims=True), rtol=1e-13)
+
+
+def test_crp_philox_equals_filled_uniforms(G):
+    """The in-kernel Philox draws are the numbers kpms_fill_uniform would have written: the table
+    counts from kpms_crp_tablecounts_philox equal those from pre-filled uniforms, bit for bit
+    (raw counts and, with thin=True, the thinned diagonal)."""
+    import torch
+    from keypointmoseq_b200 import distributions as dist
+    rng = np.random.default_rng(32)
+    K = 9
+    counts = rng.integers(0, 50, size=(K, K))
+    counts[np.arange(K), np.arange(K)] += rng.integers(500, 20000, size=K)
+    counts[2] = 0
+    betas = rng.dirichlet(np.ones(K))
+    alpha, kappa, seed = 100.0, 300.0, 77
+    randseq = dist.fill_uniform((int(counts.sum()),), seed, dist.STREAM_CRP, "cuda")
+    cap = 4096
+    u_thin = torch.empty((K, cap), device="cuda")
+    for i in range(K):   # row i of the thinning draws = numbers (i << 32) .. of the stream
+        u_thin[i] = dist.fill_uniform((1, cap), seed, dist.STREAM_THIN, "cuda", first_row=(i << 32) // cap)[0]
+    a, a_raw = G.sample_ms(seed, T_(counts), T_(betas), alpha, kappa, thin=True)
+    b, b_raw = G.sample_ms(seed, T_(counts), T_(betas), alpha, kappa, thin=True, draws={'randseq': randseq, 'u_thin': u_thin})
+    assert torch.equal(a_raw, b_raw) and torch.equal(a, b)
+    assert int(a_raw.sum()) > 0 and (N_(a).diagonal() < N_(a_raw).diagonal()).any()
+    c, c_raw = G.sample_ms(seed, T_(counts), T_(betas), alpha, kappa)      # reference behaviour: no thinning
+    assert torch.equal(c, a_raw) and torch.equal(c_raw, a_raw)
 
 
 def test_resample_hdp_transitions_philox_is_valid(G):
@@ -475,7 +514,7 @@ def test_ar_stats_empty_states_and_ragged(G, D, L, K, T):
     assert np.array_equal(got, again)
 
 
-def test_hmm_backward_chunks_are_repaired(G, monkeypatch):
+def test_hmm_backward_chunks_are_repaired(G, options):
     """With no warm-up at all every sampler chunk starts from the wrong carry; the device-side
     repair pass must then reproduce, bit for bit, what well warmed-up chunks give."""
     import torch
@@ -483,9 +522,9 @@ def test_hmm_backward_chunks_are_repaired(G, monkeypatch):
     kw = dict(ll=T_(ll), mask=T_(mask), pi=T_(pi), u=T_(u), chunk_len=300, burn_in=256, strict=False,
               return_info=True)
     z_ref, l_ref, i_ref = G.sample_hmm_stateseqs(**kw)
-    monkeypatch.setenv("KPMS_HMM_BWD_BURN", "0")
+    options("hmm_bwd_burn", 0)
     z_rep, l_rep, i_rep = G.sample_hmm_stateseqs(**kw)
-    monkeypatch.setenv("KPMS_HMM_BWD_BURN", "3")
+    options("hmm_bwd_burn", 3)
     z_rep3, _, _ = G.sample_hmm_stateseqs(**kw)
     torch.cuda.synchronize()
     assert torch.equal(z_ref, z_rep) and torch.equal(z_ref, z_rep3)
@@ -495,9 +534,9 @@ def test_hmm_backward_chunks_are_repaired(G, monkeypatch):
     assert (N_(z_rep)[valid] == zo[valid]).mean() >= 0.999
 
 
-def test_alternative_kernel_paths_agree(G, monkeypatch):
-    """The kernels kept behind environment switches stay correct: KPMS_KALMAN_IMPL=0 (CTA-per-chunk
-    shared-memory Kalman filter) and KPMS_HMM_TC=0 (CUDA-core chunked HMM filter)."""
+def test_alternative_kernel_paths_agree(G, options):
+    """The kernels kept behind library options stay correct: kalman_impl=0 (CTA-per-chunk
+    shared-memory Kalman filter) and hmm_tc=0 (CUDA-core chunked HMM filter)."""
     import torch
     d, s, p, Gm = H.problem(seed=61, N=3, T=700, k=8, dk=2, D=10, L=3, K=8, ragged=True)
     rng = np.random.default_rng(3)
@@ -506,14 +545,14 @@ def test_alternative_kernel_paths_agree(G, monkeypatch):
               Cd=T_(p['Cd']), sigmasq=T_(p['sigmasq']), Ab=T_(p['Ab']), Q=T_(p['Q']), Gamma=T_(Gm),
               draws={'w': T_(w), 'w_last': T_(wl)}, chunk_len=128, burn_in=160, strict=False)
     x0 = G.resample_latents(0, **kw)
-    monkeypatch.setenv("KPMS_KALMAN_IMPL", "0")
+    options("kalman_impl", 0)
     x1 = G.resample_latents(0, **kw)
-    monkeypatch.delenv("KPMS_KALMAN_IMPL")
+    options("kalman_impl", 1)
     assert float((x0 - x1).abs().max()) < 1e-5 * max(1.0, float(x0.abs().max()))
     ll, mask, pi, u = _hmm_case(31, N=4, T=2400, K=40, ragged=True)
     hk = dict(ll=T_(ll), mask=T_(mask), pi=T_(pi), u=T_(u), chunk_len=300, burn_in=256, strict=False, return_info=True)
     z0, l0, _ = G.sample_hmm_stateseqs(**hk)
-    monkeypatch.setenv("KPMS_HMM_TC", "0")
+    options("hmm_tc", 0)
     z1, l1, i1 = G.sample_hmm_stateseqs(**hk)
     torch.cuda.synchronize()
     assert float(i1['boundary_err']) < 1e-5
