@@ -406,3 +406,30 @@ def gibbs_sweep_host(key, host_data, host_states, params, hyp, Gamma=None, group
         for label, e in marks:
             timeline[label] = ev_start.elapsed_time(e)
     return out, pr, st
+
+
+def arhmm_sweep_host(key, host_data, host_states, params, hyp, group=None, session_offset=None, out=None,
+                     device=None):
+    """`arhmm_sweep` driven from HOST arrays: x, z and mask go up (pinned buffers, copy stream), the
+    new z comes back.  Returns (out, params_on_device, states_on_device)."""
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    main = torch.cuda.current_stream(dev)
+    cs_in, cs_out = _copy_streams(dev)
+    cs_in.wait_stream(main)
+    with torch.cuda.stream(cs_in):
+        dd = {"mask": torch.as_tensor(host_data["mask"]).to(dev, non_blocking=True)}
+        ds = {a: torch.as_tensor(host_states[a]).to(dev, non_blocking=True) for a in ("x", "z")}
+    main.wait_stream(cs_in)
+    for t in list(dd.values()) + list(ds.values()):
+        t.record_stream(main)
+    st, pr = arhmm_sweep(key, dd, ds, params, hyp, group=group, session_offset=session_offset)
+    if out is None:
+        out = {}
+    if "z" not in out:
+        out["z"] = torch.empty(st["z"].shape, dtype=st["z"].dtype).pin_memory()
+    cs_out.wait_stream(main)
+    with torch.cuda.stream(cs_out):
+        out["z"].copy_(st["z"], non_blocking=True)
+    st["z"].record_stream(cs_out)
+    cs_out.synchronize()
+    return out, pr, st

@@ -52,6 +52,12 @@ def _worker(rank, world, port, out):
         two_stage_ok = bool(torch.equal(F3, F2) and torch.equal(c3, c2) and torch.equal(S3, S2) and
                             torch.equal(m3.reshape(-1), m2.reshape(-1)) and torch.equal(F4, F2) and
                             torch.equal(S4, S2) and torch.equal(c4, c2))
+        # verdict flags of the chunked HMM passes ride in the same all-reduce; shard offsets from sizes
+        flags = torch.tensor([float(rank == 1), 1.0 - float(rank == 1), 1.0], dtype=torch.float64)
+        F5, S5, m5, c5, fsum = parallel.all_reduce_stats(F, S_y, msum, counts, None, flags)
+        flags_ok = bool(torch.equal(F5, F2) and torch.equal(c5, c2) and fsum.tolist() == [1.0, 1.0, 2.0])
+        off = parallel.session_offset_of(hi - lo)
+        off_ok = (off == lo)
         Ab, Q = G.sample_ar_params((3, 1), F2, nlags=L, nu_0=hp['nu_0'], S_0=torch.as_tensor(hp['S_0']),
                                    M_0=torch.as_tensor(hp['M_0']), K_0=torch.as_tensor(hp['K_0']))
         sig = G.sample_obs_variance((3, 1), S2, m2, nu_sigma=hp['nu_sigma'], sigmasq_0=hp['sigmasq_0'])
@@ -61,6 +67,7 @@ def _worker(rank, world, port, out):
             Ff, Sf, mf, cf = _local_stats(d, s, p, Gm, L, K, 0, N)
             out.put(dict(F_err=float((F2 - Ff).abs().max() / Ff.abs().max()), S_err=float((S2 - Sf).abs().max()),
                          m_ok=bool(torch.equal(m2, mf)), c_ok=bool(torch.equal(c2, cf)), two_stage_ok=two_stage_ok,
+                         flags_ok=flags_ok, off_ok=off_ok,
                          same_params=bool(all(torch.equal(g, Ab) for g in gathered)),
                          finite=bool(torch.isfinite(Ab).all() and torch.isfinite(Q).all() and (sig > 0).all())))
     finally:
@@ -90,3 +97,31 @@ def test_packed_allreduce_and_replicated_draws_gloo():
         assert p.exitcode == 0
     assert res["F_err"] < 1e-13 and res["S_err"] < 1e-9
     assert res["m_ok"] and res["c_ok"] and res["same_params"] and res["finite"] and res["two_stage_ok"]
+    assert res["flags_ok"] and res["off_ok"]
+
+
+def test_shared_hmm_warmup_moves_identically_from_summed_verdicts():
+    """The warm-up multiplier of the chunked HMM passes is a function of all-reduced verdict counts
+    only, so every rank changes it at the same sweep."""
+    from keypointmoseq_b200 import gibbs as G, parallel
+    saved = dict(G._HMM_ADAPT)
+    try:
+        G._HMM_ADAPT.update(boost=1, streak=0)
+        parallel._apply_verdicts(1.0, 6.0, 8.0)          # one of eight ranks failed its check
+        assert G._HMM_ADAPT["boost"] == 2 and G._HMM_ADAPT["streak"] == 0
+        for _ in range(7):
+            parallel._apply_verdicts(0.0, 8.0, 8.0)
+        assert G._HMM_ADAPT["boost"] == 2 and G._HMM_ADAPT["streak"] == 7
+        parallel._apply_verdicts(0.0, 7.0, 8.0)          # one rank not comfortable: the streak starts over
+        assert G._HMM_ADAPT["streak"] == 0
+        for _ in range(8):
+            parallel._apply_verdicts(0.0, 8.0, 8.0)
+        assert G._HMM_ADAPT["boost"] == 1
+        parallel._apply_verdicts(0.0, 0.0, 0.0)          # nothing reported (sequential passes): no change
+        assert G._HMM_ADAPT == {"boost": 1, "streak": 0}
+        for _ in range(10):
+            parallel._apply_verdicts(3.0, 0.0, 8.0)
+        assert G._HMM_ADAPT["boost"] == G.HMM_MAX_BOOST
+    finally:
+        G._HMM_ADAPT.clear()
+        G._HMM_ADAPT.update(saved)
