@@ -380,6 +380,21 @@ def main():
         td.all_gather_object(per_rank, {"ms": round(my_ms, 2), "fallbacks": fallbacks_timed,
                                         "hmm_burn_boost": G._HMM_ADAPT["boost"]})
     clocks = clk.summary()
+    # one more sweep with an event after every phase: where the time of a sweep goes (ms since its start)
+    timeline = None
+    if slds:
+        marks = []
+
+        def _mark(label):
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            marks.append((label, e, time.perf_counter()))
+        torch.cuda.synchronize()
+        _mark("start")
+        parallel.gibbs_sweep((0, 999), d, ss, pp, hyp, Gamma=Gm, session_offset=off, _mark=_mark)
+        torch.cuda.synchronize()
+        timeline = {lab: {"gpu_ms": round(marks[0][1].elapsed_time(e), 3), "host_ms": round((t - marks[0][2]) * 1e3, 3)}
+                    for lab, e, t in marks[1:]}
 
     # ---- per-step breakdown and rooflines (rank-local)
     def timed(fn, reps):
@@ -550,7 +565,7 @@ def main():
                 "vs_baseline": None, "dtype": "f64 (Kalman, statistics) / f32 (HMM messages, emission GEMM)",
                 "data": "synthetic", "config": cfg, "clocks": clocks, "e2e": e2e, "e2e_resident": e2e_res,
                 "gpu_launches": launches, "roofline": roofline, "roofline_per_kernel": per_kernel,
-                "cpu_baseline": cpu, "breakdown_ms": bd}
+                "cpu_baseline": cpu, "breakdown_ms": bd, "sweep_timeline": timeline}
         print(json.dumps(line), flush=True)
     if world > 1:
         td.destroy_process_group()

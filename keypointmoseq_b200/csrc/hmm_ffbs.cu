@@ -22,6 +22,13 @@
 #include "common.cuh"
 #include <stdlib.h>
 
+bool kpms_hmm_big_supported(int Tm, int K, int chunk_len);  // hmm_big.cu
+int kpms_hmm_big_kp(int K);
+int kpms_hmm_big(const float* ll, const float* mask, long long mask_stride, const double* pi, const float* u,
+                 const int* tv, int N, int Tm, int K, int Kl, int chunk_len, int burn_in, int bwd_burn, int nch,
+                 float* pf, float* pT, float* alphan, double* llpart, float* bnd, int* carry_warm, int* carry_out,
+                 int* z, int forward_only, cudaStream_t st);
+
 #define HMM_STAGE 16    // frames of ll / mask / u staged ahead by the forward pass
 #define HMM_BRING 128   // frames of stay bits / u / mask staged ahead by the backward sampler
 
@@ -46,6 +53,7 @@ struct HmmWs {
   // chunk chains u = n*nch + t/chunk_len are interleaved 128 at a time so that a CTA stepping 128
   // chains moves whole 512-byte lines:  float4 index (((u/128)*CL + t%CL) * K/4 + j/4) * 128 + u%128.
   int tiled, tile_cl, tile_nch;
+  int Kl;  // layout width of the messages and of the boundary records: K rounded up to a multiple of 4
 };
 
 __device__ __forceinline__ size_t hmm_msg_base4(const HmmWs& ws, int n, int t, int Tm, int K) {
@@ -53,11 +61,12 @@ __device__ __forceinline__ size_t hmm_msg_base4(const HmmWs& ws, int n, int t, i
   if (!ws.tiled) return ((size_t)n * Tm + t) * (K >> 2);
   const int cc = t / ws.tile_cl, r = t - cc * ws.tile_cl;
   const int u = n * ws.tile_nch + cc;
-  return (((size_t)(u >> 7) * ws.tile_cl + r) * (K >> 2)) * 128 + (u & 127);
+  return (((size_t)(u >> 7) * ws.tile_cl + r) * (ws.Kl >> 2)) * 128 + (u & 127);
 }
 
 static size_t hmm_layout(int N, int Tm, int K, int chunk_len, void* base, HmmWs* ws) {
   const int nch = hmm_nchunks(Tm, chunk_len);
+  const int Kl = (K + 3) & ~3;
   size_t off = 0;
   char* b = (char*)base;
   auto take = [&](size_t bytes) {
@@ -67,17 +76,18 @@ static size_t hmm_layout(int N, int Tm, int K, int chunk_len, void* base, HmmWs*
   };
   void* p;
   // chunked mode may use the tiled layout: units padded to 128, chunks to their full length
-  const size_t msg = (nch > 1) ? (size_t)((N * (size_t)nch + 127) / 128 * 128) * chunk_len * K : (size_t)N * Tm * K;
+  const size_t msg = (nch > 1) ? (size_t)((N * (size_t)nch + 127) / 128 * 128) * chunk_len * Kl : (size_t)N * Tm * K;
   p = take(msg * sizeof(float)); if (ws) ws->alphan = (float*)p;
-  p = take((size_t)K * K * sizeof(float)); if (ws) ws->pf = (float*)p;
-  p = take((size_t)K * K * sizeof(float)); if (ws) ws->pT = (float*)p;
+  const size_t KPP = (K > 128 && K <= 512) ? (size_t)kpms_hmm_big_kp(K) : (size_t)K;  // padded fp32 tables of hmm_big.cu
+  p = take(KPP * KPP * sizeof(float)); if (ws) ws->pf = (float*)p;
+  p = take(KPP * KPP * sizeof(float)); if (ws) ws->pT = (float*)p;
   p = take((size_t)N * Tm * 4 * sizeof(unsigned)); if (ws) ws->stay = (unsigned*)p;
   p = take((size_t)N * nch * sizeof(double)); if (ws) ws->llpart = (double*)p;
-  p = take((size_t)N * nch * 2 * K * sizeof(float)); if (ws) ws->bnd = (float*)p;
+  p = take((size_t)N * nch * 2 * Kl * sizeof(float)); if (ws) ws->bnd = (float*)p;
   p = take((size_t)N * sizeof(int)); if (ws) ws->tv = (int*)p;
   p = take((size_t)N * nch * sizeof(int)); if (ws) ws->carry_warm = (int*)p;
   p = take((size_t)N * nch * sizeof(int)); if (ws) ws->carry_out = (int*)p;
-  if (nch > 1 && K <= 128) {
+  if (nch > 1 && K <= 104) {
     p = take(msg * sizeof(float)); if (ws) ws->Tbuf = (float*)p;
     p = take(msg * sizeof(float)); if (ws) ws->lltile = (float*)p;
   } else if (ws) {
@@ -88,6 +98,7 @@ static size_t hmm_layout(int N, int Tm, int K, int chunk_len, void* base, HmmWs*
     ws->tiled = 0;
     ws->tile_cl = chunk_len;
     ws->tile_nch = nch;
+    ws->Kl = Kl;
   }
   return off;
 }
@@ -182,7 +193,7 @@ __global__ void __launch_bounds__(KP, 3)
   double logtot = 0.0;
 #pragma unroll 1
   for (int t = tb; t < t1; t++) {
-    if (t == t0 && cc > 0 && j < K) ws.bnd[((size_t)(n * nch + cc) * 2 + 0) * K + j] = in_pot;
+    if (t == t0 && cc > 0 && j < K) ws.bnd[((size_t)(n * nch + cc) * 2 + 0) * ws.Kl + j] = in_pot;
     const int buf = t & 1, slot = t % HMM_STAGE;
     float cmax = wmax_s[buf][0];
 #pragma unroll
@@ -261,7 +272,7 @@ __global__ void __launch_bounds__(KP, 3)
     if (m > 0.0f) in_pot = tot * inv;
     if (store && j == 0 && m > 0.0f) logtot += (double)__logf(norm) + (double)cmax;
   }
-  if (nch > 1 && j < K) ws.bnd[((size_t)(n * nch + cc) * 2 + 1) * K + j] = in_pot;
+  if (nch > 1 && j < K) ws.bnd[((size_t)(n * nch + cc) * 2 + 1) * ws.Kl + j] = in_pot;
   if (j == 0) ws.llpart[(size_t)n * nch + cc] = logtot;
   asm volatile("cp.async.wait_group 0;\n" ::);
   (void)loglik;
@@ -282,8 +293,8 @@ __global__ void hmm_finish_kernel(HmmWs ws, int nch, int K, int chunk_len, doubl
   const int tvn = ws.tv[n];
   for (int c = 0; c + 1 < nch; c++) {
     if ((c + 1) * chunk_len >= tvn) break;  // the next chunk starts inside the trailing padding
-    const float* a = ws.bnd + ((size_t)(n * nch + c) * 2 + 1) * K;
-    const float* b = ws.bnd + ((size_t)(n * nch + c + 1) * 2 + 0) * K;
+    const float* a = ws.bnd + ((size_t)(n * nch + c) * 2 + 1) * ws.Kl;
+    const float* b = ws.bnd + ((size_t)(n * nch + c + 1) * 2 + 0) * ws.Kl;
     for (int e = threadIdx.x; e < K; e += blockDim.x) {
       const float d = fabsf(a[e] - b[e]);
       worst = (d != d) ? INFINITY : fmaxf(worst, d);  // a NaN boundary must fail the check, not vanish in fmax
@@ -361,7 +372,7 @@ __device__ __forceinline__ int hmm_backward_walk(const float* __restrict__ mk_n,
       float run = 0.0f;
       float al4[4] = {0.f, 0.f, 0.f, 0.f};
       if (PER == 4 && ws.tiled) {  // the lane's four states are one 16-byte piece of the tile
-        if (lane * 4 < K) {
+        if (lane * 4 < ws.Kl) {
           const float4 v = __ldg(reinterpret_cast<const float4*>(ws.alphan) + mb4 + (size_t)lane * 128);
           al4[0] = v.x; al4[1] = v.y; al4[2] = v.z; al4[3] = v.w;
         }
@@ -641,7 +652,7 @@ int kpms_hmm_ffbs_impl(const float* ll, int ll_tiled, const float* mask, int64_t
   KPMS_REQUIRE(N > 0 && Tm > 0 && K > 0 && mask_stride >= Tm, KPMS_ERR_SHAPE);
   KPMS_REQUIRE(K <= 1024, KPMS_ERR_UNSUPPORTED);
   KPMS_REQUIRE(chunk_len <= 0 || burn_in >= 0, KPMS_ERR_SHAPE);
-  if (K > 128) chunk_len = 0;  // the generic kernel walks whole sessions
+  if (K > 128 && !kpms_hmm_big_supported(Tm, K, chunk_len)) chunk_len = 0;  // the generic kernel walks whole sessions
   // chunked mode reports what it could not verify through boundary_err: it is not optional there
   KPMS_REQUIRE(hmm_nchunks(Tm, chunk_len) == 1 || boundary_err != nullptr, KPMS_ERR_NULL);
   HmmWs ws;
@@ -656,6 +667,21 @@ int kpms_hmm_ffbs_impl(const float* ll, int ll_tiled, const float* mask, int64_t
   if (K <= 128) KPMS_HMM_GO(128);
 #undef KPMS_HMM_GO
   if (boundary_err) KPMS_CUDA(cudaMemsetAsync(boundary_err, 0, sizeof(float), st));
+  if (kpms_hmm_big_supported(Tm, K, chunk_len)) {
+    // chunk-parallel, 32 chains per CTA (hmm_big.cu); same verification protocol as K <= 128
+    const int nch = hmm_nchunks(Tm, chunk_len);
+    hmm_tv_kernel<<<N, 256, 0, st>>>(mask, mask_stride, Tm, ws.tv);
+    int rc = kpms_last_launch();
+    if (rc) return rc;
+    rc = kpms_hmm_mask_check(mask, mask_stride, Tm, ws.tv, N, (unsigned*)boundary_err, st);
+    if (rc) return rc;
+    rc = kpms_hmm_big(ll, mask, mask_stride, pi, u, ws.tv, N, Tm, K, ws.Kl, chunk_len, burn_in, kpms_opts.hmm_bwd_burn,
+                      nch, ws.pf, ws.pT, ws.alphan, ws.llpart, ws.bnd, ws.carry_warm, ws.carry_out, z,
+                      kpms_opts.hmm_flags & 1, st);
+    if (rc) return rc;
+    hmm_finish_kernel<<<N, 128, 0, st>>>(ws, nch, K, chunk_len, loglik, (unsigned*)boundary_err);
+    return kpms_last_launch();
+  }
   hmm_prep_pi_kernel<<<(K * K + 255) / 256, 256, 0, st>>>(pi, K, ws.pf, ws.pT);
   int rc = kpms_last_launch();
   if (rc) return rc;

@@ -32,6 +32,8 @@ struct HmmTcArgs {
   double* llpart;  // [N][nch]
   float* bnd;      // [N][nch][2][K]
   int N, Tm, K, chunk_len, burn_in, nch;
+  int Kt;  // true number of states; K is the layout width (Kt rounded up to a multiple of 4, padded
+           // states carry ll = -inf and zero transition probability)
 };
 
 template <int KD, int NP>
@@ -62,7 +64,7 @@ __device__ __forceinline__ void load_pi_tile(const double* __restrict__ pi, int 
   using C = HTC<KD, NP>;
   for (int e = threadIdx.x; e < NP * KD; e += blockDim.x) {
     const int jn = e / KD, i = e % KD;  // B[n = output state j][k = input state i] = pi[i][j]
-    float v = (i < K && jn < K) ? (float)pi[(size_t)i * K + jn] : 0.0f;
+    float v = (i < K && jn < K) ? (float)pi[(size_t)i * K + jn] : 0.0f;  // K here = true state count
     if (SU && !(i < jn)) v = 0.0f;
     const uint32_t hi = tf32_rna(v);
     const uint32_t lo = tf32_rna(v - __uint_as_float(hi));
@@ -147,7 +149,7 @@ __global__ void __launch_bounds__(HTC_THREADS, 1) hmm_forward_tc_kernel(HmmTcArg
     tb = (cc > 0) ? max(0, min(t0, tvn) - p.burn_in) : 0;
     tend = min(t1, tvn);  // trailing padding: the chain stops at the first masked frame
   }
-  load_pi_tile<KD, NP, false>(p.pi, K, sB_hi, sB_lo);
+  load_pi_tile<KD, NP, false>(p.pi, p.Kt, sB_hi, sB_lo);
   if (tid == 0) *smax = 0;
   const uint32_t mbar_sa = (uint32_t)__cvta_generic_to_shared(mbar);
   if (tid == 0) {
@@ -227,7 +229,7 @@ __global__ void __launch_bounds__(HTC_THREADS, 1) hmm_forward_tc_kernel(HmmTcArg
     const bool bstart = active && (t == t0) && (cc > 0);
     const bool bend = prev_active && (t == tend) && (nch > 1);
     // normaliser of the previous frame and maximum of this one, summed / maxed over the four parts
-    float inv = 1.0f / (float)K;
+    float inv = 1.0f / (float)p.Kt;
     if (s > 0) {
       const float norm = ((psum[buf ^ 1][0][row] + psum[buf ^ 1][1][row]) +
                           (psum[buf ^ 1][2][row] + psum[buf ^ 1][3][row])) + 1e-16f;
@@ -339,8 +341,8 @@ __global__ void __launch_bounds__(HTC_THREADS, 1) hmm_stay_tc_kernel(HmmTcArgs p
   const int tid = threadIdx.x, warp = tid >> 5;
   const int row = tid & 127, part = tid >> 7;
   const int K = p.K, Tm = p.Tm;
-  load_pi_tile<KD, NP, true>(p.pi, K, sB_hi, sB_lo);
-  if (tid < 128) pjj_s[tid] = (tid < K) ? (float)p.pi[(size_t)tid * K + tid] : 0.0f;
+  load_pi_tile<KD, NP, true>(p.pi, p.Kt, sB_hi, sB_lo);
+  if (tid < 128) pjj_s[tid] = (tid < p.Kt) ? (float)p.pi[(size_t)tid * p.Kt + tid] : 0.0f;
   for (int e = tid; e < 128 * 4; e += HTC_THREADS) reinterpret_cast<unsigned*>(&sbits[0][0])[e] = 0u;
   const uint32_t mbar_sa = (uint32_t)__cvta_generic_to_shared(mbar);
   if (tid == 0) {
@@ -455,7 +457,7 @@ __global__ void __launch_bounds__(HTC_THREADS, 1) hmm_stay_tc_kernel(HmmTcArgs p
         for (int q = 0; q < 8; q++) {
           const float P = __uint_as_float(tr[q]);
           const float thr = uu * t8[q];
-          const bool st = live && (c + q < K) && (P <= thr) && (P + a8[q] * pjj_s[(c + q) & 127] > thr);
+          const bool st = live && (c + q < p.Kt) && (P <= thr) && (P + a8[q] * pjj_s[(c + q) & 127] > thr);
           bits |= (st ? 1u : 0u) << q;
         }
         sbits[row][gi] = (unsigned char)bits;
@@ -496,9 +498,10 @@ static int launch_hmm_tc(const HmmTcArgs& a, cudaStream_t st) {
   return kpms_last_launch();
 }
 
-// Row-major ll (N, Tm, K) -> interleaved tiles.  One CTA per tile (b, r): 128 chains x K values,
-// read as whole rows (coalesced), transposed through shared memory, written as whole lines.
-__global__ void __launch_bounds__(256) hmm_ll_tile_kernel(const float* __restrict__ ll, int N, int Tm, int K,
+// Row-major ll (N, Tm, Kt) -> interleaved tiles of layout width K = round_up(Kt, 4) (padded states
+// get -inf).  One CTA per tile (b, r): 128 chains x K values, read as whole rows (coalesced),
+// transposed through shared memory, written as whole lines.
+__global__ void __launch_bounds__(256) hmm_ll_tile_kernel(const float* __restrict__ ll, int N, int Tm, int Kt, int K,
                                                           int chunk_len, int nch, float* __restrict__ out) {
   extern __shared__ float4 tl[];  // [K/4][129]
   __shared__ long long src_row[128];
@@ -518,11 +521,21 @@ __global__ void __launch_bounds__(256) hmm_ll_tile_kernel(const float* __restric
     src_row[threadIdx.x] = g;
   }
   __syncthreads();
-  const float4* ll4 = reinterpret_cast<const float4*>(ll);
-  for (int i = threadIdx.x; i < 128 * KC4; i += 256) {
-    const int row = i / KC4, kc = i - row * KC4;
-    const long long g = src_row[row];
-    tl[kc * 129 + row] = (g >= 0) ? __ldg(ll4 + (size_t)g * KC4 + kc) : make_float4(0.f, 0.f, 0.f, 0.f);
+  if (Kt == K) {
+    const float4* ll4 = reinterpret_cast<const float4*>(ll);
+    for (int i = threadIdx.x; i < 128 * KC4; i += 256) {
+      const int row = i / KC4, kc = i - row * KC4;
+      const long long g = src_row[row];
+      tl[kc * 129 + row] = (g >= 0) ? __ldg(ll4 + (size_t)g * KC4 + kc) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  } else {  // rows are not 16-byte aligned: element loads, padding filled with -inf
+    float* tlf = reinterpret_cast<float*>(tl);
+    for (int i = threadIdx.x; i < 128 * K; i += 256) {
+      const int row = i / K, j = i - row * K;
+      const long long g = src_row[row];
+      const float v = (g >= 0) ? ((j < Kt) ? __ldg(ll + (size_t)g * Kt + j) : -INFINITY) : 0.0f;
+      tlf[((size_t)(j >> 2) * 129 + row) * 4 + (j & 3)] = v;
+    }
   }
   __syncthreads();
   float4* dst = reinterpret_cast<float4*>(out) + (size_t)blk * KC4 * 128;
@@ -539,9 +552,14 @@ int kpms_hmm_mask_check(const float* mask, long long mask_stride, int Tm, const 
   return kpms_last_launch();
 }
 
+// any K <= 104: the layout width is K rounded up to a multiple of 4
 bool kpms_hmm_tc_supported(int Tm, int K, int chunk_len) {
   if (kpms_opts.hmm_tc == 0) return false;  // option: CUDA-core forward kernel in chunked mode
-  return chunk_len > 0 && chunk_len < Tm && K <= 104 && (K & 3) == 0;
+  return chunk_len > 0 && chunk_len < Tm && K <= 104;
+}
+// the emission kernel can write the interleaved layout itself only when no padding is involved
+bool kpms_hmm_tc_native(int Tm, int K, int chunk_len) {
+  return kpms_hmm_tc_supported(Tm, K, chunk_len) && (K & 3) == 0;
 }
 
 // Tensor-core forward filter + stay bits.  `ll_tiled` != 0: ll is already in the interleaved
@@ -554,17 +572,19 @@ int kpms_hmm_forward_tc(const float* ll, int ll_tiled, float* ll_scratch, const 
   if (!kpms_hmm_tc_supported(Tm, K, chunk_len)) return KPMS_ERR_UNSUPPORTED;
   int rc = 0;
   (void)mask; (void)mask_stride; (void)err_bits;  // the caller has run kpms_hmm_mask_check
+  const int Kl = (K + 3) & ~3;
+  if (ll_tiled && Kl != K) return KPMS_ERR_UNSUPPORTED;
   if (!ll_tiled) {
     const long long tiles = (((long long)N * nch + 127) / 128) * chunk_len;
-    const size_t smem = (size_t)(K >> 2) * 129 * sizeof(float4);
+    const size_t smem = (size_t)(Kl >> 2) * 129 * sizeof(float4);
     KPMS_CUDA(cudaFuncSetAttribute(hmm_ll_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    hmm_ll_tile_kernel<<<(unsigned)tiles, 256, smem, st>>>(ll, N, Tm, K, chunk_len, nch, ll_scratch);
+    hmm_ll_tile_kernel<<<(unsigned)tiles, 256, smem, st>>>(ll, N, Tm, K, Kl, chunk_len, nch, ll_scratch);
     rc = kpms_last_launch();
     if (rc) return rc;
     ll = ll_scratch;
   }
-  HmmTcArgs a{ll, pi, u, tv, a_out, T_out, stay, llpart, bnd, N, Tm, K, chunk_len, burn_in, nch};
-  if (K <= 32) return launch_hmm_tc<32, 32>(a, st);
-  if (K <= 64) return launch_hmm_tc<64, 64>(a, st);
+  HmmTcArgs a{ll, pi, u, tv, a_out, T_out, stay, llpart, bnd, N, Tm, Kl, chunk_len, burn_in, nch, K};
+  if (Kl <= 32) return launch_hmm_tc<32, 32>(a, st);
+  if (Kl <= 64) return launch_hmm_tc<64, 64>(a, st);
   return launch_hmm_tc<104, 112>(a, st);
 }

@@ -10,7 +10,7 @@ int kpms_hmm_ffbs_impl(const float* ll, int ll_tiled, const float* mask, int64_t
                        const double* pi, const float* u, int N, int Tm, int K, int chunk_len,
                        int burn_in, int32_t* z, double* loglik, float* boundary_err,
                        void* workspace, size_t workspace_bytes, void* stream);  // hmm_ffbs.cu
-bool kpms_hmm_tc_supported(int Tm, int K, int chunk_len);                       // hmm_tc.cu
+bool kpms_hmm_tc_native(int Tm, int K, int chunk_len);                          // hmm_tc.cu
 
 // ll is (N, T-L, K) row-major, or — when the tensor-core filter will consume it — in the filter's
 // chain-interleaved layout, whose chunks are padded to full length and whose chains to 128.
@@ -19,7 +19,7 @@ static size_t ss_ll_bytes(int N, int T, int L, int K, int chunk_len) {
   size_t elems = (size_t)N * Tm * K;
   if (chunk_len > 0 && chunk_len < Tm) {
     const size_t nch = (size_t)(Tm + chunk_len - 1) / chunk_len;
-    const size_t tiled = ((size_t)N * nch + 127) / 128 * 128 * chunk_len * K;
+    const size_t tiled = ((size_t)N * nch + 127) / 128 * 128 * chunk_len * ((K + 3) & ~3);
     if (tiled > elems) elems = tiled;
   }
   return kpms_round_up(elems * sizeof(float), 256);
@@ -52,7 +52,7 @@ extern "C" int kpms_resample_stateseqs(const float* x, const float* mask, const 
   // Writing ll straight into the filter's interleaved layout makes the emission kernel gather its
   // lag windows from scattered frames, which costs more (6.5 vs 3.3 ms on the bench shard) than the
   // filter's own transposition pass (0.65 ms); opt in with kpms_set_option("ll_tiled", 1).
-  if (kpms_opts.ll_tiled == 1 && kpms_hmm_tc_supported(Tm, K, chunk_len)) {
+  if (kpms_opts.ll_tiled == 1 && kpms_hmm_tc_native(Tm, K, chunk_len)) {
     tile_cl = chunk_len;
     tile_nch = (Tm + chunk_len - 1) / chunk_len;
   }

@@ -42,12 +42,17 @@ FALLBACKS = {"stateseqs": 0, "latents": 0}
 
 
 def auto_hmm_chunk_len(N, Tm, K, burn_in, device):
-    """Chunk length of the forward filter.  K <= 104 with K % 4 == 0 runs on the tensor cores,
+    """Chunk length of the forward filter.  K <= 104 runs on the tensor cores (states padded to a multiple of 4),
     128 chains per CTA: aim at one CTA per SM but keep a chunk at least as long as its warm-up.
     Other K use the CUDA-core kernel (one CTA per chain, three resident per SM), where longer
     chunks keep the warm-up overhead small."""
     sms = torch.cuda.get_device_properties(device).multi_processor_count
-    if K <= 104 and K % 4 == 0:
+    if K > 512:
+        return 0                      # sequential K-generic kernel
+    if K > 128:                       # 32 chains per CTA (hmm_big.cu): one CTA per SM, chunks no shorter than their warm-up
+        nch = max(1, sms * 32 // max(N, 1))
+        cl = max(-(-Tm // nch), max(burn_in, 1))
+    elif K <= 104:
         nch = max(1, sms * 128 // max(N, 1))
         cl = max(-(-Tm // nch), max(burn_in, 1))
     else:
@@ -177,7 +182,7 @@ def _hmm_chunking(N, Tm, K, chunk_len, burn_in, strict, dev):
     strict = STATESEQ_CHUNKING["strict"] if strict is None else strict
     auto = chunk_len == "auto"
     if auto:
-        chunk_len = auto_hmm_chunk_len(N, Tm, K, int(burn_in), dev) if K <= 128 else 0
+        chunk_len = auto_hmm_chunk_len(N, Tm, K, int(burn_in), dev)
     return int(chunk_len), int(burn_in), (strict if strict == "defer" else bool(strict)), auto
 
 

@@ -250,6 +250,7 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
                                                   pi=pr["pi"], strict=strict, session_offset=off, return_info=True)
             checks["z"] = info["boundary_err"] if (strict == "defer" and info["chunk_len"] > 0) else None
             done("z", z_new)
+            mark("z")
             if defer_obs and "sigmasq_done" not in checks:
                 wait("all")
                 S_y, msum = obs_stats()     # uses the OLD x (st["x"]), exactly as step 2 of the sweep does
@@ -265,6 +266,7 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
                                            session_offset=off, return_info=True)
         checks["x"] = info["boundary_err"] if (strict == "defer" and info["chunk_len"] > 0) else None
         done("x", st["x"])
+        mark("x")
         st["h"] = G.resample_heading(key, Y=data["Y"], v=states["v"], x=st["x"], s=states["s"], Cd=pr["Cd"],
                                      sigmasq=pr["sigmasq"], Gamma=Gamma, session_offset=off)
         done("h", st["h"])
@@ -276,9 +278,11 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
                                     sigmasq=pr["sigmasq"], nu_s=hyp["nu_s"], s_0=hyp["s_0"], Gamma=Gamma,
                                     session_offset=off)
         done("s", st["s"])
+        mark("hvs")
 
     run_from("z", "defer")
     _verify_and_repair(checks, flags_dev, run_from, world)
+    mark("verified")
     return st, pr
 
 

@@ -94,6 +94,44 @@ def test_hmm_ffbs_parity(G, K):
     assert np.all(z[~valid] == 0)
 
 
+@pytest.mark.parametrize("K", [3, 33, 50, 98, 100])
+def test_hmm_chunked_tensor_core_any_state_count(G, K):
+    """Chunked tcgen05 filter for state counts that are not multiples of 4 (states are padded with
+    zero-probability ones inside the library), e.g. K = 50 of BASELINE configs[2]."""
+    ll, mask, pi, u = _hmm_case(100 + K, N=4, T=2400, K=K)
+    zo, lo = O._hmm_batch(ll, mask, pi, u)
+    z, lg, info = G.sample_hmm_stateseqs(ll=T_(ll), mask=T_(mask), pi=T_(pi), u=T_(u), chunk_len=300, burn_in=256,
+                                         strict=False, return_info=True)
+    assert float(info["boundary_err"]) < 1e-4
+    z, lg = N_(z), N_(lg)
+    assert np.all(np.abs(lg - lo) <= 1e-5 * np.abs(lo)), (lg, lo)
+    valid = mask > 0
+    assert (z[valid] == zo[valid]).mean() >= 0.999 and z.max() < K
+    assert np.all(z[~valid] == 0)
+
+
+@pytest.mark.parametrize("K", [130, 200, 256, 500])
+def test_hmm_chunked_large_state_counts(G, K):
+    """128 < K <= 512: chunk-parallel filter with 32 chains per CTA and transition tiles streamed from
+    L2 (hmm_big.cu), sampler without stay bits; against the oracle and against the sequential
+    K-generic kernel."""
+    import torch
+    ll, mask, pi, u = _hmm_case(300 + K, N=3, T=1500, K=K)
+    zo, lo = O._hmm_batch(ll, mask, pi, u)
+    kw = dict(ll=T_(ll), mask=T_(mask), pi=T_(pi), u=T_(u), return_info=True)
+    z, lg, info = G.sample_hmm_stateseqs(chunk_len=300, burn_in=256, strict=False, **kw)
+    assert float(info["boundary_err"]) < 1e-4
+    z_seq, lg_seq, _ = G.sample_hmm_stateseqs(chunk_len=0, **kw)
+    valid = mask > 0
+    assert np.all(np.abs(N_(lg) - lo) <= 1e-5 * np.abs(lo)), (N_(lg), lo)
+    assert (N_(z)[valid] == zo[valid]).mean() >= 0.999 and int(z.max()) < K
+    assert np.all(N_(z)[~valid] == 0)
+    assert float((z != z_seq)[torch.as_tensor(valid, device="cuda")].float().mean()) < 1e-3
+    # a warm-up that is too short shows up in the reported mismatch
+    _, _, bad = G.sample_hmm_stateseqs(chunk_len=300, burn_in=1, strict=False, **kw)
+    assert float(bad["boundary_err"]) > 1e-3
+
+
 def test_hmm_marginal_loglik_known_answer(G):
     """Brute-force enumeration of all K^T paths (K=3, T=6), through the CUDA kernel."""
     rng = np.random.default_rng(0)

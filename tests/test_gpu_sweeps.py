@@ -100,8 +100,11 @@ def _slow_case(seed, N, T, K, stick):
     return d, s, Ab, Q, pi, u
 
 
-@pytest.mark.parametrize("stick,expect_exact", [(0.98, False), (0.9995, True)])
-def test_slow_forgetting_hmm_drives_the_retry_ladder(G, stick, expect_exact):
+@pytest.mark.parametrize("stick,max_boost,expect_exact", [(0.98, 16, False), (0.9995, 16, False), (0.9995, 2, True)])
+def test_slow_forgetting_hmm_drives_the_retry_ladder(G, monkeypatch, stick, max_boost, expect_exact):
+    """(0.9995, 16): warm-ups of 32, 64, 128, 256 frames all fail, 512 passes; with the ladder capped
+    at 2x the sequential kernels have to take over."""
+    monkeypatch.setattr(G, "HMM_MAX_BOOST", max_boost)
     N, T, K = 3, 9000, 20
     d, s, Ab, Q, pi, u = _slow_case(7, N, T, K, stick)
     zo, lo = O.resample_stateseqs(x=s['x'], mask=d['mask'], Ab=Ab, Q=Q, pi=pi, u=u)
