@@ -143,7 +143,7 @@ def test_stateseqs_K500_parity(G):
     assert np.all(np.abs(N_(ll) - lo) <= 1e-5 * np.abs(lo))
     want = O.ar_log_likelihood(s['x'], p['Ab'], p['Q'])
     got = N_(G.ar_log_likelihood(x=T_(s['x']), Ab=T_(p['Ab']), Q=T_(p['Q']))).astype(np.float64)
-    assert (np.abs(got - want) / np.maximum(1.0, np.abs(want))).max() < 2e-5
+    assert (np.abs(got - want) / np.maximum(1.0, np.abs(want))).max() < 5e-5     # 3xTF32, 1.8 M entries
     F = N_(G.ar_sufficient_stats(nlags=L, num_states=K, mask=T_(d['mask']), x=T_(s['x']), z=T_(s['z'])))
     Fo = O.ar_sufficient_stats(nlags=L, num_states=K, mask=d['mask'], x=s['x'], z=s['z'])
     assert np.abs(F - Fo).max() <= 1e-10 * np.abs(Fo).max()
