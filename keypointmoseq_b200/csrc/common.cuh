@@ -20,11 +20,13 @@
 // debugging / cross-check switches (api.cu): read from the environment once at load time,
 // changed afterwards only through kpms_set_option
 struct KpmsOptions {
-  int kalman_impl;   // 0: CTA-per-chunk shared-memory Kalman filter instead of the warp kernel
+  int kalman_impl;   // 2 (default): blocked DMMA warp kernel; 1: lane-per-column warp kernel; 0: CTA-per-chunk kernel
   int hmm_tc;        // 0: CUDA-core chunked HMM filter instead of the tcgen05 one
   int hmm_bwd_burn;  // >= 0: warm-up of the HMM sampler only (0 forces every chunk through the repair pass)
   int ll_tiled;      // 1: the emission kernel writes the interleaved HMM layout directly
   int hmm_flags;     // bit 0: forward pass only (timing)
+  int kalman_warps;  // warps per CTA of the blocked Kalman filter: 8, 12 (default) or 16
+  int kalman_lockstep;  // 1 (default): the warps of a CTA step together (shared instruction fetch)
 };
 extern KpmsOptions kpms_opts;
 

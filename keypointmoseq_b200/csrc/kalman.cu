@@ -67,6 +67,9 @@ struct KalWs {
   double* bndx;
   unsigned long long* errs;
   int* tv;
+  double* tabg;  // per-state G in MMA accumulator layout (blocked kernel)
+  double* tabf;  // per-state [unit columns | F] in MMA B-operand layout (blocked kernel)
+  double* fin;   // [N][BND] carry after the last transition step (input of kalman_final_kernel)
 };
 
 __host__ __device__ static inline int kal_nchunks(int Tt, int chunk_len) {
@@ -99,6 +102,12 @@ static size_t kal_layout(int N, int T, int D, int L, int K, int chunk_len, void*
   p = take((size_t)N * nch * 2 * NN * 8); if (ws) ws->bndx = (double*)p;
   p = take(2 * 8); if (ws) ws->errs = (unsigned long long*)p;
   p = take((size_t)N * 4); if (ws) ws->tv = (int*)p;
+  {  // blocked kernel (kalman_blk.cuh: KB<NN, DD>)
+    const int NBK = (NN + 1 + 7) / 8, NBLK = NBK * (NBK + 1) / 2, CB0 = (NN - D) / 8;
+    p = take((size_t)K * NBLK * 64 * 8); if (ws) ws->tabg = (double*)p;
+    p = take((size_t)K * (2 * NBK) * (NBK - CB0) * 32 * 8); if (ws) ws->tabf = (double*)p;
+    p = take((size_t)N * (NTRI + NN) * 8); if (ws) ws->fin = (double*)p;
+  }
   return off;
 }
 
@@ -594,6 +603,14 @@ __device__ __forceinline__ double rsqrt_pos(double x) {
   return fma(y * e, p, y);
 }
 
+// 1/x for the pivots of an SPD matrix (x > 0, normal): hardware seed and one third-order correction.
+__device__ __forceinline__ double rcp_pos(double x) {
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  const double e = fma(-x, y, 1.0);
+  return fma(y, fma(e, e, e), y);
+}
+
 template <int NN, int DD>
 __global__ void __launch_bounds__(KW_WARPS * 32, 1)
     kalman_forward_warp_kernel(const float* __restrict__ mask, const int* __restrict__ z,
@@ -924,6 +941,8 @@ __global__ void __launch_bounds__(KW_WARPS * 32, 1)
   if (lane == NN) ws.llpart[(size_t)n * nch + cc] = llacc;
 }
 
+#include "kalman_blk.cuh"
+
 // ------------------------------------------------------------------ backward sampler
 // One warp per session (or session chunk).  x_t = L (L^T h + w_t),
 // h = eta_c + A^T Qinv (x_{t+1} - B) with A^T Qinv = [100 E | F_D] (see file header).
@@ -1131,7 +1150,28 @@ static int launch_latents(const float* Y, const float* mask, const float* v, con
   {
     const size_t smem = (size_t)(2 * NN * YL::NS + NN * YL::NV + 3 * NN + NN * NN + NN * DD + DD * DD +
                                  NN + DD + 2 + YL::OBS_SIZE) * sizeof(double) + 2 * YL::NTRI;
-    if (kpms_opts.kalman_impl == 0 || NN > 30) {  // CTA-per-chunk shared-memory kernel (cross-checks; n > 30)
+    if (kpms_opts.kalman_impl >= 2 && NN <= 31) {
+      // blocked DMMA kernel (default) + the final update / last-state draw as a kernel of its own
+      using KBt = KB<NN, DD>;
+      kalman_tables_blk_kernel<NN, DD><<<K, 32, 0, st>>>(ws.tab, ws.tabg, ws.tabf);
+      rc = kpms_last_launch();
+      if (rc) return rc;
+      const int wpb = kpms_opts.kalman_warps;
+      const int lockstep = kpms_opts.kalman_lockstep;
+#define KPMS_BLK_GO(W)                                                                                              \
+  {                                                                                                                 \
+    const size_t smb = (size_t)(W) * KBt::SM_TOTAL * sizeof(double);                                                \
+    auto kern = kalman_forward_blk_kernel<NN, DD, W>;                                                               \
+    KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smb));                   \
+    kern<<<(N * nch + (W) - 1) / (W), (W) * 32, smb, st>>>(mask, z, ws, N, T, Lg, chunk_len, burn_in,               \
+                                                          loglik != nullptr, lockstep);                             \
+  }
+      if (wpb == 8) KPMS_BLK_GO(8) else if (wpb == 16) KPMS_BLK_GO(16) else KPMS_BLK_GO(12)
+#undef KPMS_BLK_GO
+      rc = kpms_last_launch();
+      if (rc) return rc;
+      kalman_final_kernel<NN, DD><<<N, 32, 0, st>>>(w_last, ws, N, T, Lg, nch);
+    } else if (kpms_opts.kalman_impl == 0 || NN > 30) {  // CTA-per-chunk shared-memory kernel (cross-checks; n > 30)
       auto kern = kalman_forward_kernel<NN, DD>;
       KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       kern<<<N * nch, KAL_NT, smem, st>>>(mask, z, w_last, ws, N, T, Lg, chunk_len, burn_in,
