@@ -51,6 +51,9 @@ SIGNATURES = {
     "kpms_log_joint": (c_int, [P] * 13 + [c_double] * 3 + [c_int] * 7 + [P, P, c_size_t, P]),
     "kpms_obs_params_stats": (c_int, [P] * 7 + [c_int] * 5 + [P, P, P, c_size_t, P]),
     "kpms_resample_scales": (c_int, [P] * 6 + [c_double, c_double, P] + [c_int] * 5 + [P, P]),
+    "kpms_resample_scales_stats": (c_int, [P] * 7 + [c_double, c_double, P, c_uint64, c_uint64, c_uint64] + [c_int] * 5 +
+                                   [P, P, P, P, c_size_t, P]),
+    "kpms_resample_heading_philox": (c_int, [P] * 6 + [c_uint64, c_uint64, c_uint64] + [c_int] * 5 + [P, P, P, P, P]),
     "kpms_resample_heading": (c_int, [P] * 7 + [c_int] * 6 + [P, P, P, P]),
     "kpms_resample_location_workspace_bytes": (c_size_t, [c_int] * 3),
     "kpms_resample_location": (c_int, [P] * 7 + [c_double, P, P] + [c_int] * 5 + [P, P, P, c_size_t, P]),

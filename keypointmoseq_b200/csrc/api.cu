@@ -14,7 +14,7 @@ static int env_int(const char* name, int dflt) {
 }
 KpmsOptions kpms_opts = {env_int("KPMS_KALMAN_IMPL", 2), env_int("KPMS_HMM_TC", 1), env_int("KPMS_HMM_BWD_BURN", -1),
                          env_int("KPMS_LL_TILED", 0), env_int("KPMS_HMM_FLAGS", 0), env_int("KPMS_KALMAN_WARPS", 12),
-                         env_int("KPMS_KALMAN_LOCKSTEP", 1)};
+                         env_int("KPMS_KALMAN_LOCKSTEP", 0)};
 
 static int* option_slot(const char* name) {
   if (!name) return nullptr;

@@ -26,7 +26,7 @@ struct KpmsOptions {
   int ll_tiled;      // 1: the emission kernel writes the interleaved HMM layout directly
   int hmm_flags;     // bit 0: forward pass only (timing)
   int kalman_warps;  // warps per CTA of the blocked Kalman filter: 8, 12 (default) or 16
-  int kalman_lockstep;  // 1 (default): the warps of a CTA step together (shared instruction fetch)
+  int kalman_lockstep;  // 1: the warps of a CTA step together (helps the lane-per-column kernel, not the blocked one; default 0)
 };
 extern KpmsOptions kpms_opts;
 

@@ -515,6 +515,109 @@ extern "C" int kpms_resample_scales(const float* Y, const float* v, const float*
   return kpms_last_launch();
 }
 
+// Fused variant: the Gamma((nu_s+3)/2, 1) variates are drawn inside the kernel when g == NULL
+// (Philox4x32-10 keyed by the GLOBAL element index elem_offset + f*k + kp: the value
+// kpms_fill_gamma_at would have written there), and, when S_y is requested, the kernel also
+// accumulates  S_y(k) = sum_f mask ||Ytild - Ybar||^2 / s_new  and  sum_f mask  for the state it has
+// just produced — the statistics resample_obs_variance needs at the start of the NEXT sweep
+// (gibbs.py:86-94), so that sweep does not have to pass over Y once more.
+__global__ void __launch_bounds__(OV_THREADS)
+    scales_stats_kernel(const float* __restrict__ Y, const float* __restrict__ mask, const float* __restrict__ v,
+                        const float* __restrict__ h, const float* __restrict__ x,
+                        const double* __restrict__ Cdfull, const double* __restrict__ sigmasq, double nu_s,
+                        double s_0, const float* __restrict__ g, uint2 key, uint32_t sid,
+                        unsigned long long elem_offset, ObsDims dm, float* __restrict__ s_out,
+                        double* __restrict__ partial) {
+  extern __shared__ __align__(16) double Cs[];
+  __shared__ double red[OV_THREADS / 32];
+  const int k = dm.k, dk = dm.dk, D = dm.D;
+  double* isig = Cs + (size_t)k * dk * (D + 1);
+  double* accs = isig + k;   // [k+1][OV_THREADS], only when partial != NULL
+  load_cd(Cdfull, k * dk, D, Cs);
+  for (int i = threadIdx.x; i < k; i += blockDim.x) isig[i] = 1.0 / sigmasq[i];
+  if (partial)
+    for (int i = 0; i <= k; i++) accs[i * OV_THREADS + threadIdx.x] = 0.0;
+  __syncthreads();
+  const long long frames = (long long)dm.N * dm.T;
+  const double base = s_0 * nu_s;
+  const float shape = (float)((nu_s + 3.0) * 0.5);
+  for (long long f = (long long)blockIdx.x * blockDim.x + threadIdx.x; f < frames;
+       f += (long long)gridDim.x * blockDim.x) {
+    double xr[OBS_XMAX];
+    load_x(x, (size_t)f, D, xr);
+    double sn, cs;
+    sincos((double)h[f], &sn, &cs);
+    double vv[OBS_DKMAX];
+#pragma unroll
+    for (int dim = 0; dim < OBS_DKMAX; dim++) vv[dim] = (dim < dk) ? (double)v[f * dk + dim] : 0.0;
+    const double m = partial ? (double)mask[f] : 0.0;
+#pragma unroll 2
+    for (int kp = 0; kp < k; kp++) {
+      double yb[OBS_DKMAX], yt[OBS_DKMAX];
+      ybar_kp(Cs, kp, dk, D, xr, yb);
+      ytild_kp(Y + ((size_t)f * k + kp) * dk, vv, cs, sn, dk, yt);
+      double e = 0.0;
+#pragma unroll
+      for (int dim = 0; dim < OBS_DKMAX; dim++) {
+        const double r = yt[dim] - yb[dim];
+        e = fma(r, r, e);
+      }
+      const size_t el = (size_t)f * k + kp;
+      const double gg = g ? (double)g[el] : (double)philox_gamma(elem_offset + el, shape, key, sid);
+      const float sv = (float)((e * isig[kp] + base) * 0.5 / gg);
+      s_out[el] = sv;
+      if (partial && m > 0.0) accs[kp * OV_THREADS + threadIdx.x] += m * e / (double)sv;
+    }
+    if (partial && m > 0.0) accs[k * OV_THREADS + threadIdx.x] += m;
+  }
+  if (!partial) return;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int i = 0; i <= k; i++) {
+    double w = warp_sum_d(accs[i * OV_THREADS + threadIdx.x]);
+    __syncthreads();
+    if (lane == 0) red[warp] = w;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double t = 0.0;
+      for (int q = 0; q < OV_THREADS / 32; q++) t += red[q];
+      partial[(size_t)blockIdx.x * (OBS_KPMAX + 1) + (i < k ? i : OBS_KPMAX)] = t;
+    }
+  }
+}
+
+extern "C" int kpms_resample_scales_stats(const float* Y, const float* mask, const float* v, const float* h,
+                                          const float* x, const double* Cdfull, const double* sigmasq,
+                                          double nu_s, double s_0, const float* g, uint64_t seed,
+                                          uint64_t stream_id, uint64_t elem_offset, int N, int T, int k, int dk,
+                                          int D, float* s_out, double* S_y, double* mask_sum, void* workspace,
+                                          size_t workspace_bytes, void* stream) {
+  KPMS_REQUIRE(Y && v && h && x && Cdfull && sigmasq && s_out, KPMS_ERR_NULL);
+  int rc = obs_check(N, T, k, dk, D);
+  if (rc) return rc;
+  KPMS_REQUIRE(g != nullptr || nu_s + 3.0 >= 2.0, KPMS_ERR_UNSUPPORTED);   // in-kernel sampler needs shape >= 1
+  const bool stats = S_y != nullptr;
+  if (stats) {
+    KPMS_REQUIRE(mask && mask_sum && workspace, KPMS_ERR_NULL);
+    KPMS_REQUIRE(kpms_aligned(workspace, 256) && workspace_bytes >= kpms_obs_variance_stats_workspace_bytes(N, T, k),
+                 KPMS_ERR_WORKSPACE);
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  ObsDims dm{N, T, k, dk, D};
+  const size_t smem = ((size_t)k * dk * (D + 1) + k + (stats ? (size_t)(k + 1) * OV_THREADS : 0)) * sizeof(double);
+  KPMS_CUDA(cudaFuncSetAttribute(scales_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const long long frames = (long long)N * T;
+  (void)frames;
+  const long long blocks = OV_BLOCKS;   // the grid of obs_variance_kernel: the statistics come out bit-identical to that pass
+  scales_stats_kernel<<<(unsigned)blocks, OV_THREADS, smem, st>>>(Y, mask, v, h, x, Cdfull, sigmasq, nu_s, s_0, g,
+                                                                  split_seed(seed), (uint32_t)stream_id,
+                                                                  (unsigned long long)elem_offset, dm, s_out,
+                                                                  stats ? (double*)workspace : nullptr);
+  rc = kpms_last_launch();
+  if (rc || !stats) return rc;
+  obs_variance_reduce_kernel<<<1, OBS_KPMAX + 1, 0, st>>>((const double*)workspace, (int)blocks, k, S_y, mask_sum);
+  return kpms_last_launch();
+}
+
 // ======================================================================== a15
 // Best & Fisher (1979) von Mises rejection sampler on injected uniforms; contract shared
 // with oracle/kpms_oracle.py:sample_vonmises.
@@ -537,12 +640,43 @@ __device__ __forceinline__ double vonmises_dev(double kappa, const float* __rest
   return 0.0;
 }
 
+// The same sampler with its uniforms drawn in place: round rd of GLOBAL frame fg uses the Philox
+// block (counter = (fg, rd), key = seed, stream id), so no uniform buffer exists and the proposal
+// loop simply runs until it accepts (Best-Fisher accepts with probability >= 0.66 per round; the
+// cap of 64 rounds leaves < 1e-30 and is counted in `exhausted` should it ever be hit).
+#define VM_MAX_ROUNDS 64
+__device__ __forceinline__ double vonmises_philox(double kappa, unsigned long long fg, uint2 key, uint32_t sid,
+                                                  int* __restrict__ exhausted) {
+  if (kappa < 1e-8) {
+    const uint4 r = philox4x32_10(make_uint4((uint32_t)fg, (uint32_t)(fg >> 32), 0u, sid), key);
+    return KPMS_PI * (2.0 * (double)u01(r.z) - 1.0);
+  }
+  const double tau = 1.0 + sqrt(1.0 + 4.0 * kappa * kappa);
+  const double rho = (tau - sqrt(2.0 * tau)) / (2.0 * kappa);
+  const double rr = (1.0 + rho * rho) / (2.0 * rho);
+  for (uint32_t rd = 0; rd < VM_MAX_ROUNDS; rd++) {
+    const uint4 r = philox4x32_10(make_uint4((uint32_t)fg, (uint32_t)(fg >> 32), rd, sid), key);
+    const double u1 = (double)u01(r.x), u2 = (double)u01_open0(r.y), u3 = (double)u01(r.z);
+    const double zc = cospi(u1);
+    double f = (1.0 + rr * zc) / (rr + zc);
+    const double c = kappa * (rr - f);
+    if (c * (2.0 - c) - u2 > 0.0 || log(c / u2) + 1.0 - c >= 0.0) {
+      f = fmin(1.0, fmax(-1.0, f));
+      return (u3 > 0.5) ? acos(f) : -acos(f);
+    }
+  }
+  if (exhausted) atomicAdd(exhausted, 1);
+  return 0.0;
+}
+
+template <bool PHILOX>
 __global__ void __launch_bounds__(256)
     heading_kernel(const float* __restrict__ Y, const float* __restrict__ v,
                    const float* __restrict__ x, const float* __restrict__ s,
                    const double* __restrict__ Cdfull, const double* __restrict__ sigmasq,
-                   const float* __restrict__ u, int rounds, ObsDims dm, float* __restrict__ h_out,
-                   double* __restrict__ theta_out, double* __restrict__ kappa_out) {
+                   const float* __restrict__ u, int rounds, uint2 key, uint32_t sid,
+                   unsigned long long frame_offset, int* __restrict__ exhausted, ObsDims dm,
+                   float* __restrict__ h_out, double* __restrict__ theta_out, double* __restrict__ kappa_out) {
   extern __shared__ __align__(16) double Cs[];
   const int k = dm.k, dk = dm.dk, D = dm.D;
   double* isig = Cs + (size_t)k * dk * (D + 1);
@@ -575,7 +709,8 @@ __global__ void __launch_bounds__(256)
   const double kappa = sqrt(kc * kc + ks * ks);
   if (theta_out) theta_out[f] = ang;
   if (kappa_out) kappa_out[f] = kappa;
-  double hh = ang + vonmises_dev(kappa, u + (size_t)f * rounds * 3, rounds);
+  double hh = ang + (PHILOX ? vonmises_philox(kappa, frame_offset + (unsigned long long)f, key, sid, exhausted)
+                            : vonmises_dev(kappa, u + (size_t)f * rounds * 3, rounds));
   hh = hh - 2.0 * KPMS_PI * rint(hh / (2.0 * KPMS_PI));
   h_out[f] = (float)hh;
 }
@@ -591,8 +726,27 @@ extern "C" int kpms_resample_heading(const float* Y, const float* v, const float
   ObsDims dm{N, T, k, dk, D};
   const size_t smem = ((size_t)k * dk * (D + 1) + k) * sizeof(double);
   const long long frames = (long long)N * T;
-  heading_kernel<<<(unsigned)((frames + 255) / 256), 256, smem, (cudaStream_t)stream>>>(
-      Y, v, x, s, Cdfull, sigmasq, u, rounds, dm, h_out, theta_out, kappa_out);
+  heading_kernel<false><<<(unsigned)((frames + 255) / 256), 256, smem, (cudaStream_t)stream>>>(
+      Y, v, x, s, Cdfull, sigmasq, u, rounds, make_uint2(0u, 0u), 0u, 0ULL, nullptr, dm, h_out, theta_out, kappa_out);
+  return kpms_last_launch();
+}
+
+extern "C" int kpms_resample_heading_philox(const float* Y, const float* v, const float* x, const float* s,
+                                            const double* Cdfull, const double* sigmasq, uint64_t seed,
+                                            uint64_t stream_id, uint64_t frame_offset, int N, int T, int k, int dk,
+                                            int D, float* h_out, double* theta_out, double* kappa_out,
+                                            int32_t* exhausted, void* stream) {
+  KPMS_REQUIRE(Y && v && x && s && Cdfull && sigmasq && h_out, KPMS_ERR_NULL);
+  int rc = obs_check(N, T, k, dk, D);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (exhausted) KPMS_CUDA(cudaMemsetAsync(exhausted, 0, sizeof(int32_t), st));
+  ObsDims dm{N, T, k, dk, D};
+  const size_t smem = ((size_t)k * dk * (D + 1) + k) * sizeof(double);
+  const long long frames = (long long)N * T;
+  heading_kernel<true><<<(unsigned)((frames + 255) / 256), 256, smem, st>>>(
+      Y, v, x, s, Cdfull, sigmasq, nullptr, 0, split_seed(seed), (uint32_t)stream_id,
+      (unsigned long long)frame_offset, exhausted, dm, h_out, theta_out, kappa_out);
   return kpms_last_launch();
 }
 

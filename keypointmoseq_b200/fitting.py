@@ -49,7 +49,7 @@ def save_checkpoint(directory, iteration, states, params, history, rank=0, phase
     path = checkpoint_path(directory, rank)
     tmp = path + ".tmp"
     torch.save({"iteration": int(iteration), "phase": phase,
-                "states": {a: b.detach().cpu() for a, b in states.items()},
+                "states": {a: b.detach().cpu() for a, b in states.items() if torch.is_tensor(b)},
                 "params": {a: b.detach().cpu() for a, b in params.items()},
                 "history": history}, tmp)
     os.replace(tmp, path)     # a crash mid-write leaves the previous checkpoint intact
@@ -113,4 +113,5 @@ def fit(key, data, states, params, *, trans_hypparams, ar_hypparams, obs_hyppara
                 log_fn(rec)
         if checkpoint_dir and ((i + 1) % int(checkpoint_every) == 0 or i == total - 1):
             save_checkpoint(checkpoint_dir, i, st, pr, history, rank, "ar_only" if warm else "full")
+    st.pop(parallel.OBS_STATS_KEY, None)   # the sweeps' private cache of next sweep's statistics
     return st, pr, history

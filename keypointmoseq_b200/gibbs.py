@@ -18,7 +18,6 @@ from . import _lib
 from . import distributions as dist
 from .util import center_embedding, expand_Cd, f32, f64, i32
 
-VONMISES_ROUNDS = 8          # Best-Fisher rejection rounds pre-drawn per frame
 # Kalman time-chunking: "auto" cuts every session into chunks sized so that one wave of warps
 # covers the shard; each chunk is warmed up over `burn_in` earlier steps.  With strict=True the
 # reported chunk-boundary mismatch is read back and the call is repeated in the exact sequential
@@ -321,20 +320,30 @@ def resample_heading(key, *, Y, v, x, s, Cd, sigmasq, Gamma=None, draws=None, re
     v, x, s, sigmasq = f32(v, dev), f32(x, dev), f32(s, dev), f64(sigmasq, dev)
     D = x.shape[-1]
     Cdfull = expand_Cd(f64(Cd, dev), _gamma(Gamma, k, dev), dk)
-    if draws is not None:
-        u = f32(draws["u"], dev)
-    else:
-        u = dist.fill_uniform((N, T, VONMISES_ROUNDS, 3), dist.seed_of(key), dist.STREAM_H, dev, session_offset)
-    rounds = u.shape[2]
     hout = torch.empty((N, T), dtype=torch.float32, device=dev)
     theta = torch.empty((N, T), dtype=torch.float64, device=dev) if return_info else None
     kappa = torch.empty((N, T), dtype=torch.float64, device=dev) if return_info else None
-    _lib.check(lib.kpms_resample_heading(
-        _lib.ptr(Y), _lib.ptr(v), _lib.ptr(x), _lib.ptr(s), _lib.ptr(Cdfull), _lib.ptr(sigmasq), _lib.ptr(u),
-        rounds, N, T, k, dk, D, _lib.ptr(hout), _lib.ptr(theta), _lib.ptr(kappa), _lib.stream_ptr(dev)),
-        "kpms_resample_heading")
+    info = {"theta": theta, "kappa": kappa}
+    if draws is not None:
+        # injected proposals: u (N,T,rounds,3); a frame whose rounds are all rejected gets the mean direction
+        u = f32(draws["u"], dev)
+        rounds = u.shape[2]
+        _lib.check(lib.kpms_resample_heading(
+            _lib.ptr(Y), _lib.ptr(v), _lib.ptr(x), _lib.ptr(s), _lib.ptr(Cdfull), _lib.ptr(sigmasq), _lib.ptr(u),
+            rounds, N, T, k, dk, D, _lib.ptr(hout), _lib.ptr(theta), _lib.ptr(kappa), _lib.stream_ptr(dev)),
+            "kpms_resample_heading")
+    else:
+        # uniforms drawn inside the kernel, keyed by the global frame index; the rejection loop runs
+        # until it accepts (no pre-drawn round limit)
+        exhausted = torch.zeros((1,), dtype=torch.int32, device=dev) if return_info else None
+        _lib.check(lib.kpms_resample_heading_philox(
+            _lib.ptr(Y), _lib.ptr(v), _lib.ptr(x), _lib.ptr(s), _lib.ptr(Cdfull), _lib.ptr(sigmasq),
+            dist.seed_of(key), dist.STREAM_H, int(session_offset) * T, N, T, k, dk, D, _lib.ptr(hout),
+            _lib.ptr(theta), _lib.ptr(kappa), _lib.ptr(exhausted), _lib.stream_ptr(dev)),
+            "kpms_resample_heading_philox")
+        info["exhausted"] = exhausted
     if return_info:
-        return hout, {"theta": theta, "kappa": kappa}
+        return hout, info
     return hout
 
 
@@ -492,8 +501,12 @@ def resample_obs_variance(key, *, Y, mask, Cd, v, h, x, s, nu_sigma, sigmasq_0, 
 
 # ------------------------------------------------------------------------ a14
 def resample_scales(key, *, x, v, h, Y, Cd, sigmasq, nu_s, s_0, Gamma=None, draws=None, session_offset=0,
-                    **kwargs):
-    """gibbs.py:117-125 -> s (N,T,k) float32 (no mask, as the reference)."""
+                    mask=None, return_stats=False, **kwargs):
+    """gibbs.py:117-125 -> s (N,T,k) float32 (no mask, as the reference).
+    Without `draws` the Gamma variates are generated inside the kernel (keyed by the global element
+    index).  `return_stats=True` (needs `mask`) also returns (S_y (k,), mask.sum() (1,)) of
+    gibbs.py:86-94 for the state just produced — what the next sweep's resample_obs_variance needs —
+    accumulated in the same pass over Y."""
     lib = _lib.load()
     Y = f32(Y)
     dev = Y.device
@@ -501,15 +514,24 @@ def resample_scales(key, *, x, v, h, Y, Cd, sigmasq, nu_s, s_0, Gamma=None, draw
     x, v, h, sigmasq = f32(x, dev), f32(v, dev), f32(h, dev), f64(sigmasq, dev)
     D = x.shape[-1]
     Cdfull = expand_Cd(f64(Cd, dev), _gamma(Gamma, k, dev), dk)
-    if draws is not None:
-        g = f32(draws["g"], dev)
-    else:
-        g = dist.fill_gamma((N, T, k), (nu_s + 3) / 2, dist.seed_of(key), dist.STREAM_S, dev, session_offset)
+    g = f32(draws["g"], dev) if draws is not None else None
     sout = torch.empty((N, T, k), dtype=torch.float32, device=dev)
-    _lib.check(lib.kpms_resample_scales(
-        _lib.ptr(Y), _lib.ptr(v), _lib.ptr(h), _lib.ptr(x), _lib.ptr(Cdfull), _lib.ptr(sigmasq),
-        float(nu_s), float(s_0), _lib.ptr(g), N, T, k, dk, D, _lib.ptr(sout), _lib.stream_ptr(dev)),
-        "kpms_resample_scales")
+    S_y = msum = ws = None
+    if return_stats:
+        if mask is None:
+            raise ValueError("resample_scales(return_stats=True) needs mask")
+        mask = f32(mask, dev)
+        S_y = torch.empty((k,), dtype=torch.float64, device=dev)
+        msum = torch.empty((1,), dtype=torch.float64, device=dev)
+        ws = _lib.WORKSPACE.get("obsvar", lib.kpms_obs_variance_stats_workspace_bytes(N, T, k), dev)
+    _lib.check(lib.kpms_resample_scales_stats(
+        _lib.ptr(Y), _lib.ptr(mask) if return_stats else None, _lib.ptr(v), _lib.ptr(h), _lib.ptr(x),
+        _lib.ptr(Cdfull), _lib.ptr(sigmasq), float(nu_s), float(s_0), _lib.ptr(g), dist.seed_of(key),
+        dist.STREAM_S, int(session_offset) * T * k, N, T, k, dk, D, _lib.ptr(sout), _lib.ptr(S_y),
+        _lib.ptr(msum), _lib.ptr(ws), ws.numel() if ws is not None else 0, _lib.stream_ptr(dev)),
+        "kpms_resample_scales_stats")
+    if return_stats:
+        return sout, (S_y, msum)
     return sout
 
 

@@ -192,6 +192,19 @@ def _verify_and_repair(checks, flags_dev, run_from, world):
         run_from("x", True)
 
 
+OBS_STATS_KEY = "_obs_stats"   # entry of the states dict that carries next sweep's (S_y, mask sum)
+
+
+def _tensor_id(t):
+    return (t.data_ptr(), t._version, tuple(t.shape)) if torch.is_tensor(t) else id(t)
+
+
+def _obs_stats_tag(data, st, pr):
+    """Identity of everything the observation-noise statistics depend on: they are reused only when
+    the very tensors they were computed from come back unmodified."""
+    return tuple(_tensor_id(t) for t in (data["Y"], data["mask"], st["x"], st["v"], st["h"], st["s"], pr["Cd"]))
+
+
 def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessions_global=None,
                 session_offset=None, _wait=None, _done=None, _mark=None):
     """One full sweep.  `data`/`states` hold this rank's shard; `params` are replicated.
@@ -221,9 +234,14 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
     counts = G.transition_counts(z=st["z"], mask=data["mask"], num_states=K)
     mark("counts")
 
+    cached = st.pop(OBS_STATS_KEY, None)
+
     def obs_stats():
-        return G.obs_variance_stats(Y=data["Y"], mask=data["mask"], Cd=pr["Cd"], v=st["v"], h=st["h"],
-                                    x=st["x"], s=st["s"], Gamma=Gamma)
+        # the scales step of the previous sweep has already accumulated these over its pass of Y
+        if cached is not None and cached["tag"] == _obs_stats_tag(data, states, params):
+            return cached["S_y"], cached["msum"]
+        return G.obs_variance_stats(Y=data["Y"], mask=data["mask"], Cd=pr["Cd"], v=states["v"], h=states["h"],
+                                    x=states["x"], s=states["s"], Gamma=Gamma)
     S_y = msum = None
     flags_dev = None
     if not defer_obs:
@@ -274,9 +292,11 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
                                       Cd=pr["Cd"], sigmasq=pr["sigmasq"], sigmasq_loc=hyp["sigmasq_loc"],
                                       Gamma=Gamma, session_offset=off)
         done("v", st["v"])
-        st["s"] = G.resample_scales(key, x=st["x"], v=st["v"], h=st["h"], Y=data["Y"], Cd=pr["Cd"],
-                                    sigmasq=pr["sigmasq"], nu_s=hyp["nu_s"], s_0=hyp["s_0"], Gamma=Gamma,
-                                    session_offset=off)
+        st["s"], (S_new, m_new) = G.resample_scales(key, x=st["x"], v=st["v"], h=st["h"], Y=data["Y"], Cd=pr["Cd"],
+                                                    sigmasq=pr["sigmasq"], nu_s=hyp["nu_s"], s_0=hyp["s_0"],
+                                                    Gamma=Gamma, session_offset=off, mask=data["mask"],
+                                                    return_stats=True)
+        st[OBS_STATS_KEY] = {"S_y": S_new, "msum": m_new, "tag": _obs_stats_tag(data, st, pr)}
         done("s", st["s"])
         mark("hvs")
 

@@ -259,7 +259,60 @@ def test_gibbs_sweep_equals_step_sequence(G):
         assert torch.equal(pr[name], q[name]), name
     for name in ('z', 'x', 'h', 'v', 's'):
         assert torch.equal(st[name], t[name]), name
-    assert set(ss) == set(st) and all(ss[a] is not st[a] for a in ('z', 'x', 'h', 'v', 's'))   # inputs untouched
+    assert set(ss) == {a for a in st if not a.startswith("_")} and all(ss[a] is not st[a] for a in ('z', 'x', 'h', 'v', 's'))   # inputs untouched
+
+
+def test_gibbs_sweep_reuses_scales_pass_statistics(G):
+    """The scales step leaves next sweep's observation-noise statistics behind (same pass over Y): a
+    second sweep that gets the states back untouched gives exactly what it gives when it recomputes
+    them, and the statistics themselves equal kpms_obs_variance_stats on the new state."""
+    import torch
+    from keypointmoseq_b200 import parallel
+    N, T, k, D, L, K = 3, 400, 8, 10, 3, 6
+    d, s, p, Gm, dd, ss, pp = _device_problem(73, N, T, k, D, L, K)
+    hp = {a: (T_(b) if isinstance(b, np.ndarray) else b) for a, b in H.hyp(D, L, K).items()}
+    st1, pr1 = parallel.gibbs_sweep((2, 0), dd, ss, pp, hp, Gamma=T_(Gm))
+    cache = st1[parallel.OBS_STATS_KEY]
+    S_ref, m_ref = G.obs_variance_stats(Y=dd["Y"], mask=dd["mask"], Cd=pr1["Cd"], v=st1["v"], h=st1["h"], x=st1["x"],
+                                        s=st1["s"], Gamma=T_(Gm))
+    assert torch.allclose(cache["S_y"], S_ref, rtol=1e-12) and torch.equal(cache["msum"], m_ref)
+    st2a, pr2a = parallel.gibbs_sweep((2, 1), dd, st1, pr1, hp, Gamma=T_(Gm))
+    plain = {a: b for a, b in st1.items() if not a.startswith("_")}
+    st2b, pr2b = parallel.gibbs_sweep((2, 1), dd, plain, pr1, hp, Gamma=T_(Gm))
+    assert torch.allclose(pr2a["sigmasq"], pr2b["sigmasq"], rtol=1e-12)
+    for name in ("z", "x", "h", "v", "s"):
+        assert torch.equal(st2a[name], st2b[name]) or torch.allclose(st2a[name].double(), st2b[name].double(), rtol=1e-5), name
+    # a state modified in place invalidates the cache
+    st1["s"].mul_(1.5)
+    st3, pr3 = parallel.gibbs_sweep((2, 1), dd, st1, pr1, hp, Gamma=T_(Gm))
+    S_mod, m_mod = G.obs_variance_stats(Y=dd["Y"], mask=dd["mask"], Cd=pr1["Cd"], v=st1["v"], h=st1["h"], x=st1["x"],
+                                        s=st1["s"], Gamma=T_(Gm))
+    want = G.sample_obs_variance((2, 1), S_mod, m_mod, nu_sigma=hp["nu_sigma"], sigmasq_0=hp["sigmasq_0"])
+    assert torch.allclose(pr3["sigmasq"], want, rtol=1e-12)
+
+
+def test_heading_and_scales_in_kernel_draws(G):
+    """Default (no injected draws) paths: scales with in-kernel Gamma variates equal the injected path fed
+    with kpms_fill_gamma's values; the heading sampler never exhausts its proposals and follows the von Mises
+    concentration."""
+    import torch
+    from keypointmoseq_b200 import distributions as dist
+    N, T, k, D, L, K = 3, 300, 8, 10, 3, 5
+    d, s, p, Gm, dd, ss, pp = _device_problem(74, N, T, k, D, L, K)
+    hp = H.hyp(D, L, K)
+    kw = dict(**dd, **ss, **pp, Gamma=T_(Gm), nu_s=hp["nu_s"], s_0=hp["s_0"])
+    s_a = G.resample_scales(9, **kw, session_offset=2)
+    g = dist.fill_gamma((N, T, k), (hp["nu_s"] + 3) / 2, dist.seed_of(9), dist.STREAM_S, "cuda", first_row=2)
+    s_b = G.resample_scales(9, **kw, draws={"g": g})
+    assert torch.equal(s_a, s_b)
+    h, info = G.resample_heading(9, **dd, **ss, **pp, Gamma=T_(Gm), return_info=True)
+    assert int(info["exhausted"]) == 0
+    dev_ = torch.remainder(h.double() - info["theta"] + np.pi, 2 * np.pi) - np.pi
+    strong = info["kappa"] > 50
+    assert bool(strong.any()) and float(dev_[strong].abs().max()) < 1.0
+    assert abs(float((dev_[strong] * info["kappa"][strong].sqrt()).std()) - 1.0) < 0.1   # ~ N(0, 1/kappa) at large kappa
+    h2 = G.resample_heading(9, **dd, **ss, **pp, Gamma=T_(Gm))
+    assert torch.equal(h, h2)
 
 
 def test_gibbs_sweep_repairs_a_failed_chunk_check(G):
