@@ -13,7 +13,7 @@ static int env_int(const char* name, int dflt) {
   return (e && e[0]) ? atoi(e) : dflt;
 }
 KpmsOptions kpms_opts = {env_int("KPMS_KALMAN_IMPL", 2), env_int("KPMS_HMM_TC", 1), env_int("KPMS_HMM_BWD_BURN", -1),
-                         env_int("KPMS_LL_TILED", 0), env_int("KPMS_HMM_FLAGS", 0), env_int("KPMS_KALMAN_WARPS", 12),
+                         env_int("KPMS_LL_TILED", 0), env_int("KPMS_HMM_FLAGS", 0), env_int("KPMS_LOCATION_IMPL", 0), env_int("KPMS_KALMAN_WARPS", 12),
                          env_int("KPMS_KALMAN_LOCKSTEP", 0)};
 
 static int* option_slot(const char* name) {
@@ -23,6 +23,7 @@ static int* option_slot(const char* name) {
   if (!strcmp(name, "hmm_bwd_burn")) return &kpms_opts.hmm_bwd_burn;
   if (!strcmp(name, "ll_tiled")) return &kpms_opts.ll_tiled;
   if (!strcmp(name, "hmm_flags")) return &kpms_opts.hmm_flags;
+  if (!strcmp(name, "location_impl")) return &kpms_opts.location_impl;
   if (!strcmp(name, "kalman_warps")) return &kpms_opts.kalman_warps;
   if (!strcmp(name, "kalman_lockstep")) return &kpms_opts.kalman_lockstep;
   return nullptr;

@@ -25,6 +25,7 @@ struct KpmsOptions {
   int hmm_bwd_burn;  // >= 0: warm-up of the HMM sampler only (0 forces every chunk through the repair pass)
   int ll_tiled;      // 1: the emission kernel writes the interleaved HMM layout directly
   int hmm_flags;     // bit 0: forward pass only (timing)
+  int location_impl; // 0 (default): exact associative scan over time; 1: chunks with a fixed warm-up (no verification)
   int kalman_warps;  // warps per CTA of the blocked Kalman filter: 8, 12 (default) or 16
   int kalman_lockstep;  // 1: the warps of a CTA step together (helps the lane-per-column kernel, not the blocked one; default 0)
 };

@@ -771,10 +771,12 @@ __host__ __device__ static inline int loc_nchunks(int T) {
 extern "C" size_t kpms_resample_location_workspace_bytes(int N, int T, int dk) {
   if (N <= 0 || T <= 0 || dk <= 0) return 0;
   // stats: (2+dk) doubles per frame; filter: (1+dk) doubles per frame; ll partials; tv
+  const size_t units = (size_t)N * ((T - 1 + 127) / 128 + 1);   // chunks of the scan variant (LSC_CHUNK = 128) >= those of the warm-up variant
   return kpms_round_up((size_t)N * T * (2 + dk) * sizeof(double), 256) +
          kpms_round_up((size_t)N * T * (1 + dk) * sizeof(double), 256) +
-         kpms_round_up((size_t)N * loc_nchunks(T) * sizeof(double), 256) +
-         kpms_round_up((size_t)N * sizeof(int), 256);
+         kpms_round_up(units * sizeof(double), 256) +
+         kpms_round_up((size_t)N * sizeof(int), 256) +
+         kpms_round_up(units * (6 + 2 * dk) * sizeof(double), 256);
 }
 
 __global__ void __launch_bounds__(256)
@@ -994,6 +996,242 @@ __global__ void __launch_bounds__(64)
   }
 }
 
+// ------------------------------------------------------------------ exact time-parallel variant
+// In this scalar model every pass over time is a composition of maps that compose in closed form:
+//   filter precision   lam' = (lam + rg) / (q lam + q rg + 1)          a Moebius map (2 x 2 matrix)
+//   filter mean        eta' = r_t (eta + em_t),  r_t = 1/(q (lam_t + rg_t) + 1)   affine given the lam path
+//   backward sample    x_t  = a_t x_{t+1} + b_t,  a_t = S_t / q,  b_t = S_t ec_t + sqrt(S_t) w_t   affine
+// so the session is cut into chunks, every chunk composes its map, a chunk's exact starting value
+// is the composition of the maps of the chunks before (after) it applied to the prior (to x_last), and
+// the chunk is then run from that value: an associative scan over time, two levels deep, with no
+// warm-up, no tolerance and no fallback (kalman.py:86-95,129-140 specialised as in gibbs.py:38-54).
+#define LSC_CHUNK 128
+__host__ __device__ static inline int lsc_nchunks(int T) { return (T - 1 + LSC_CHUNK - 1) / LSC_CHUNK; }
+
+struct LocScan {
+  double* mob;   // [units][4]  Moebius map of the chunk's filter-precision recursion
+  double* fA;    // [units]     affine map of the chunk's filter-mean recursion: eta_out = fA eta_in + fB
+  double* fB;    // [units][DK]
+  double* bA;    // [units]     affine map of the chunk's backward recursion: x_out = bA x_in + bB
+  double* bB;    // [units][DK]
+};
+
+__device__ __forceinline__ double lsc_lam_start(const double* __restrict__ mob, int n, int nch, int cc) {
+  double lam = 1e-6;   // gibbs.py:48: S0 = 1e6 I
+  const double* m = mob + (size_t)n * nch * 4;
+  for (int c = 0; c < cc; c++) lam = fma(m[4 * c], lam, m[4 * c + 1]) / fma(m[4 * c + 2], lam, m[4 * c + 3]);
+  return lam;
+}
+
+// pass 1: Moebius composite of every chunk
+__global__ void __launch_bounds__(64) lsc_mobius_kernel(const double* __restrict__ st, const float* __restrict__ mask,
+                                                         double q, int N, int T, int DK, LocScan ls) {
+  const int nch = lsc_nchunks(T);
+  const int unit = blockIdx.x * blockDim.x + threadIdx.x;
+  if (unit >= N * nch) return;
+  const int n = unit / nch, cc = unit % nch;
+  const int t0 = cc * LSC_CHUNK, t1 = min(T - 1, t0 + LSC_CHUNK);
+  const double* st_n = st + (size_t)n * T * (2 + DK);
+  const float* mk = mask + (size_t)n * T;
+  double a = 1.0, b = 0.0, c = 0.0, d = 1.0;
+  int since = 0;
+  for (int t = t0; t < t1; t++) {
+    if (!(mk[t] > 0.0f)) continue;
+    const double rg = st_n[(size_t)t * (2 + DK)];
+    // [1 rg; q q rg + 1] . [a b; c d]
+    const double na = fma(rg, c, a), nb = fma(rg, d, b);
+    const double nc = fma(q, na, c), nd = fma(q, nb, d);
+    a = na; b = nb; c = nc; d = nd;
+    if (++since == 8) {   // the map is projective: rescale before the entries grow out of range
+      const double sc = 1.0 / d;
+      a *= sc; b *= sc; c *= sc; d = 1.0;
+      since = 0;
+    }
+  }
+  double* m = ls.mob + (size_t)unit * 4;
+  m[0] = a; m[1] = b; m[2] = c; m[3] = d;
+}
+
+// pass 2: with the exact starting precision, the affine map of the chunk's mean recursion
+template <int DK>
+__global__ void __launch_bounds__(64) lsc_mean_map_kernel(const double* __restrict__ st, const float* __restrict__ mask,
+                                                           double q, int N, int T, LocScan ls) {
+  const int nch = lsc_nchunks(T);
+  const int unit = blockIdx.x * blockDim.x + threadIdx.x;
+  if (unit >= N * nch) return;
+  const int n = unit / nch, cc = unit % nch;
+  const int t0 = cc * LSC_CHUNK, t1 = min(T - 1, t0 + LSC_CHUNK);
+  const double* st_n = st + (size_t)n * T * (2 + DK);
+  const float* mk = mask + (size_t)n * T;
+  double lam = lsc_lam_start(ls.mob, n, nch, cc);
+  double A = 1.0, Bv[DK];
+#pragma unroll
+  for (int dd = 0; dd < DK; dd++) Bv[dd] = 0.0;
+  for (int t = t0; t < t1; t++) {
+    if (!(mk[t] > 0.0f)) continue;
+    const double* o = st_n + (size_t)t * (2 + DK);
+    const double lc = lam + o[0];
+    const double r = 1.0 / fma(q, lc, 1.0);
+    A *= r;
+#pragma unroll
+    for (int dd = 0; dd < DK; dd++) Bv[dd] = (Bv[dd] + o[1 + dd]) * r;
+    lam = lc * r;
+  }
+  ls.fA[unit] = A;
+#pragma unroll
+  for (int dd = 0; dd < DK; dd++) ls.fB[(size_t)unit * DK + dd] = Bv[dd];
+}
+
+// pass 3: the filter itself from the exact chunk start (records for the sampler, log-likelihood, last state),
+// and the affine map of the chunk's backward recursion
+template <int DK>
+__global__ void __launch_bounds__(64) lsc_filter_kernel(const double* __restrict__ st, const float* __restrict__ mask,
+                                                         const float* __restrict__ w, const float* __restrict__ w_last,
+                                                         double q, int N, int T, int want_ll, double* __restrict__ fw,
+                                                         double* __restrict__ llpart, float* __restrict__ v_out,
+                                                         LocScan ls) {
+  const int nch = lsc_nchunks(T);
+  const int unit = blockIdx.x * blockDim.x + threadIdx.x;
+  if (unit >= N * nch) return;
+  const int n = unit / nch, cc = unit % nch;
+  const int Tt = T - 1;
+  const int t0 = cc * LSC_CHUNK, t1 = min(Tt, t0 + LSC_CHUNK);
+  const double* st_n = st + (size_t)n * T * (2 + DK);
+  double* fw_n = fw + (size_t)n * T * (1 + DK);
+  const float* mk = mask + (size_t)n * T;
+  const float* w_n = w + (size_t)n * Tt * DK;
+  const double lq = log(q), iq = 1.0 / q;
+  double lam = lsc_lam_start(ls.mob, n, nch, cc);
+  double eta[DK];
+#pragma unroll
+  for (int dd = 0; dd < DK; dd++) eta[dd] = 0.0;   // gibbs.py:48: m0 = 0
+  for (int c = 0; c < cc; c++) {
+    const double A = ls.fA[(size_t)n * nch + c];
+#pragma unroll
+    for (int dd = 0; dd < DK; dd++) eta[dd] = fma(A, eta[dd], ls.fB[((size_t)n * nch + c) * DK + dd]);
+  }
+  double ll = (cc == 0) ? 0.5 * DK * log(1e-6) : 0.0;
+  // records first (forward in time), then the backward map is composed from them (backward in time)
+  for (int t = t0; t < t1; t++) {
+    if (!(mk[t] > 0.0f)) continue;
+    const double* o = st_n + (size_t)t * (2 + DK);
+    const double lc = lam + o[0];
+    const double r = 1.0 / fma(q, lc, 1.0);
+    const double Lc = sqrt(q * r);
+    double* fo = fw_n + (size_t)t * (1 + DK);
+    fo[0] = Lc;
+    double uu = 0.0;
+#pragma unroll
+    for (int dd = 0; dd < DK; dd++) {
+      const double ec = eta[dd] + o[1 + dd];
+      fo[1 + dd] = ec;
+      eta[dd] = ec * r;
+      uu = fma(Lc * ec, Lc * ec, uu);
+    }
+    lam = lc * r;
+    if (want_ll) ll += o[1 + DK] - 0.5 * DK * lq + DK * log(Lc) + 0.5 * uu;
+  }
+  if (cc == nch - 1) {
+    // unconditional final update (kalman.py:117) and draw of the last state (kalman.py:150)
+    const double* o = st_n + (size_t)(T - 1) * (2 + DK);
+    const double lc = lam + o[0];
+    const double Ll = 1.0 / sqrt(lc);
+    double tt = 0.0;
+    double* xl = fw_n + (size_t)(T - 1) * (1 + DK);
+#pragma unroll
+    for (int dd = 0; dd < DK; dd++) {
+      const double ec = eta[dd] + o[1 + dd];
+      const double td = Ll * ec;
+      tt = fma(td, td, tt);
+      const double xv = Ll * (td + (double)w_last[(size_t)n * DK + dd]);
+      xl[1 + dd] = xv;
+      v_out[((size_t)n * T + (T - 1)) * DK + dd] = (float)xv;
+    }
+    ll += o[1 + DK] + DK * log(Ll) + 0.5 * tt;
+  }
+  llpart[(size_t)n * nch + cc] = ll;
+  double A = 1.0, Bv[DK];
+#pragma unroll
+  for (int dd = 0; dd < DK; dd++) Bv[dd] = 0.0;
+  for (int t = t1 - 1; t >= t0; t--) {
+    if (!(mk[t] > 0.0f)) continue;   // kalman.py:142-143: the carried sample is unchanged
+    const double* fo = fw_n + (size_t)t * (1 + DK);
+    const double Lc = fo[0], at = Lc * Lc * iq;
+    A *= at;
+#pragma unroll
+    for (int dd = 0; dd < DK; dd++)
+      Bv[dd] = fma(at, Bv[dd], Lc * fma(Lc, fo[1 + dd], (double)w_n[(size_t)t * DK + dd]));
+  }
+  ls.bA[unit] = A;
+#pragma unroll
+  for (int dd = 0; dd < DK; dd++) ls.bB[(size_t)unit * DK + dd] = Bv[dd];
+}
+
+// pass 4: backward sampler from the exact chunk start
+template <int DK>
+__global__ void __launch_bounds__(64) lsc_sample_kernel(const double* __restrict__ fw, const float* __restrict__ mask,
+                                                         const float* __restrict__ w, double q, int N, int T,
+                                                         const double* __restrict__ llpart, float* __restrict__ v_out,
+                                                         double* __restrict__ loglik, LocScan ls) {
+  const int nch = lsc_nchunks(T);
+  const int unit = blockIdx.x * blockDim.x + threadIdx.x;
+  if (unit >= N * nch) return;
+  const int n = unit / nch, cc = unit % nch;
+  const int Tt = T - 1;
+  const int t0 = cc * LSC_CHUNK, t1 = min(Tt, t0 + LSC_CHUNK);
+  const double* fw_n = fw + (size_t)n * T * (1 + DK);
+  const float* mk = mask + (size_t)n * T;
+  const float* w_n = w + (size_t)n * Tt * DK;
+  const double iq = 1.0 / q;
+  if (cc == 0 && loglik != nullptr) {
+    double s = 0.0;
+    for (int c = 0; c < nch; c++) s += llpart[(size_t)n * nch + c];
+    loglik[n] = s;
+  }
+  double xv[DK];
+#pragma unroll
+  for (int dd = 0; dd < DK; dd++) xv[dd] = fw_n[(size_t)(T - 1) * (1 + DK) + 1 + dd];
+  for (int c = nch - 1; c > cc; c--) {
+    const double A = ls.bA[(size_t)n * nch + c];
+#pragma unroll
+    for (int dd = 0; dd < DK; dd++) xv[dd] = fma(A, xv[dd], ls.bB[((size_t)n * nch + c) * DK + dd]);
+  }
+  for (int t = t1 - 1; t >= t0; t--) {
+    if (mk[t] > 0.0f) {
+      const double* fo = fw_n + (size_t)t * (1 + DK);
+      const double Lc = fo[0];
+#pragma unroll
+      for (int dd = 0; dd < DK; dd++) {
+        const double hh = fma(xv[dd], iq, fo[1 + dd]);
+        xv[dd] = Lc * fma(Lc, hh, (double)w_n[(size_t)t * DK + dd]);
+        v_out[((size_t)n * T + t) * DK + dd] = (float)xv[dd];
+      }
+    } else {
+#pragma unroll
+      for (int dd = 0; dd < DK; dd++) v_out[((size_t)n * T + t) * DK + dd] = 0.0f;  // kalman.py:142-143
+    }
+  }
+}
+
+template <int DK>
+static int launch_location_scan(const double* stats, const float* mask, const float* w, const float* w_last, double q,
+                                int N, int T, double* fw, double* llpart, float* v_out, double* loglik, LocScan ls,
+                                cudaStream_t st) {
+  const int nch = lsc_nchunks(T);
+  const unsigned grid = (unsigned)((N * nch + 63) / 64);
+  lsc_mobius_kernel<<<grid, 64, 0, st>>>(stats, mask, q, N, T, DK, ls);
+  int rc = kpms_last_launch();
+  if (rc) return rc;
+  lsc_mean_map_kernel<DK><<<grid, 64, 0, st>>>(stats, mask, q, N, T, ls);
+  rc = kpms_last_launch();
+  if (rc) return rc;
+  lsc_filter_kernel<DK><<<grid, 64, 0, st>>>(stats, mask, w, w_last, q, N, T, loglik != nullptr, fw, llpart, v_out, ls);
+  rc = kpms_last_launch();
+  if (rc) return rc;
+  lsc_sample_kernel<DK><<<grid, 64, 0, st>>>(fw, mask, w, q, N, T, llpart, v_out, loglik, ls);
+  return kpms_last_launch();
+}
+
 extern "C" int kpms_resample_location(const float* Y, const float* mask, const float* h,
                                       const float* x, const float* s, const double* Cdfull,
                                       const double* sigmasq, double sigmasq_loc, const float* w,
@@ -1022,7 +1260,14 @@ extern "C" int kpms_resample_location(const float* Y, const float* mask, const f
   char* p2 = (char*)fw + kpms_round_up((size_t)N * T * (1 + dk) * sizeof(double), 256);
   double* llpart = (double*)p2;
   const int nch = loc_nchunks(T);
-  int* tv = (int*)(p2 + kpms_round_up((size_t)N * nch * sizeof(double), 256));
+  const size_t units = (size_t)N * ((T - 1 + 127) / 128 + 1);
+  int* tv = (int*)(p2 + kpms_round_up(units * sizeof(double), 256));
+  if (kpms_opts.location_impl != 1) {   // default: exact two-level scan over time
+    double* sc = (double*)((char*)tv + kpms_round_up((size_t)N * sizeof(int), 256));
+    LocScan ls{sc, sc + units * 4, sc + units * 5, sc + units * (5 + dk), sc + units * (6 + dk)};
+    return (dk == 2) ? launch_location_scan<2>(stats, mask, w, w_last, sigmasq_loc, N, T, fw, llpart, v_out, loglik, ls, st)
+                     : launch_location_scan<3>(stats, mask, w, w_last, sigmasq_loc, N, T, fw, llpart, v_out, loglik, ls, st);
+  }
   location_tv_kernel<<<N, 128, 0, st>>>(mask, T, tv);
   rc = kpms_last_launch();
   if (rc) return rc;
