@@ -75,18 +75,16 @@ def main():
     gathered = [torch.empty_like(par) for _ in range(world)]
     td.all_gather(gathered, par)
     res["params_identical_across_ranks"] = bool(all(torch.equal(g, par) for g in gathered))
-    zs = [torch.empty((parallel.shard_range(N, r, world)[1] - parallel.shard_range(N, r, world)[0], T - L),
-                      dtype=torch.int32, device=dev) for r in range(world)]
-    xs = [torch.empty((z.shape[0], T, D), dtype=torch.float32, device=dev) for z in zs]
-    td.all_gather(zs, ss["z"].contiguous())
-    td.all_gather(xs, ss["x"].contiguous())
+    zs, xs = [None] * world, [None] * world     # shards differ in size: gather as objects
+    td.all_gather_object(zs, ss["z"].cpu())
+    td.all_gather_object(xs, ss["x"].cpu())
     if rank == 0:
         us, up = full_s, p
         for i in range(2):
             us, up = parallel.gibbs_sweep((3, i), full_d, us, up, hyp, Gamma=Gm, group=solo, session_offset=0)
         res["params_max_rel_diff_vs_unsharded"] = max(
             float((pp[a] - up[a]).abs().max() / up[a].abs().max()) for a in ("Ab", "Q", "pi", "betas", "sigmasq"))
-        zcat, xcat = torch.cat(zs), torch.cat(xs)
+        zcat, xcat = torch.cat(zs).to(dev), torch.cat(xs).to(dev)
         valid = full_d["mask"][:, L:] > 0
         res["z_agreement_vs_unsharded"] = float((zcat[valid] == us["z"][valid]).float().mean())
         res["x_max_abs_diff_vs_unsharded"] = float((xcat - us["x"]).abs().max())
