@@ -352,7 +352,7 @@ def main():
 
     def sweep(i, dd, ss, pp):
         if slds:
-            return parallel.gibbs_sweep((0, i), dd, ss, pp, hyp, Gamma=Gm, session_offset=off)
+            return parallel.gibbs_sweep((0, i), dd, ss, pp, hyp, Gamma=Gm, session_offset=off, next_key=(0, i + 1))
         return parallel.arhmm_sweep((0, i), dd, ss, pp, hyp, session_offset=off)
 
     # ---- device-resident arm

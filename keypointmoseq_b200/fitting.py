@@ -102,7 +102,8 @@ def fit(key, data, states, params, *, trans_hypparams, ar_hypparams, obs_hyppara
                                           session_offset=session_offset)
         else:
             st, pr = parallel.gibbs_sweep((key, i), data, st, pr, hyp_full, Gamma=Gamma, group=group,
-                                          session_offset=session_offset)
+                                          session_offset=session_offset,
+                                          next_key=(key, i + 1) if i + 1 < total else None)
         if log_every and (i % log_every == 0 or i == total - 1):
             usage, durations = G.stateseq_stats(st["z"], data["mask"])
             rec = {"iteration": i, "phase": "ar_only" if warm else ("full" if full else "arhmm"),
@@ -113,5 +114,6 @@ def fit(key, data, states, params, *, trans_hypparams, ar_hypparams, obs_hyppara
                 log_fn(rec)
         if checkpoint_dir and ((i + 1) % int(checkpoint_every) == 0 or i == total - 1):
             save_checkpoint(checkpoint_dir, i, st, pr, history, rank, "ar_only" if warm else "full")
-    st.pop(parallel.OBS_STATS_KEY, None)   # the sweeps' private cache of next sweep's statistics
+    st.pop(parallel.OBS_STATS_KEY, None)   # the sweeps' private caches of next sweep's statistics / parameters
+    st.pop(parallel.NEXT_PARAMS_KEY, None)
     return st, pr, history

@@ -146,25 +146,54 @@ def _apply_verdicts(failed, comfortable, reported):
         A["streak"] = 0
 
 
-def _verify_and_repair(checks, flags_dev, run_from, world):
-    """ONE device->host read of everything a sweep left to verify; redo what failed."""
-    parts, names = [], []
-    for name in ("z", "x"):
-        if name in checks and checks[name] is not None:
-            parts.append(checks[name].reshape(-1).to(torch.float64))
-            names.append((name, checks[name].numel()))
+def _verify_and_repair(checks, flags_dev, run_from, world, group=None, st=None):
+    """ONE device->host read of everything a sweep left to verify; redo what failed.
+    Sharded: the mismatches are also MAX-reduced over the ranks (a 3-float all-reduce enqueued before
+    the read), because work drawn ahead for the next sweep (`next_key`) contains collectives: if ANY
+    rank has to redo a step, EVERY rank discards what it drew ahead, so that all ranks issue the same
+    collectives in the next sweep."""
+    import torch.distributed as td
+    dev = None
+    for t in list(checks.values()) + [flags_dev]:
+        if torch.is_tensor(t):
+            dev = t.device
+    if dev is None:
+        if world == 1:
+            return
+        dev = torch.device("cuda", torch.cuda.current_device())
+    # fixed layout [z mismatch, x filter mismatch, x sampler mismatch]; 0 where a pass ran sequentially
+    zc = checks.get("z")
+    xc = checks.get("x")
+    local = torch.cat([zc.reshape(-1)[:1].to(torch.float64) if zc is not None else torch.zeros(1, dtype=torch.float64, device=dev),
+                       xc.reshape(-1)[:2].to(torch.float64) if xc is not None else torch.zeros(2, dtype=torch.float64, device=dev)])
+    local = torch.nan_to_num(local, nan=float("inf"), posinf=float("inf"))
+    parts = [local]
+    if world > 1:   # every rank, every sweep: the same collective whatever the local chunking decided
+        glob = local.clone()
+        td.all_reduce(glob, op=td.ReduceOp.MAX, group=group)
+        parts.append(glob)
     if flags_dev is not None:
-        parts.append(flags_dev.reshape(-1))
-    if not parts:
-        return
+        parts.append(flags_dev.reshape(-1).to(torch.float64))
     host = torch.cat(parts).cpu().tolist()      # the sweep's only synchronisation
-    o, vals = 0, {}
-    for name, cnt in names:
-        vals[name] = max(float("inf") if v != v else v for v in host[o:o + cnt])
-        o += cnt
-    if flags_dev is not None:                    # verdicts of the PREVIOUS sweep, summed over the ranks
+    vals = {}
+    if zc is not None:
+        vals["z"] = host[0]
+    if xc is not None:
+        vals["x"] = max(host[1], host[2])
+    o = 3
+    gvals = dict(vals)
+    if world > 1:
+        gvals = {"z": host[3], "x": max(host[4], host[5])}
+        o = 6
+    if flags_dev is not None:                    # verdicts of an earlier sweep, summed over the ranks
         _apply_verdicts(*host[o:o + _N_FLAGS])
-    tolz = G.STATESEQ_CHUNKING["tol"]
+    tolz, tolx = G.STATESEQ_CHUNKING["tol"], G.LATENTS_CHUNKING["tol"]
+    any_failed = ("z" in gvals and not gvals["z"] <= tolz) or ("x" in gvals and not gvals["x"] <= tolx)
+    if any_failed and st is not None:
+        st.pop(NEXT_PARAMS_KEY, None)
+        oc = st.get(OBS_STATS_KEY)
+        if oc is not None and oc.get("reduced"):
+            oc.update(S_y=oc["S_local"], msum=oc["m_local"], reduced=False)
     verdict = [0.0, 0.0, 0.0]
     z_failed = False
     if "z" in vals:
@@ -187,7 +216,7 @@ def _verify_and_repair(checks, flags_dev, run_from, world):
         run_from("z", True)
         if world > 1:
             G._HMM_ADAPT.update(saved)
-    elif "x" in vals and not (vals["x"] <= G.LATENTS_CHUNKING["tol"]):
+    elif "x" in vals and not (vals["x"] <= tolx):
         G.FALLBACKS["latents"] += 1
         run_from("x", True)
 
@@ -205,13 +234,42 @@ def _obs_stats_tag(data, st, pr):
     return tuple(_tensor_id(t) for t in (data["Y"], data["mask"], st["x"], st["v"], st["h"], st["s"], pr["Cd"]))
 
 
+NEXT_PARAMS_KEY = "_next_params"   # entry of the states dict: next sweep's Ab, Q, betas, pi, drawn ahead
+
+
+def _draw_dynamics_params(key, data, st, pr, hyp, group, world, with_obs=None):
+    """Steps 1 and 3 of a sweep from the states in `st`: AR statistics + transition counts (one packed
+    all-reduce when sharded, which also carries `with_obs` = (S_y, mask sum) and the ranks' verdicts on
+    their last chunked HMM pass), then the replicated draws of Ab, Q, betas, pi."""
+    K = int(hyp["num_states"])
+    F = G.ar_sufficient_stats(nlags=hyp["nlags"], num_states=K, mask=data["mask"], x=st["x"], z=st["z"])
+    counts = G.transition_counts(z=st["z"], mask=data["mask"], num_states=K)
+    S_y, msum = with_obs if with_obs is not None else (None, None)
+    flags_dev = None
+    if world > 1:
+        F, S_y, msum, counts, flags_dev = all_reduce_stats(F, S_y, msum, counts, group, _local_verdict(F.device))
+    out = {}
+    out["Ab"], out["Q"] = G.sample_ar_params(key, F, nlags=hyp["nlags"], nu_0=hyp["nu_0"], S_0=hyp["S_0"],
+                                             M_0=hyp["M_0"], K_0=hyp["K_0"])
+    out["betas"], out["pi"] = G.sample_hdp_transitions(key, counts, pr["betas"], hyp["alpha"], hyp["kappa"],
+                                                       hyp["gamma"])
+    return out, S_y, msum, flags_dev
+
+
 def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessions_global=None,
-                session_offset=None, _wait=None, _done=None, _mark=None):
+                session_offset=None, next_key=None, _wait=None, _done=None, _mark=None):
     """One full sweep.  `data`/`states` hold this rank's shard; `params` are replicated.
     Returns new (states, params) dicts; inputs are not mutated.
 
     `session_offset`: global index of this shard's first session (default: gathered once from the
     shard sizes, contiguous in rank order).  `n_sessions_global` is accepted for compatibility.
+
+    `next_key`: the key the NEXT sweep will be called with.  When given, that sweep's steps 1 and 3
+    (AR statistics, transition counts, their all-reduce and the draws of Ab, Q, betas, pi — they depend
+    on the new z and x only) are enqueued right after the latents, while the GPU still has the pose
+    steps to run; the results travel in the returned states dict and are used by the next call if it
+    presents the same tensors and the same key.  The sweep is unchanged; the launch latency of ~60 small
+    kernels and the all-reduce leave the critical path.
 
     `_wait(group)` / `_done(name, tensor)` are the hooks of `gibbs_sweep_host`: `_wait("xz")` is
     called before x, z and mask are first read, `_wait("all")` before Y, v, h and s are, and
@@ -224,39 +282,45 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
     mark = _mark or (lambda label: None)
     defer_obs = _wait is not None
     st, pr = dict(states), dict(params)
-    K = int(hyp["num_states"])
     N = st["z"].shape[0]
     off = session_offset_of(N, group) if session_offset is None else int(session_offset)
-    dev = st["z"].device if torch.is_tensor(st["z"]) else None
     wait("xz")
-    F = G.ar_sufficient_stats(nlags=hyp["nlags"], num_states=K, mask=data["mask"], x=st["x"], z=st["z"])
-    mark("ar_stats")
-    counts = G.transition_counts(z=st["z"], mask=data["mask"], num_states=K)
-    mark("counts")
-
     cached = st.pop(OBS_STATS_KEY, None)
+    ahead = st.pop(NEXT_PARAMS_KEY, None)
 
     def obs_stats():
         # the scales step of the previous sweep has already accumulated these over its pass of Y
         if cached is not None and cached["tag"] == _obs_stats_tag(data, states, params):
-            return cached["S_y"], cached["msum"]
-        return G.obs_variance_stats(Y=data["Y"], mask=data["mask"], Cd=pr["Cd"], v=states["v"], h=states["h"],
+            return cached["S_y"], cached["msum"], cached.get("reduced", False)
+        S, m = G.obs_variance_stats(Y=data["Y"], mask=data["mask"], Cd=pr["Cd"], v=states["v"], h=states["h"],
                                     x=states["x"], s=states["s"], Gamma=Gamma)
+        return S, m, False
     S_y = msum = None
     flags_dev = None
-    if not defer_obs:
-        S_y, msum = obs_stats()
-        if world > 1:
-            F, S_y, msum, counts, flags_dev = all_reduce_stats(F, S_y, msum, counts, group, _local_verdict(F.device))
-    elif world > 1:
-        F, _, _, counts, flags_dev = all_reduce_stats(F, None, None, counts, group, _local_verdict(F.device))
-    # 1-3: replicated parameter draws (same key on every rank)
-    pr["Ab"], pr["Q"] = G.sample_ar_params(key, F, nlags=hyp["nlags"], nu_0=hyp["nu_0"], S_0=hyp["S_0"],
-                                           M_0=hyp["M_0"], K_0=hyp["K_0"])
+    if (ahead is not None and ahead["key"] == key and ahead["world"] == world and
+            ahead["tag"] == tuple(_tensor_id(t) for t in (states["x"], states["z"], data["mask"], params["betas"]))):
+        # steps 1 and 3 were drawn at the end of the previous sweep, from these very states
+        pr.update(ahead["params"])
+        flags_dev = ahead["flags"]
+        if not defer_obs:
+            S_y, msum, reduced = obs_stats()
+            if world > 1 and not reduced:
+                S_y, msum = all_reduce_obs_stats(S_y, msum, group)
+    else:
+        with_obs = None
+        if not defer_obs:
+            S_y, msum, reduced = obs_stats()
+            if world > 1 and reduced:      # cannot be packed again: reduce the rest alone
+                with_obs = None
+            else:
+                with_obs = (S_y, msum)
+        drawn, S2, m2, flags_dev = _draw_dynamics_params(key, data, st, pr, hyp, group, world, with_obs)
+        if with_obs is not None and world > 1:
+            S_y, msum = S2, m2
+        pr.update(drawn)
+    mark("params_dyn")
     if not defer_obs:
         pr["sigmasq"] = G.sample_obs_variance(key, S_y, msum, nu_sigma=hyp["nu_sigma"], sigmasq_0=hyp["sigmasq_0"])
-    pr["betas"], pr["pi"] = G.sample_hdp_transitions(key, counts, pr["betas"], hyp["alpha"], hyp["kappa"],
-                                                     hyp["gamma"])
     mark("params")
     # 4-8: per-session steps on the local shard, launched without waiting for their verification
     x_old = st["x"]
@@ -271,8 +335,8 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
             mark("z")
             if defer_obs and "sigmasq_done" not in checks:
                 wait("all")
-                S_y, msum = obs_stats()     # uses the OLD x (st["x"]), exactly as step 2 of the sweep does
-                if world > 1:
+                S_y, msum, reduced = obs_stats()     # uses the OLD x (st["x"]), exactly as step 2 of the sweep does
+                if world > 1 and not reduced:
                     S_y, msum = all_reduce_obs_stats(S_y, msum, group)
                 pr["sigmasq"] = G.sample_obs_variance(key, S_y, msum, nu_sigma=hyp["nu_sigma"],
                                                       sigmasq_0=hyp["sigmasq_0"])
@@ -285,6 +349,14 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
         checks["x"] = info["boundary_err"] if (strict == "defer" and info["chunk_len"] > 0) else None
         done("x", st["x"])
         mark("x")
+        st.pop(NEXT_PARAMS_KEY, None)
+        if next_key is not None and not defer_obs and strict == "defer":
+            # next sweep's steps 1 and 3 depend on the new z and x only: enqueue them now (not in a
+            # repair pass, which runs on the failing ranks alone and must not issue collectives)
+            nxt, _, _, nflags = _draw_dynamics_params(next_key, data, st, pr, hyp, group, world, None)
+            st[NEXT_PARAMS_KEY] = {"key": next_key, "world": world, "params": nxt, "flags": nflags,
+                                   "tag": tuple(_tensor_id(t) for t in (st["x"], st["z"], data["mask"], pr["betas"]))}
+            mark("ahead")
         st["h"] = G.resample_heading(key, Y=data["Y"], v=states["v"], x=st["x"], s=states["s"], Cd=pr["Cd"],
                                      sigmasq=pr["sigmasq"], Gamma=Gamma, session_offset=off)
         done("h", st["h"])
@@ -296,12 +368,17 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
                                                     sigmasq=pr["sigmasq"], nu_s=hyp["nu_s"], s_0=hyp["s_0"],
                                                     Gamma=Gamma, session_offset=off, mask=data["mask"],
                                                     return_stats=True)
-        st[OBS_STATS_KEY] = {"S_y": S_new, "msum": m_new, "tag": _obs_stats_tag(data, st, pr)}
+        reduced, S_loc, m_loc = False, S_new, m_new
+        if world > 1 and next_key is not None and not defer_obs and strict == "defer":
+            S_new, m_new = all_reduce_obs_stats(S_loc, m_loc, group)   # k + 1 doubles, off the next sweep's start
+            reduced = True
+        st[OBS_STATS_KEY] = {"S_y": S_new, "msum": m_new, "reduced": reduced, "S_local": S_loc, "m_local": m_loc,
+                             "tag": _obs_stats_tag(data, st, pr)}
         done("s", st["s"])
         mark("hvs")
 
     run_from("z", "defer")
-    _verify_and_repair(checks, flags_dev, run_from, world)
+    _verify_and_repair(checks, flags_dev, run_from, world, group, st)
     mark("verified")
     return st, pr
 
@@ -334,7 +411,7 @@ def arhmm_sweep(key, data, states, params, hyp, group=None, session_offset=None)
         st["z"] = z_new
 
     run_from("z", "defer")
-    _verify_and_repair(checks, flags_dev, run_from, world)
+    _verify_and_repair(checks, flags_dev, run_from, world, group, st)
     return st, pr
 
 
