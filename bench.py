@@ -311,8 +311,8 @@ def main():
     N, T = sh["sessions"], sh["frames"]
     k, dk, D, L, K = sh["k"], sh["dk"], sh["D"], sh["L"], sh["K"]
     off = rank * N          # contiguous shards of N sessions, in rank order
-    data, st, pr, Gamma = simulate(1000 + rank, N, T, k=k, dk=dk, D=D, L=L, K=K)
-    pr0 = simulate(999, 1, 8, k=k, dk=dk, D=D, L=L, K=K)[2]  # replicated params
+    pr0 = simulate(999, 1, 8, k=k, dk=dk, D=D, L=L, K=K)[2]  # the model all shards are drawn from; replicated params
+    data, st, pr, Gamma = simulate(1000 + rank, N, T, k=k, dk=dk, D=D, L=L, K=K, params=pr0)
     trans, ar, obs, loc = default_hypparams(D, L, K, full_model=slds)
     hyp = {}
     for h in (trans, ar, obs, loc):

@@ -51,15 +51,18 @@ def make_params(rng, D, L, K, k, dk):
     return dict(pi=pi, Ab=Ab, Q=Q, Cd=Cd, betas=betas, sigmasq=sigmasq)
 
 
-def simulate(seed, N, T, *, k=8, dk=2, D=10, L=3, K=50, ragged=False, dtype=np.float32):
-    """Draw (data, states, params, Gamma) of the named shape.
+def simulate(seed, N, T, *, k=8, dk=2, D=10, L=3, K=50, ragged=False, dtype=np.float32, params=None):
+    """Draw (data, states, params, Gamma) of the named shape.  `params`: model parameters to draw the
+    sessions from (default: drawn from `seed` too) — shards of one sharded job share them.
 
     data   : Y (N,T,k,dk), mask (N,T) (trailing padding only when `ragged`)
     states : x (N,T,D), z (N,T-L), v (N,T,dk), h (N,T), s (N,T,k)
     params : Ab, Q, pi, betas, Cd, sigmasq (float64)
     """
     rng = np.random.default_rng(seed)
-    p = make_params(rng, D, L, K, k, dk)
+    p = make_params(rng, D, L, K, k, dk)     # always drawn, so that the session draws below do not depend on `params`
+    if params is not None:
+        p = {a: np.asarray(b) for a, b in params.items()}
     Gamma = center_embedding(k)
     # state sequences (frames L..T-1), vectorised over sessions
     z = np.empty((N, T - L), dtype=np.int64)
