@@ -116,6 +116,52 @@ __device__ __forceinline__ float philox_uniform_at(unsigned long long e, uint2 k
   return u01(w);
 }
 
+// Four keypoints of one frame: Y (dk coordinates each) and, optionally, s.  Thread-per-frame kernels
+// walk their frame's keypoints in groups of four: with dk == 2 and k % 4 == 0 (every BASELINE config)
+// a group is two 16-byte loads of Y and one of s instead of twelve 4-byte ones — the scalar loads of a
+// warp hit 32 different sectors each, which made these kernels LSU-bound at a fifth of the HBM rate.
+struct Kp4 {
+  float y[12];   // [j*dk + dim]
+  float s[4];
+};
+__device__ __forceinline__ void load_kp4(const float* __restrict__ Yf, const float* __restrict__ sf, int kp0, int k,
+                                         int dk, bool vec, Kp4& o) {
+  if (vec) {   // dk == 2, k % 4 == 0, 16-byte aligned rows
+    const float4 a = __ldg(reinterpret_cast<const float4*>(Yf + kp0 * 2));
+    const float4 b = __ldg(reinterpret_cast<const float4*>(Yf + kp0 * 2) + 1);
+    o.y[0] = a.x; o.y[1] = a.y; o.y[2] = a.z; o.y[3] = a.w;
+    o.y[4] = b.x; o.y[5] = b.y; o.y[6] = b.z; o.y[7] = b.w;
+    if (sf) {
+      const float4 c = __ldg(reinterpret_cast<const float4*>(sf + kp0));
+      o.s[0] = c.x; o.s[1] = c.y; o.s[2] = c.z; o.s[3] = c.w;
+    }
+  } else {
+#pragma unroll
+    for (int e = 0; e < 12; e++) o.y[e] = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      o.s[j] = 1.0f;
+      if (kp0 + j < k) {
+        const float* yp = Yf + (kp0 + j) * dk;
+        if (dk == 2) {
+          o.y[2 * j] = yp[0];
+          o.y[2 * j + 1] = yp[1];
+        } else {
+          o.y[3 * j] = yp[0];
+          o.y[3 * j + 1] = yp[1];
+          o.y[3 * j + 2] = yp[2];
+        }
+        if (sf) o.s[j] = sf[kp0 + j];
+      }
+    }
+  }
+}
+// coordinates of keypoint j (compile-time) of the group, without dynamic register indexing
+#define KP4_Y(q, j, dk, dim) ((dk) == 2 ? ((dim) < 2 ? (q).y[2 * (j) + ((dim) < 2 ? (dim) : 0)] : 0.0f) : (q).y[3 * (j) + (dim)])
+__device__ __forceinline__ bool kp4_vec_ok(const float* Y, const float* s, int k, int dk) {
+  return dk == 2 && (k & 3) == 0 && ((uintptr_t)Y % 16 == 0) && (s == nullptr || (uintptr_t)s % 16 == 0);
+}
+
 // R(-h)(y - v) in the first two coordinates (reference util.py:140-166)
 __device__ __forceinline__ void rot_inv(double c, double s, double y0, double y1, double& o0,
                                         double& o1) {

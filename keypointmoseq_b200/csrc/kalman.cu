@@ -272,47 +272,73 @@ __global__ void __launch_bounds__(128)
   }
   __syncthreads();
   const int Tp = T - Lg + 1;
+  const long long total = (long long)N * Tp;
   const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= (long long)N * Tp) return;
-  const int n = (int)(g / Tp), tau = (int)(g % Tp);
-  const size_t f = (size_t)n * T + tau + Lg - 1;
-  double J[Y_::NJ], ev[DD];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  // per-warp staging of the 32 records of a warp: threads fill their own record (row stride odd:
+  // conflict-free), then the warp writes the 32 x OBS_SIZE doubles, which are contiguous in `obs`,
+  // as whole 256-byte lines (a thread writing its own 528-byte record touches 32 sectors per store)
+  constexpr int SST = Y_::OBS_SIZE | 1;
+  double* stage = sg + k + (size_t)wib * 32 * SST;
+  const bool act = g < total;
+  if (act) {
+    const int n = (int)(g / Tp), tau = (int)(g % Tp);
+    const size_t f = (size_t)n * T + tau + Lg - 1;
+    double J[Y_::NJ], ev[DD];
 #pragma unroll
-  for (int i = 0; i < Y_::NJ; i++) J[i] = 0.0;
+    for (int i = 0; i < Y_::NJ; i++) J[i] = 0.0;
 #pragma unroll
-  for (int i = 0; i < DD; i++) ev[i] = 0.0;
-  double ct = 0.0;
-  double sn, cs;
-  sincos((double)h[f], &sn, &cs);
-  const double v0 = (double)v[f * dk], v1 = (double)v[f * dk + 1];
-  const double v2 = (dk > 2) ? (double)v[f * dk + 2] : 0.0;
-  for (int kp = 0; kp < k; kp++) {
-    const double R = (double)s[f * k + kp] * sg[kp];
-    const double ri = 1.0 / R;
-    const float* Yf = Y + (f * k + kp) * dk;
-    double yt[3];
-    rot_inv(cs, sn, (double)Yf[0] - v0, (double)Yf[1] - v1, yt[0], yt[1]);
-    yt[2] = (dk > 2) ? (double)Yf[2] - v2 : 0.0;
-    double q = 0.0;
-    for (int dim = 0; dim < dk; dim++) {
-      const double* row = Cs + (size_t)(kp * dk + dim) * (DD + 1);
-      const double yy = yt[dim] - row[DD];
-      q = fma(yy, yy, q);
-      const double wgt = yy * ri;
+    for (int i = 0; i < DD; i++) ev[i] = 0.0;
+    double ct = 0.0;
+    double sn, cs;
+    sincos((double)h[f], &sn, &cs);
+    const double v0 = (double)v[f * dk], v1 = (double)v[f * dk + 1];
+    const double v2 = (dk > 2) ? (double)v[f * dk + 2] : 0.0;
+    const bool vec = kp4_vec_ok(Y, s, k, dk);
+    for (int kp0 = 0; kp0 < k; kp0 += 4) {
+      Kp4 q;
+      load_kp4(Y + f * k * dk, s + f * k, kp0, k, dk, vec, q);
 #pragma unroll
-      for (int a = 0; a < DD; a++) ev[a] = fma(row[a], wgt, ev[a]);
+      for (int j = 0; j < 4; j++) {
+        const int kp = kp0 + j;
+        if (kp >= k) continue;
+        const double R = (double)q.s[j] * sg[kp];
+        const double ri = 1.0 / R;
+        double yt[3];
+        rot_inv(cs, sn, (double)KP4_Y(q, j, dk, 0) - v0, (double)KP4_Y(q, j, dk, 1) - v1, yt[0], yt[1]);
+        yt[2] = (dk > 2) ? (double)KP4_Y(q, j, dk, 2) - v2 : 0.0;
+        double qq = 0.0;
+#pragma unroll
+        for (int dim = 0; dim < 3; dim++) {
+          if (dim < dk) {
+            const double* row = Cs + (size_t)(kp * dk + dim) * (DD + 1);
+            const double yy = yt[dim] - row[DD];
+            qq = fma(yy, yy, qq);
+            const double wgt = yy * ri;
+#pragma unroll
+            for (int a = 0; a < DD; a++) ev[a] = fma(row[a], wgt, ev[a]);
+          }
+        }
+        ct += -0.5 * (double)dk * (KPMS_LOG_2PI + log(R)) - 0.5 * qq * ri;
+        const double* cc = CC + (size_t)kp * Y_::NJ;
+#pragma unroll
+        for (int i = 0; i < Y_::NJ; i++) J[i] = fma(cc[i], ri, J[i]);
+      }
     }
-    ct += -0.5 * (double)dk * (KPMS_LOG_2PI + log(R)) - 0.5 * q * ri;
-    const double* cc = CC + (size_t)kp * Y_::NJ;
+    double* o = stage + (size_t)lane * SST;
 #pragma unroll
-    for (int i = 0; i < Y_::NJ; i++) J[i] = fma(cc[i], ri, J[i]);
+    for (int i = 0; i < Y_::NJ; i++) o[Y_::OBS_J + i] = J[i];
+#pragma unroll
+    for (int i = 0; i < DD; i++) o[Y_::OBS_E + i] = ev[i];
+    o[Y_::OBS_C] = ct;
+    if (Y_::OBS_SIZE > Y_::OBS_C + 1) o[Y_::OBS_C + 1] = 0.0;
   }
-  double* o = obs + (size_t)g * Y_::OBS_SIZE;
-#pragma unroll
-  for (int i = 0; i < Y_::NJ; i++) o[Y_::OBS_J + i] = J[i];
-#pragma unroll
-  for (int i = 0; i < DD; i++) o[Y_::OBS_E + i] = ev[i];
-  o[Y_::OBS_C] = ct;
+  __syncwarp();
+  const long long g0 = g - lane;                      // first record of this warp
+  const long long left = total - g0;
+  const int nrec = left >= 32 ? 32 : (left > 0 ? (int)left : 0);
+  double* dst = obs + (size_t)g0 * Y_::OBS_SIZE;
+  for (int i = lane; i < nrec * Y_::OBS_SIZE; i += 32) dst[i] = stage[(size_t)(i / Y_::OBS_SIZE) * SST + (i % Y_::OBS_SIZE)];
 }
 
 // number of unmasked transition steps per session (trailing padding assumed for chunking)
@@ -1133,7 +1159,7 @@ static int launch_latents(const float* Y, const float* mask, const float* v, con
   int rc = kpms_last_launch();
   if (rc) return rc;
   {
-    const size_t smem = ((size_t)k * dk * (DD + 1) + (size_t)k * YL::NJ + k) * sizeof(double);
+    const size_t smem = ((size_t)k * dk * (DD + 1) + (size_t)k * YL::NJ + k + 4 * 32 * (size_t)(YL::OBS_SIZE | 1)) * sizeof(double);
     auto kern = kalman_obs_kernel<NN, DD>;
     KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long tot = (long long)N * Tp;

@@ -59,6 +59,29 @@ __device__ __forceinline__ void ytild_kp(const float* __restrict__ Yf, const dou
   yt[2] = (dk > 2) ? (double)Yf[2] - vv[2] : 0.0;
 }
 
+__device__ __forceinline__ void ytild3(float y0, float y1, float y2, const double (&vv)[OBS_DKMAX], double c, double s,
+                                       int dk, double (&yt)[OBS_DKMAX]) {
+  rot_inv(c, s, (double)y0 - vv[0], (double)y1 - vv[1], yt[0], yt[1]);
+  yt[2] = (dk > 2) ? (double)y2 - vv[2] : 0.0;
+}
+
+// x row as float2 pairs when D is even (rows are then 8-byte aligned)
+__device__ __forceinline__ void load_x2(const float* __restrict__ x, size_t frame, int D, double (&xr)[OBS_XMAX]) {
+  if ((D & 1) == 0) {
+    const float2* p = reinterpret_cast<const float2*>(x + frame * D);
+#pragma unroll
+    for (int d = 0; d < OBS_XMAX / 2; d++) {
+      float2 v = make_float2(0.f, 0.f);
+      if (2 * d < D) v = __ldg(p + d);
+      xr[2 * d] = (double)v.x;
+      xr[2 * d + 1] = (double)v.y;
+    }
+    if (OBS_XMAX & 1) xr[OBS_XMAX - 1] = 0.0;
+  } else {
+    load_x(x, frame, D, xr);
+  }
+}
+
 // ======================================================================== a13
 #define OV_BLOCKS (148 * 4)
 #define OV_THREADS 256
@@ -84,29 +107,37 @@ __global__ void __launch_bounds__(OV_THREADS)
   double* accs = Cs + (size_t)k * dk * (D + 1);
   for (int i = 0; i <= k; i++) accs[i * OV_THREADS + threadIdx.x] = 0.0;
   const long long frames = (long long)dm.N * dm.T;
+  const bool vec = kp4_vec_ok(Y, s, k, dk);
   for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < frames;
        g += (long long)gridDim.x * blockDim.x) {
     const double m = (double)mask[g];
     if (m > 0.0) {
       double xr[OBS_XMAX];
-      load_x(x, (size_t)g, D, xr);
+      load_x2(x, (size_t)g, D, xr);
       double sn, cs;
       sincos((double)h[g], &sn, &cs);
       double vv[OBS_DKMAX];
 #pragma unroll
       for (int dim = 0; dim < OBS_DKMAX; dim++) vv[dim] = (dim < dk) ? (double)v[g * dk + dim] : 0.0;
-#pragma unroll 2
-      for (int kp = 0; kp < k; kp++) {
-        double yb[OBS_DKMAX], yt[OBS_DKMAX];
-        ybar_kp(Cs, kp, dk, D, xr, yb);
-        ytild_kp(Y + ((size_t)g * k + kp) * dk, vv, cs, sn, dk, yt);
-        double e = 0.0;
+      for (int kp0 = 0; kp0 < k; kp0 += 4) {
+        Kp4 q;
+        load_kp4(Y + (size_t)g * k * dk, s + (size_t)g * k, kp0, k, dk, vec, q);
 #pragma unroll
-        for (int dim = 0; dim < OBS_DKMAX; dim++) {
-          const double r = yt[dim] - yb[dim];
-          e = fma(r, r, e);
+        for (int j = 0; j < 4; j++) {
+          const int kp = kp0 + j;
+          if (kp < k) {
+            double yb[OBS_DKMAX], yt[OBS_DKMAX];
+            ybar_kp(Cs, kp, dk, D, xr, yb);
+            ytild3(KP4_Y(q, j, dk, 0), KP4_Y(q, j, dk, 1), KP4_Y(q, j, dk, 2), vv, cs, sn, dk, yt);
+            double e = 0.0;
+#pragma unroll
+            for (int dim = 0; dim < OBS_DKMAX; dim++) {
+              const double r = yt[dim] - yb[dim];
+              e = fma(r, r, e);
+            }
+            accs[kp * OV_THREADS + threadIdx.x] += m * e / (double)q.s[j];
+          }
         }
-        accs[kp * OV_THREADS + threadIdx.x] += m * e / (double)s[(size_t)g * k + kp];
       }
       accs[k * OV_THREADS + threadIdx.x] += m;
     }
@@ -541,32 +572,43 @@ __global__ void __launch_bounds__(OV_THREADS)
   const long long frames = (long long)dm.N * dm.T;
   const double base = s_0 * nu_s;
   const float shape = (float)((nu_s + 3.0) * 0.5);
+  const bool vec = kp4_vec_ok(Y, nullptr, k, dk) && ((uintptr_t)s_out % 16 == 0) && (g == nullptr || (uintptr_t)g % 16 == 0);
   for (long long f = (long long)blockIdx.x * blockDim.x + threadIdx.x; f < frames;
        f += (long long)gridDim.x * blockDim.x) {
     double xr[OBS_XMAX];
-    load_x(x, (size_t)f, D, xr);
+    load_x2(x, (size_t)f, D, xr);
     double sn, cs;
     sincos((double)h[f], &sn, &cs);
     double vv[OBS_DKMAX];
 #pragma unroll
     for (int dim = 0; dim < OBS_DKMAX; dim++) vv[dim] = (dim < dk) ? (double)v[f * dk + dim] : 0.0;
     const double m = partial ? (double)mask[f] : 0.0;
-#pragma unroll 2
-    for (int kp = 0; kp < k; kp++) {
-      double yb[OBS_DKMAX], yt[OBS_DKMAX];
-      ybar_kp(Cs, kp, dk, D, xr, yb);
-      ytild_kp(Y + ((size_t)f * k + kp) * dk, vv, cs, sn, dk, yt);
-      double e = 0.0;
+    for (int kp0 = 0; kp0 < k; kp0 += 4) {
+      Kp4 q;
+      load_kp4(Y + (size_t)f * k * dk, g ? g + (size_t)f * k : nullptr, kp0, k, dk, vec, q);   // q.s = injected gammas
+      float sv4[4];
 #pragma unroll
-      for (int dim = 0; dim < OBS_DKMAX; dim++) {
-        const double r = yt[dim] - yb[dim];
-        e = fma(r, r, e);
+      for (int j = 0; j < 4; j++) {
+        const int kp = kp0 + j;
+        sv4[j] = 0.0f;
+        if (kp < k) {
+          double yb[OBS_DKMAX], yt[OBS_DKMAX];
+          ybar_kp(Cs, kp, dk, D, xr, yb);
+          ytild3(KP4_Y(q, j, dk, 0), KP4_Y(q, j, dk, 1), KP4_Y(q, j, dk, 2), vv, cs, sn, dk, yt);
+          double e = 0.0;
+#pragma unroll
+          for (int dim = 0; dim < OBS_DKMAX; dim++) {
+            const double r = yt[dim] - yb[dim];
+            e = fma(r, r, e);
+          }
+          const size_t el = (size_t)f * k + kp;
+          const double gg = g ? (double)q.s[j] : (double)philox_gamma(elem_offset + el, shape, key, sid);
+          sv4[j] = (float)((e * isig[kp] + base) * 0.5 / gg);
+          if (!vec) s_out[el] = sv4[j];
+          if (partial && m > 0.0) accs[kp * OV_THREADS + threadIdx.x] += m * e / (double)sv4[j];
+        }
       }
-      const size_t el = (size_t)f * k + kp;
-      const double gg = g ? (double)g[el] : (double)philox_gamma(elem_offset + el, shape, key, sid);
-      const float sv = (float)((e * isig[kp] + base) * 0.5 / gg);
-      s_out[el] = sv;
-      if (partial && m > 0.0) accs[kp * OV_THREADS + threadIdx.x] += m * e / (double)sv;
+      if (vec) *reinterpret_cast<float4*>(s_out + (size_t)f * k + kp0) = make_float4(sv4[0], sv4[1], sv4[2], sv4[3]);
     }
     if (partial && m > 0.0) accs[k * OV_THREADS + threadIdx.x] += m;
   }
@@ -687,19 +729,27 @@ __global__ void __launch_bounds__(256)
   const long long f = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (f >= frames) return;
   double xr[OBS_XMAX];
-  load_x(x, (size_t)f, D, xr);
+  load_x2(x, (size_t)f, D, xr);
   const double v0 = (double)v[f * dk + 0], v1 = (double)v[f * dk + 1];
   double S00 = 0.0, S01 = 0.0, S10 = 0.0, S11 = 0.0;
-  for (int kp = 0; kp < k; kp++) {
-    double yb[OBS_DKMAX];
-    ybar_kp(Cs, kp, dk, D, xr, yb);
-    const float* Yf = Y + ((size_t)f * k + kp) * dk;
-    const double w = 1.0 / ((double)s[(size_t)f * k + kp] * isig[kp]);
-    const double y0 = ((double)Yf[0] - v0) * w, y1 = ((double)Yf[1] - v1) * w;
-    S00 = fma(yb[0], y0, S00);
-    S01 = fma(yb[0], y1, S01);
-    S10 = fma(yb[1], y0, S10);
-    S11 = fma(yb[1], y1, S11);
+  const bool vec = kp4_vec_ok(Y, s, k, dk);
+  for (int kp0 = 0; kp0 < k; kp0 += 4) {
+    Kp4 q;
+    load_kp4(Y + (size_t)f * k * dk, s + (size_t)f * k, kp0, k, dk, vec, q);
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int kp = kp0 + j;
+      if (kp < k) {
+        double yb[OBS_DKMAX];
+        ybar_kp(Cs, kp, dk, D, xr, yb);
+        const double w = 1.0 / ((double)q.s[j] * isig[kp]);
+        const double y0 = ((double)KP4_Y(q, j, dk, 0) - v0) * w, y1 = ((double)KP4_Y(q, j, dk, 1) - v1) * w;
+        S00 = fma(yb[0], y0, S00);
+        S01 = fma(yb[0], y1, S01);
+        S10 = fma(yb[1], y0, S10);
+        S11 = fma(yb[1], y1, S11);
+      }
+    }
   }
   const double kc = S00 + S11, ks = S01 - S10;
   // util.py:80-82 vector_to_angle
@@ -794,21 +844,29 @@ __global__ void __launch_bounds__(256)
   const long long f = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (f >= frames) return;
   double xr[OBS_XMAX];
-  load_x(x, (size_t)f, D, xr);
+  load_x2(x, (size_t)f, D, xr);
   double sn, cs;
   sincos((double)h[f], &sn, &cs);
   double wsum = 0.0, acc[OBS_DKMAX] = {0.0, 0.0, 0.0};
-  for (int kp = 0; kp < k; kp++) {
-    double yb[OBS_DKMAX];
-    ybar_kp(Cs, kp, dk, D, xr, yb);
-    const float* Yf = Y + ((size_t)f * k + kp) * dk;
-    const double w = 1.0 / ((double)s[(size_t)f * k + kp] * sig[kp]);
-    // R(h) Ybar  (util.py:85-109): [c -s; s c] on the first two coordinates
-    const double r0 = cs * yb[0] - sn * yb[1], r1 = sn * yb[0] + cs * yb[1];
-    acc[0] = fma((double)Yf[0] - r0, w, acc[0]);
-    acc[1] = fma((double)Yf[1] - r1, w, acc[1]);
-    if (dk > 2) acc[2] = fma((double)Yf[2] - yb[2], w, acc[2]);
-    wsum += w;
+  const bool vec = kp4_vec_ok(Y, s, k, dk);
+  for (int kp0 = 0; kp0 < k; kp0 += 4) {
+    Kp4 q;
+    load_kp4(Y + (size_t)f * k * dk, s + (size_t)f * k, kp0, k, dk, vec, q);
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int kp = kp0 + j;
+      if (kp < k) {
+        double yb[OBS_DKMAX];
+        ybar_kp(Cs, kp, dk, D, xr, yb);
+        const double w = 1.0 / ((double)q.s[j] * sig[kp]);
+        // R(h) Ybar  (util.py:85-109): [c -s; s c] on the first two coordinates
+        const double r0 = cs * yb[0] - sn * yb[1], r1 = sn * yb[0] + cs * yb[1];
+        acc[0] = fma((double)KP4_Y(q, j, dk, 0) - r0, w, acc[0]);
+        acc[1] = fma((double)KP4_Y(q, j, dk, 1) - r1, w, acc[1]);
+        if (dk > 2) acc[2] = fma((double)KP4_Y(q, j, dk, 2) - yb[2], w, acc[2]);
+        wsum += w;
+      }
+    }
   }
   // mu = acc * gammasq with gammasq = 1/wsum  ->  em = mu/gammasq, rg = wsum
   const double g2 = 1.0 / wsum;

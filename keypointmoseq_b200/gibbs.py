@@ -61,13 +61,13 @@ def auto_hmm_chunk_len(N, Tm, K, burn_in, device):
 
 
 def auto_chunk_len(N, T, L, burn_in, device):
-    """Kalman chunk length such that N * n_chunks is just under one wave of resident warps."""
+    """Kalman chunk length such that N * n_chunks is just under one wave of resident warps.  With few
+    sessions the wave cannot be filled with long chunks: the chain latency (chunk + warm-up steps) is
+    then what counts, and chunks shrink down to twice the warm-up."""
     Tt = T - L
     slots = torch.cuda.get_device_properties(device).multi_processor_count * KALMAN_WARPS_PER_SM
     nch = max(1, slots // max(N, 1))
-    cl = -(-Tt // nch)
-    if nch == 1 or cl < 4 * max(burn_in, 1):
-        cl = max(4 * max(burn_in, 1), 256)
+    cl = max(-(-Tt // nch), 2 * max(burn_in, 1), 256)
     return 0 if cl >= Tt else cl
 
 
