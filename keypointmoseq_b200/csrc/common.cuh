@@ -27,7 +27,7 @@ struct KpmsOptions {
   int hmm_flags;     // bit 0: forward pass only (timing)
   int location_impl; // 0 (default): exact associative scan over time; 1: chunks with a fixed warm-up (no verification)
   int kalman_warps;  // warps per CTA of the blocked Kalman filter: 8, 12 (default) or 16
-  int kalman_lockstep;  // 1: the warps of a CTA step together (helps the lane-per-column kernel, not the blocked one; default 0)
+  int kalman_lockstep;  // blocked filter, bit mask: 1 = the warps of a CTA step together (no gain measured), 2 = L1 prefetch of the per-state tables; default 0
 };
 extern KpmsOptions kpms_opts;
 

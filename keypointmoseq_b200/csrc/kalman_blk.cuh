@@ -85,6 +85,8 @@ __global__ void kalman_tables_blk_kernel(const double* __restrict__ tab, double*
     }
 }
 
+__device__ __forceinline__ void kb_prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
 template <int NN, int DD, int KB_WARPS>
 __global__ void __launch_bounds__(KB_WARPS * 32, 1)
     kalman_forward_blk_kernel(const float* __restrict__ mask, const int* __restrict__ z, KalWs ws, int N, int T,
@@ -185,7 +187,7 @@ __global__ void __launch_bounds__(KB_WARPS * 32, 1)
         }
   };
   for (int it = 0; it < maxit; it++) {
-    if (lockstep) __syncthreads();   // keeps the warps that share a scheduler on the same code (instruction cache)
+    if (lockstep & 1) __syncthreads();   // keeps the warps that share a scheduler on the same code (instruction cache)
     const int tau = tb + it;
     if (tau >= t1) continue;
     if (tau == t0 && cc > 0) record_carry(ws.bndf + ((size_t)(n * nch + cc) * 2 + 0) * Y::BND);
@@ -206,6 +208,10 @@ __global__ void __launch_bounds__(KB_WARPS * 32, 1)
     const double* tgz = ws.tabg + (size_t)zt * B::TABG;
     const double* tfz = ws.tabf + (size_t)zt * B::TABF;
     double* fwp = fw_n + (size_t)tau * Y::FW_SIZE;
+    if (lockstep & 2) {   // bit 1: pull the tables phase C and the carry update read (F fragments, Qinv, qb) into L1 now
+      if (lane * 16 < B::TABF) kb_prefetch_l1(tfz + lane * 16);
+      if (lane * 16 < Y::TAB_SIZE - Y::TAB_QI + 16) kb_prefetch_l1(tabz + Y::TAB_QI + min(lane * 16, Y::TAB_SIZE - Y::TAB_QI - 1));
+    }
     // ---- eta_c = eta_p + e (row NN of the carry), h = eta_c - f to shared memory, eta_c to the record
 #pragma unroll
     for (int j = 0; j <= B::IB; j++)
@@ -316,12 +322,32 @@ __global__ void __launch_bounds__(KB_WARPS * 32, 1)
       }
       __syncwarp();
     }
-    // ---- phase B: L_ij = -(sum_{j<k<=i} L_ik M_kj) Li_jj, diagonal by diagonal (blocks at the same distance
-    //      from the diagonal are independent).  M stays in the lower blocks until the end: an L block is
-    //      parked, untransposed, in the free upper block (j, i), which is also the scratch that turns the
-    //      accumulator S into an A operand; the finished blocks stay in registers and replace M at the end.
+    // ---- phase B: L_ij = -(sum_{j<k<=i} L_ik M_kj) Li_jj.  First every off-diagonal block of M is scaled
+    //      on the right in place, N_kj = M_kj Li_jj (independent products); then L_ij = -sum_k L_ik N_kj
+    //      has no layout change inside its chain, diagonal by diagonal (blocks at the same distance from
+    //      the diagonal are independent).  N stays in the lower blocks until the end: an L block is
+    //      parked, untransposed, in the free upper block (j, i), where the next diagonals read it as an
+    //      A operand; the finished blocks stay in registers and replace N at the end.
     {
       double Lr[B::NBLK][2];
+#pragma unroll
+      for (int k = 1; k < NBK; k++)
+#pragma unroll
+        for (int j = 0; j < k; j++) {
+          double* acc = Lr[B::blk(k, j)];
+          acc[0] = acc[1] = 0.0;
+#pragma unroll
+          for (int half = 0; half < 2; half++)
+            KB_DMMA(acc, buf[(8 * k + g) * SA + 8 * j + 4 * half + qd], buf[(8 * j + 4 * half + qd) * SA + 8 * j + g]);
+        }
+      __syncwarp();
+#pragma unroll
+      for (int k = 1; k < NBK; k++)
+#pragma unroll
+        for (int j = 0; j < k; j++)
+          *reinterpret_cast<double2*>(buf + (8 * k + g) * SA + 8 * j + 2 * qd) =
+              make_double2(Lr[B::blk(k, j)][0], Lr[B::blk(k, j)][1]);
+      __syncwarp();
 #pragma unroll
       for (int sd = 1; sd < NBK; sd++) {
 #pragma unroll
@@ -335,29 +361,15 @@ __global__ void __launch_bounds__(KB_WARPS * 32, 1)
             for (int half = 0; half < 2; half++) {
               // A operand L_ik: the diagonal block in place, an off-diagonal one from its parking block (k, i)
               const double av = buf[(8 * k + g) * SA + 8 * i + 4 * half + qd];
-              KB_DMMA(acc, av, buf[(8 * k + 4 * half + qd) * SA + 8 * j + g]);
+              KB_DMMA(acc, -av, buf[(8 * k + 4 * half + qd) * SA + 8 * j + g]);
             }
         }
-        __syncwarp();
+        if (sd + 1 < NBK) {
 #pragma unroll
-        for (int i = sd; i < NBK; i++)
-          *reinterpret_cast<double2*>(buf + (8 * (i - sd) + g) * SA + 8 * i + 2 * qd) =
-              make_double2(Lr[B::blk(i, i - sd)][0], Lr[B::blk(i, i - sd)][1]);
-        __syncwarp();
-#pragma unroll
-        for (int i = sd; i < NBK; i++) {
-          const int j = i - sd;
-          double* acc = Lr[B::blk(i, j)];
-          acc[0] = acc[1] = 0.0;
-#pragma unroll
-          for (int half = 0; half < 2; half++)
-            KB_DMMA(acc, -buf[(8 * j + g) * SA + 8 * i + 4 * half + qd], buf[(8 * j + 4 * half + qd) * SA + 8 * j + g]);
+          for (int i = sd; i < NBK; i++)
+            *reinterpret_cast<double2*>(buf + (8 * (i - sd) + g) * SA + 8 * i + 2 * qd) =
+                make_double2(Lr[B::blk(i, i - sd)][0], Lr[B::blk(i, i - sd)][1]);
         }
-        __syncwarp();
-#pragma unroll
-        for (int i = sd; i < NBK; i++)
-          *reinterpret_cast<double2*>(buf + (8 * (i - sd) + g) * SA + 8 * i + 2 * qd) =
-              make_double2(Lr[B::blk(i, i - sd)][0], Lr[B::blk(i, i - sd)][1]);
         __syncwarp();
       }
 #pragma unroll
@@ -377,6 +389,12 @@ __global__ void __launch_bounds__(KB_WARPS * 32, 1)
       __syncwarp();
     }
     // ---- phase C: T = L^T [unit columns | F | h], dense column blocks by DMMA
+    if ((lockstep & 2) && tau + 1 < Tt) {   // the G fragments of the next step's state
+      const double* tgn = ws.tabg + (size_t)z_next * B::TABG;
+#pragma unroll
+      for (int o = 0; o < B::TABG; o += 512)
+        if (o + lane * 16 < B::TABG) kb_prefetch_l1(tgn + o + lane * 16);
+    }
     {
       double Tacc[NBK][NDB][2];
 #pragma unroll
@@ -444,11 +462,12 @@ __global__ void __launch_bounds__(KB_WARPS * 32, 1)
 #pragma unroll
         for (int e = 0; e < 2; e++) {
           const int row = 8 * i + g, col = 8 * j + 2 * qd + e;
-          double qv = 0.0;
-          if (row < OFF) qv = (row == col) ? 100.0 : 0.0;
-          else if (8 * i + 7 >= OFF && 8 * j + 7 >= OFF && col >= OFF && col < NN) {
-            if (row < NN) qv = __ldg(tabz + Y::TAB_QI + (row - OFF) * DD + (col - OFF));
-            else if (row == NN) qv = __ldg(tabz + Y::TAB_QB + (col - OFF));
+          double qv = (row < OFF && row == col) ? 100.0 : 0.0;
+          if (8 * i + 7 >= OFF && 8 * j + 7 >= OFF) {   // blocks that meet Qinv_ / qb_: one unconditional load, then a select
+            const bool in = row >= OFF && row <= NN && col >= OFF && col < NN;
+            const int idx = (row < NN) ? Y::TAB_QI + (row - OFF) * DD + (col - OFF) : Y::TAB_QB + (col - OFF);
+            const double tv = __ldg(tabz + (in ? idx : Y::TAB_QI));
+            if (in) qv = tv;
           }
           const double zv = C[B::blk(i, j)][e];
           C[B::blk(i, j)][e] = (row == NN) ? qv + zv : qv - zv;

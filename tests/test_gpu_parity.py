@@ -215,9 +215,10 @@ def test_resample_latents_chunked_matches_exact(G):
     # too short a warm-up must be visible in the reported mismatch
     _, i2 = G.resample_latents(0, chunk_len=128, burn_in=2, strict=False, **kw)
     assert N_(i2['boundary_err']).max() > 1e-6
-    # strict mode notices the mismatch and silently redoes the call exactly
+    # strict mode notices the mismatch and redoes the call (longer warm-up, then unchunked) until the
+    # mismatch is at rounding level
     x3, i3 = G.resample_latents(0, chunk_len=128, burn_in=2, strict=True, **kw)
-    assert float((x0 - x3).abs().max()) == 0.0 and N_(i3['boundary_err']).max() == 0.0
+    assert float((x0 - x3).abs().max()) < 1e-6 and N_(i3['boundary_err']).max() < 1e-12
 
 
 # ------------------------------------------------------------------ a8-a11

@@ -24,13 +24,13 @@ w = torch.randn((N, T - L, D * L), device="cuda")
 wl = torch.randn((N, D * L), device="cuda")
 kw = dict(**d, **s, **p, Gamma=tt(Gamma), draws={'w': w, 'w_last': wl}, return_info=True)
 out = {}
-variants = [(2, 12, 1), (2, 12, 0), (2, 8, 1), (2, 8, 0), (2, 16, 1), (2, 16, 0), (1, 12, 1)]
+variants = [(2, 12, 0), (2, 12, 2), (2, 8, 0), (2, 8, 2), (2, 16, 0), (2, 16, 2), (2, 12, 1), (1, 12, 1)]
 for impl, warps, lock in variants:
     _lib.set_option("kalman_impl", impl)
     _lib.set_option("kalman_warps", warps)
     _lib.set_option("kalman_lockstep", lock)
     G.KALMAN_WARPS_PER_SM = warps
-    print("---- impl", impl, "warps/CTA", warps, "lockstep", lock)
+    print("---- impl", impl, "warps/CTA", warps, "lockstep/prefetch mask", lock)
     G.resample_latents(0, **kw)
     torch.cuda.synchronize()
     with profile(activities=[ProfilerActivity.CUDA]) as prof:

@@ -139,28 +139,29 @@ def step(NN, DD, Lam_p, eta_p, Gz, J, e_obs, FD, f, Qi, qb):
         Lis.append(Li)
     for b in range(NBK):
         buf.m[8 * b:8 * b + 8, 8 * b:8 * b + 8] = Lis[b]
-    # ---- phase B: L_ij = -(sum_{k=j+1..i} L_ik M_kj) Li_jj, diagonal by diagonal (blocks at the same
-    #      distance from the diagonal are independent).  M stays in the lower blocks until the end: an L
-    #      block is parked (untransposed) in the free upper block (j, i), which also serves as the
-    #      scratch that turns the accumulator S into an A operand.
+    # ---- phase B: L_ij = -(sum_{k=j+1..i} L_ik M_kj) Li_jj.  First every off-diagonal block of M is
+    #      scaled on the right, N_kj = M_kj Li_jj (six independent products, in place); then
+    #      L_ij = -sum_k L_ik N_kj needs one product per term and no layout change inside the chain.
+    #      Blocks at the same distance from the diagonal are independent.  N stays in the lower blocks
+    #      until the end: an L block is parked, untransposed, in the free upper block (j, i).
+    Nn = {}
+    for k in range(1, NBK):
+        for j in range(k):
+            n_ = np.zeros((32, 2))
+            for half in range(2):
+                dmma(n_, buf.rfrag(8 * k, 8 * j + 4 * half), buf.kfrag(8 * j + 4 * half, 8 * j))
+            Nn[(k, j)] = n_
+    for (k, j), n_ in Nn.items():
+        buf.cstore(8 * k, 8 * j, n_)
     Lreg = {}
     for sd in range(1, NBK):
-        S = {}
-        for i in range(sd, NBK):
-            j = i - sd
-            s_ = np.zeros((32, 2))
-            for k in range(j + 1, i + 1):
-                for half in range(2):
-                    a = buf.rfrag(8 * i, 8 * i + 4 * half) if k == i else buf.rfrag(8 * k, 8 * i + 4 * half)
-                    dmma(s_, a, buf.kfrag(8 * k + 4 * half, 8 * j))
-            S[i] = s_
-        for i in range(sd, NBK):
-            buf.cstore(8 * (i - sd), 8 * i, S[i])
         for i in range(sd, NBK):
             j = i - sd
             l = np.zeros((32, 2))
-            for half in range(2):
-                dmma(l, -buf.rfrag(8 * j, 8 * i + 4 * half), buf.kfrag(8 * j + 4 * half, 8 * j))
+            for k in range(j + 1, i + 1):
+                for half in range(2):
+                    a = buf.rfrag(8 * i, 8 * i + 4 * half) if k == i else buf.rfrag(8 * k, 8 * i + 4 * half)
+                    dmma(l, -a, buf.kfrag(8 * k + 4 * half, 8 * j))
             Lreg[(i, j)] = l
         for i in range(sd, NBK):
             buf.cstore(8 * (i - sd), 8 * i, Lreg[(i, i - sd)])
