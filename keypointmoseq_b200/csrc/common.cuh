@@ -28,6 +28,7 @@ struct KpmsOptions {
   int location_impl; // 0 (default): exact associative scan over time; 1: chunks with a fixed warm-up (no verification)
   int kalman_warps;  // warps per CTA of the blocked Kalman filter: 8, 12 (default) or 16
   int kalman_lockstep;  // blocked filter, bit mask: 1 = the warps of a CTA step together (no gain measured), 2 = L1 prefetch of the per-state tables; default 0
+  int kalman_obs_mma;   // 1 (default): observation records by FP64 tensor cores when dk == 2 and k % 4 == 0; 0: thread-per-frame kernel
 };
 extern KpmsOptions kpms_opts;
 

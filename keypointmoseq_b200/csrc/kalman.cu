@@ -242,6 +242,14 @@ __global__ void kalman_tables_kernel(const double* __restrict__ Ab, const double
   }
 }
 
+// 1/x for x > 0, normal: hardware seed and one third-order correction (relative error ~2^-66 before rounding)
+__device__ __forceinline__ double rcp_pos_obs(double x) {
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  const double e = fma(-x, y, 1.0);
+  return fma(y, fma(e, e, e), y);
+}
+
 // ------------------------------------------------------------------ observation information
 // One thread per LDS step tau (frame tau+L-1):  J = C_D^T R^-1 C_D (packed lower),
 // e = C_D^T R^-1 (ytild - d),  c = -1/2 sum_p [log(2 pi R_p) + (ytild_p - d_p)^2 / R_p],
@@ -339,6 +347,148 @@ __global__ void __launch_bounds__(128)
   const int nrec = left >= 32 ? 32 : (left > 0 ? (int)left : 0);
   double* dst = obs + (size_t)g0 * Y_::OBS_SIZE;
   for (int i = lane; i < nrec * Y_::OBS_SIZE; i += 32) dst[i] = stage[(size_t)(i / Y_::OBS_SIZE) * SST + (i % Y_::OBS_SIZE)];
+}
+
+// The same records by FP64 tensor cores, for dk == 2 and k % 4 == 0 (every BASELINE config).  Both
+// J = sum_kp (1/R_kp) C_kp^T C_kp and e = sum_(kp,dim) C_(kp,dim) (ytild - d)/R are products of a
+// per-frame weight row with a table that depends on the keypoint only, so eight frames make the M
+// dimension of mma.m8n8k4: lane (g, qd) prepares frame g's keypoints qd, qd+4, ... (its A operands),
+// the tables come from shared memory as B operands, and the accumulator rows are the records.
+// A warp takes 32 frames at a time: sincos(h) once per lane, then four batches of eight frames.
+// The thread-per-frame kernel above needs ~2400 instructions per frame at 242 registers; this one
+// ~1000 per 32 frames, so the pass is bound by its record writes instead of instruction issue.
+#define KO_DMMA(c, a, b)                                                                           \
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" \
+               : "+d"((c)[0]), "+d"((c)[1])                                                        \
+               : "d"(a), "d"(b))
+template <int NN, int DD>
+__global__ void __launch_bounds__(256)
+    kalman_obs_mma_kernel(const float* __restrict__ Y, const float* __restrict__ v,
+                          const float* __restrict__ h, const float* __restrict__ s,
+                          const double* __restrict__ Cdfull, const double* __restrict__ sigmasq,
+                          int N, int T, int k, int Lg, double* __restrict__ obs) {
+  using Y_ = KL<NN, DD>;
+  constexpr int NJ = Y_::NJ, NJB = (NJ + 7) / 8, NEB = (DD + 7) / 8;
+  constexpr int NJP = 8 * NJB + 4;   // row strides (doubles) of the two tables: the four k rows of a B
+  constexpr int CSP = 8 * NEB + 2;   // fragment land on distinct bank pairs (60 -> 12, 2*18 -> 4 mod 16)
+  constexpr unsigned FULL = 0xffffffffu;
+  extern __shared__ __align__(16) double sm[];
+  double* CC = sm;                          // k x NJP : C_kp^T C_kp packed lower, zero padded
+  double* Cs = CC + (size_t)k * NJP;        // (2k) x CSP : rows of C_D, zero padded
+  double* dd = Cs + (size_t)2 * k * CSP;    // 2k : d
+  double* sg = dd + 2 * k;                  // k : sigmasq
+  for (int i = threadIdx.x; i < 2 * k * CSP; i += blockDim.x) {
+    const int r = i / CSP, c = i % CSP;
+    Cs[i] = c < DD ? Cdfull[(size_t)r * (DD + 1) + c] : 0.0;
+  }
+  for (int i = threadIdx.x; i < 2 * k; i += blockDim.x) dd[i] = Cdfull[(size_t)i * (DD + 1) + DD];
+  for (int i = threadIdx.x; i < k; i += blockDim.x) sg[i] = sigmasq[i];
+  __syncthreads();
+  for (int i = threadIdx.x; i < k * NJP; i += blockDim.x) {
+    const int kp = i / NJP, ab = i % NJP;
+    double sacc = 0.0;
+    if (ab < NJ) {
+      int a = 0;
+      while ((a + 1) * (a + 2) / 2 <= ab) a++;
+      const int b = ab - a * (a + 1) / 2;
+      sacc = Cs[(2 * kp) * CSP + a] * Cs[(2 * kp) * CSP + b] + Cs[(2 * kp + 1) * CSP + a] * Cs[(2 * kp + 1) * CSP + b];
+    }
+    CC[i] = sacc;
+  }
+  __syncthreads();
+  const int Tp = T - Lg + 1;
+  const long long total = (long long)N * Tp;
+  const int lane = threadIdx.x & 31, g = lane >> 2, qd = lane & 3;
+  const long long nwarp = (long long)gridDim.x * (blockDim.x >> 5);
+  const int KS = k >> 2;
+  for (long long grp = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); grp * 32 < total; grp += nwarp) {
+    const long long g0 = grp * 32;
+    // lane i: frame g0 + i
+    double cs_i = 1.0, sn_i = 0.0;
+    float v0_i = 0.0f, v1_i = 0.0f;
+    long long f_i = 0;
+    if (g0 + lane < total) {
+      const int n = (int)((g0 + lane) / Tp), tau = (int)((g0 + lane) % Tp);
+      f_i = (long long)n * T + tau + Lg - 1;
+      sincos((double)h[f_i], &sn_i, &cs_i);
+      const float2 vv = __ldg(reinterpret_cast<const float2*>(v) + f_i);
+      v0_i = vv.x;
+      v1_i = vv.y;
+    }
+#pragma unroll 1
+    for (int b = 0; b < 4; b++) {
+      const int src = 8 * b + g;
+      const double cs = __shfl_sync(FULL, cs_i, src), sn = __shfl_sync(FULL, sn_i, src);
+      const double v0 = (double)__shfl_sync(FULL, v0_i, src), v1 = (double)__shfl_sync(FULL, v1_i, src);
+      const long long f = __shfl_sync(FULL, f_i, src);
+      const bool act = g0 + src < total;
+      const float2* Yf = reinterpret_cast<const float2*>(Y) + (size_t)f * k;
+      const float* sf = s + (size_t)f * k;
+      double Ja[NJB][2], Ea[NEB][2];
+#pragma unroll
+      for (int i = 0; i < NJB; i++) Ja[i][0] = Ja[i][1] = 0.0;
+#pragma unroll
+      for (int i = 0; i < NEB; i++) Ea[i][0] = Ea[i][1] = 0.0;
+      double qq = 0.0, lr = 0.0, pr = 1.0;
+      for (int ks = 0; ks < KS; ks++) {
+        const int kp = 4 * ks + qd;
+        double ri = 0.0, w0 = 0.0, w1 = 0.0;
+        if (act) {
+          const float2 yv = __ldg(Yf + kp);
+          const double R = (double)__ldg(sf + kp) * sg[kp];
+          ri = rcp_pos_obs(R);
+          pr *= R;
+          double y0, y1;
+          rot_inv(cs, sn, (double)yv.x - v0, (double)yv.y - v1, y0, y1);
+          y0 -= dd[2 * kp];
+          y1 -= dd[2 * kp + 1];
+          w0 = y0 * ri;
+          w1 = y1 * ri;
+          qq = fma(y0, w0, qq);
+          qq = fma(y1, w1, qq);
+        }
+        if ((ks & 3) == 3) {   // fold the running product of R into a log before it can leave the double range
+          lr += log(pr);
+          pr = 1.0;
+        }
+        const double* ccr = CC + (size_t)kp * NJP + g;
+#pragma unroll
+        for (int nb = 0; nb < NJB; nb++) KO_DMMA(Ja[nb], ri, ccr[8 * nb]);
+        const double* c0 = Cs + (size_t)(2 * kp) * CSP + g;
+#pragma unroll
+        for (int nb = 0; nb < NEB; nb++) {
+          KO_DMMA(Ea[nb], w0, c0[8 * nb]);
+          KO_DMMA(Ea[nb], w1, c0[CSP + 8 * nb]);
+        }
+      }
+      if (KS & 3) lr += log(pr);
+      // c = -1/2 sum_p [log(2 pi R_p) + (ytild_p - d_p)^2 / R_p], two coordinates per keypoint
+      double ct = -lr - 0.5 * qq;
+      ct += __shfl_xor_sync(FULL, ct, 1);
+      ct += __shfl_xor_sync(FULL, ct, 2);
+      ct -= (double)k * KPMS_LOG_2PI;
+      if (act) {
+        double* o = obs + (size_t)(g0 + src) * Y_::OBS_SIZE;
+#pragma unroll
+        for (int nb = 0; nb < NJB; nb++) {
+          const int i0 = 8 * nb + 2 * qd;
+          if (i0 + 1 < NJ) *reinterpret_cast<double2*>(o + Y_::OBS_J + i0) = make_double2(Ja[nb][0], Ja[nb][1]);
+          else if (i0 < NJ) o[Y_::OBS_J + i0] = Ja[nb][0];
+        }
+#pragma unroll
+        for (int nb = 0; nb < NEB; nb++)
+#pragma unroll
+          for (int e = 0; e < 2; e++) {
+            const int a = 8 * nb + 2 * qd + e;
+            if (a < DD) o[Y_::OBS_E + a] = Ea[nb][e];
+          }
+        if (qd == 0) {
+          o[Y_::OBS_C] = ct;
+          if (Y_::OBS_SIZE > Y_::OBS_C + 1) o[Y_::OBS_C + 1] = 0.0;
+        }
+      }
+    }
+  }
 }
 
 // number of unmasked transition steps per session (trailing padding assumed for chunking)
@@ -986,10 +1136,11 @@ __global__ void __launch_bounds__(32)
   constexpr int NCP = (FW * 8 + 16 * 32 - 1) / (16 * 32);   // 16-byte pieces per lane and record
   extern __shared__ __align__(16) double sm[];
   double* rec = sm;            // 2 x FW: packed records, double-buffered
-  double* hs = rec + 2 * FW;   // NN
-  double* ys = hs + NN;        // NN
-  double* xs = ys + NN;        // NN
-  double* FDs = xs + NN;       // NN*DD
+  constexpr int NNP = (NN + 1) / 2 * 2;   // the vectors are read as broadcast double2: keep them 16-byte aligned
+  double* hs = rec + 2 * FW;   // NNP
+  double* ys = hs + NNP;       // NNP
+  double* xs = ys + NNP;       // NNP
+  double* FDs = xs + NNP;      // NN*DD
   double* bs = FDs + NN * DD;  // DD
   const int lane = threadIdx.x;
   const int Tp = T - Lg + 1, Tt = Tp - 1;
@@ -1029,20 +1180,28 @@ __global__ void __launch_bounds__(32)
   __syncwarp();
   int cur_z = -1;
   float wpre = (ts - 1 >= t0 && lane < NN) ? w_n[(size_t)(ts - 1) * NN + lane] : 0.0f;
+  // mask and state of a step are loaded one step ahead too: a global load at the top of a step would sit
+  // on the serial chain of this one-warp recursion
+  float mpre = (ts - 1 >= t0) ? mk[ts - 1] : 0.0f;
+  int zpre = (ts - 1 >= t0) ? zn[ts - 1] : 0;
   const int rowbase = lane * (lane + 1) / 2;
   int buf = 0;
   for (int tau = ts - 1; tau >= t0; tau--, buf ^= 1) {
     if (tau == t1 - 1 && c < nch - 1 && lane < NN)
       ws.bndx[((size_t)(n * nch + c) * 2 + 0) * NN + lane] = xs[lane];
-    const bool live = mk[tau] > 0.0f;
+    const bool live = mpre > 0.0f;
+    const int zt = zpre;
     fetch(tau - 1, buf ^ 1);          // next step's record, one step ahead
     const float wcur = wpre;
-    if (tau - 1 >= t0 && lane < NN) wpre = w_n[(size_t)(tau - 1) * NN + lane];
+    if (tau - 1 >= t0) {
+      if (lane < NN) wpre = w_n[(size_t)(tau - 1) * NN + lane];
+      mpre = mk[tau - 1];
+      zpre = zn[tau - 1];
+    }
     asm volatile("cp.async.wait_group 1;\n" ::);   // this step's record has landed
     __syncwarp();
     if (live) {
       const double* Pk = rec + buf * FW;
-      const int zt = zn[tau];
       if (zt != cur_z) {
         const double* tb_ = ws.tab + (size_t)zt * Y::TAB_SIZE;
         for (int e = lane; e < NN * DD; e += 32) FDs[e] = tb_[Y::TAB_FD + e];
@@ -1051,31 +1210,37 @@ __global__ void __launch_bounds__(32)
       }
       __syncwarp();
       if (lane < NN) {
-        double hh = Pk[NTRI + lane] + ((lane >= DD) ? 100.0 * xs[lane - DD] : 0.0);
+        double hh = Pk[NTRI + lane] + ((lane >= DD) ? 100.0 * xs[lane - DD] : 0.0), h2 = 0.0;
 #pragma unroll
-        for (int a = 0; a < DD; a++) hh = fma(FDs[lane * DD + a], xs[OFF + a] - bs[a], hh);
-        hs[lane] = hh;
+        for (int a = 0; a + 1 < DD; a += 2) {
+          hh = fma(FDs[lane * DD + a], xs[OFF + a] - bs[a], hh);
+          h2 = fma(FDs[lane * DD + a + 1], xs[OFF + a + 1] - bs[a + 1], h2);
+        }
+        if (DD & 1) hh = fma(FDs[lane * DD + DD - 1], xs[OFF + DD - 1] - bs[DD - 1], hh);
+        hs[lane] = hh + h2;
       }
       __syncwarp();
-      if (lane < NN) {
-        double t0a = 0.0, t1a = 0.0;
+      if (lane < NN) {   // four partial sums: the dependent-FMA chain is the latency of this step
+        double ta[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
         for (int q = 0; q < NN; q += 2) {
-          if (q >= lane) t0a = fma(Pk[q * (q + 1) / 2 + lane], hs[q], t0a);
-          if (q + 1 < NN && q + 1 >= lane) t1a = fma(Pk[(q + 1) * (q + 2) / 2 + lane], hs[q + 1], t1a);
+          const double2 h2 = *reinterpret_cast<const double2*>(hs + q);   // one broadcast load for two rows
+          if (q >= lane) ta[q & 3] = fma(Pk[q * (q + 1) / 2 + lane], h2.x, ta[q & 3]);
+          if (q + 1 < NN && q + 1 >= lane) ta[(q + 1) & 3] = fma(Pk[(q + 1) * (q + 2) / 2 + lane], h2.y, ta[(q + 1) & 3]);
         }
-        ys[lane] = (t0a + t1a) + (double)wcur;
+        ys[lane] = ((ta[0] + ta[1]) + (ta[2] + ta[3])) + (double)wcur;
       }
       __syncwarp();
       double xn = 0.0;
       if (lane < NN) {
-        double a0 = 0.0, a1 = 0.0;
+        double xa[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
         for (int q = 0; q < NN; q += 2) {
-          if (q <= lane) a0 = fma(Pk[rowbase + q], ys[q], a0);
-          if (q + 1 < NN && q + 1 <= lane) a1 = fma(Pk[rowbase + q + 1], ys[q + 1], a1);
+          const double2 y2 = *reinterpret_cast<const double2*>(ys + q);
+          if (q <= lane) xa[q & 3] = fma(Pk[rowbase + q], y2.x, xa[q & 3]);
+          if (q + 1 < NN && q + 1 <= lane) xa[(q + 1) & 3] = fma(Pk[rowbase + q + 1], y2.y, xa[(q + 1) & 3]);
         }
-        xn = a0 + a1;
+        xn = (xa[0] + xa[1]) + (xa[2] + xa[3]);
       }
       __syncwarp();
       if (lane < NN) xs[lane] = xn;
@@ -1159,12 +1324,24 @@ static int launch_latents(const float* Y, const float* mask, const float* v, con
   int rc = kpms_last_launch();
   if (rc) return rc;
   {
-    const size_t smem = ((size_t)k * dk * (DD + 1) + (size_t)k * YL::NJ + k + 4 * 32 * (size_t)(YL::OBS_SIZE | 1)) * sizeof(double);
-    auto kern = kalman_obs_kernel<NN, DD>;
-    KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long tot = (long long)N * Tp;
-    kern<<<(unsigned)((tot + 127) / 128), 128, smem, st>>>(Y, v, h, s, Cdfull, sigmasq, N, T, k, dk,
-                                                          Lg, ws.obs);
+    if (dk == 2 && k % 4 == 0 && k <= 64 && kpms_opts.kalman_obs_mma && kpms_aligned(Y, 8) && kpms_aligned(v, 8)) {
+      // tensor-core records: a warp per 32 frames, a few waves of CTAs striding over the frames
+      constexpr int NJP = 8 * ((YL::NJ + 7) / 8) + 4, CSP = 8 * ((DD + 7) / 8) + 2;
+      const size_t smem = ((size_t)k * NJP + (size_t)2 * k * CSP + 3 * (size_t)k) * sizeof(double);
+      auto kern = kalman_obs_mma_kernel<NN, DD>;
+      KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      const long long groups = (tot + 31) / 32;
+      const long long want = (groups + 7) / 8;
+      const unsigned grid = (unsigned)(want < 148LL * 8 ? (want > 0 ? want : 1) : 148LL * 8);
+      kern<<<grid, 256, smem, st>>>(Y, v, h, s, Cdfull, sigmasq, N, T, k, Lg, ws.obs);
+    } else {
+      const size_t smem = ((size_t)k * dk * (DD + 1) + (size_t)k * YL::NJ + k + 4 * 32 * (size_t)(YL::OBS_SIZE | 1)) * sizeof(double);
+      auto kern = kalman_obs_kernel<NN, DD>;
+      KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      kern<<<(unsigned)((tot + 127) / 128), 128, smem, st>>>(Y, v, h, s, Cdfull, sigmasq, N, T, k, dk,
+                                                            Lg, ws.obs);
+    }
     rc = kpms_last_launch();
     if (rc) return rc;
   }
@@ -1215,7 +1392,7 @@ static int launch_latents(const float* Y, const float* mask, const float* v, con
     if (rc) return rc;
   }
   {
-    const size_t smem = (size_t)(2 * YL::FW_SIZE + 3 * NN + NN * DD + DD) * sizeof(double);
+    const size_t smem = (size_t)(2 * YL::FW_SIZE + 3 * ((NN + 1) / 2 * 2) + NN * DD + DD) * sizeof(double);
     auto kern = kalman_backward_kernel<NN, DD>;
     KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<N * nch, 32, smem, st>>>(mask, z, w, ws, N, T, Lg, chunk_len, burn_in, x);

@@ -586,7 +586,8 @@ def test_hmm_backward_chunks_are_repaired(G, options):
 
 def test_alternative_kernel_paths_agree(G, options):
     """The kernels kept behind library options stay correct: kalman_impl=0 (CTA-per-chunk
-    shared-memory Kalman filter) and hmm_tc=0 (CUDA-core chunked HMM filter)."""
+    shared-memory Kalman filter), kalman_impl=1 (lane-per-column warp filter), kalman_obs_mma=0
+    (thread-per-frame observation records) and hmm_tc=0 (CUDA-core chunked HMM filter)."""
     import torch
     d, s, p, Gm = H.problem(seed=61, N=3, T=700, k=8, dk=2, D=10, L=3, K=8, ragged=True)
     rng = np.random.default_rng(3)
@@ -594,11 +595,14 @@ def test_alternative_kernel_paths_agree(G, options):
     kw = dict(Y=T_(d['Y']), mask=T_(d['mask']), v=T_(s['v']), h=T_(s['h']), z=T_(s['z']), s=T_(s['s']),
               Cd=T_(p['Cd']), sigmasq=T_(p['sigmasq']), Ab=T_(p['Ab']), Q=T_(p['Q']), Gamma=T_(Gm),
               draws={'w': T_(w), 'w_last': T_(wl)}, chunk_len=128, burn_in=160, strict=False)
-    x0 = G.resample_latents(0, **kw)
-    options("kalman_impl", 0)
-    x1 = G.resample_latents(0, **kw)
-    options("kalman_impl", 1)
-    assert float((x0 - x1).abs().max()) < 1e-5 * max(1.0, float(x0.abs().max()))
+    x0, i0 = G.resample_latents(0, return_info=True, **kw)
+    for name, value in (("kalman_impl", 0), ("kalman_impl", 1), ("kalman_obs_mma", 0)):
+        options(name, value)
+        x1, i1 = G.resample_latents(0, return_info=True, **kw)
+        options(name, 2 if name == "kalman_impl" else 1)
+        assert float((x0 - x1).abs().max()) < 1e-5 * max(1.0, float(x0.abs().max())), name
+        l0, l1 = N_(i0['loglik']), N_(i1['loglik'])
+        assert np.all(np.abs(l0 - l1) <= 1e-9 * np.abs(l0)), (name, l0, l1)
     ll, mask, pi, u = _hmm_case(31, N=4, T=2400, K=40, ragged=True)
     hk = dict(ll=T_(ll), mask=T_(mask), pi=T_(pi), u=T_(u), chunk_len=300, burn_in=256, strict=False, return_info=True)
     z0, l0, _ = G.sample_hmm_stateseqs(**hk)

@@ -37,7 +37,7 @@ for impl, warps, lock in variants:
         x, info = G.resample_latents(0, **kw)
         torch.cuda.synchronize()
     out[impl] = x
-    top = sorted(prof.key_averages(), key=lambda e: -e.device_time_total)[:1]
+    top = sorted(prof.key_averages(), key=lambda e: -e.device_time_total)[:4 if (impl, warps, lock) == variants[0] else 1]
     print("== kalman_impl", impl, "boundary_err", info['boundary_err'].cpu().tolist(), "loglik[0]", float(info['loglik'][0]))
     for e in top:
         print("   %10.3f ms  x%d  %s" % (e.device_time_total / 1e3, e.count, e.key[:100]))
