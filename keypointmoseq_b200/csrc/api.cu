@@ -14,7 +14,7 @@ static int env_int(const char* name, int dflt) {
 }
 KpmsOptions kpms_opts = {env_int("KPMS_KALMAN_IMPL", 2), env_int("KPMS_HMM_TC", 1), env_int("KPMS_HMM_BWD_BURN", -1),
                          env_int("KPMS_LL_TILED", 0), env_int("KPMS_HMM_FLAGS", 0), env_int("KPMS_LOCATION_IMPL", 0), env_int("KPMS_KALMAN_WARPS", 12),
-                         env_int("KPMS_KALMAN_LOCKSTEP", 0), env_int("KPMS_KALMAN_OBS_MMA", 1)};
+                         env_int("KPMS_KALMAN_LOCKSTEP", 0), env_int("KPMS_EMISSION_PIPE", 1), env_int("KPMS_KALMAN_OBS_MMA", 1)};
 
 static int* option_slot(const char* name) {
   if (!name) return nullptr;
@@ -27,6 +27,7 @@ static int* option_slot(const char* name) {
   if (!strcmp(name, "kalman_warps")) return &kpms_opts.kalman_warps;
   if (!strcmp(name, "kalman_lockstep")) return &kpms_opts.kalman_lockstep;
   if (!strcmp(name, "kalman_obs_mma")) return &kpms_opts.kalman_obs_mma;
+  if (!strcmp(name, "emission_pipe")) return &kpms_opts.emission_pipe;
   return nullptr;
 }
 extern "C" int kpms_set_option(const char* name, int value) {

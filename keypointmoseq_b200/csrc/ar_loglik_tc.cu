@@ -254,6 +254,225 @@ __global__ void __launch_bounds__(TC_THREADS)
   }
 }
 
+// The same contraction, software-pipelined inside one CTA per SM: two A stages in shared memory and two
+// accumulators in TMEM (columns 0.. and 256..), so that while the tensor core works on block i+1 the
+// threads read block i's accumulator (epilogue) and build the A tile of block i+2.  x of block i+2 is
+// loaded into registers before the epilogue, so its latency is covered as well.  Per block the CTA costs
+// max(MMA, epilogue + A build) instead of their sum.
+template <int DD, int LL>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+    ar_loglik_tc_pipe_kernel(const float* __restrict__ x, const unsigned char* __restrict__ tiles,
+                             const float* __restrict__ cst, int N, int T, int K, int nstripes,
+                             int tile_cl, int tile_nch, float* __restrict__ ll) {
+  using C = TC<DD, LL>;
+  constexpr int NCH = (C::KC + 1) / 2;   // 16-byte chunks of a row built by one thread
+  extern __shared__ __align__(1024) unsigned char smem[];
+  unsigned char* sA = smem;                                   // [stage][hi | lo]
+  unsigned char* sB_hi = sA + 4 * C::A_BYTES;
+  unsigned char* sB_lo = sB_hi + C::B_BYTES;
+  float* s_cst = reinterpret_cast<float*>(sB_lo + C::B_BYTES);
+  uint64_t* mbar = reinterpret_cast<uint64_t*>(s_cst + TC_STATES);   // two barriers, one per stage
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mbar + 2);
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int row = tid & (TC_M - 1), half = tid >> 7;
+  const int tile = blockIdx.x, stripe = blockIdx.y;
+  const int k0 = tile * TC_STATES;
+  const int Tm = T - LL;
+  const long long frames = (long long)N * Tm;
+  const long long units = (long long)N * tile_nch;
+  const long long nblk = (tile_cl > 0) ? ((units + 127) / 128) * tile_cl : (frames + TC_M - 1) / TC_M;
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(tiles + (size_t)tile * 2 * C::B_BYTES);
+    uint4* dst = reinterpret_cast<uint4*>(sB_hi);
+    for (int i = tid; i < 2 * C::B_BYTES / 16; i += TC_THREADS) dst[i] = src[i];
+    if (tid < TC_STATES) s_cst[tid] = (k0 + tid < K) ? cst[k0 + tid] : 0.0f;
+  }
+  const uint32_t mbar_sa = (uint32_t)__cvta_generic_to_shared(mbar);
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(mbar_sa));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(mbar_sa + 8));
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::);
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;\n" ::"r"(
+        (uint32_t)__cvta_generic_to_shared(tmem_slot)));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::);
+  }
+  TC_FENCE_PROXY();
+  TC_FENCE_BEFORE();
+  __syncthreads();
+  TC_FENCE_AFTER();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t a_sa = (uint32_t)__cvta_generic_to_shared(sA);
+  const uint32_t b_hi_sa = (uint32_t)__cvta_generic_to_shared(sB_hi);
+  const uint32_t b_lo_sa = (uint32_t)__cvta_generic_to_shared(sB_lo);
+
+  // where row `row` of block blk lives: frame index g (row-major ll), liveness, start of its lag window
+  auto locate = [&](long long blk, long long& g, const float*& xp) -> bool {
+    g = blk * TC_M + row;
+    xp = x;
+    if (tile_cl > 0) {
+      const long long b = blk / tile_cl;
+      const int r = (int)(blk - b * tile_cl);
+      const long long uu = b * 128 + row;
+      if (uu >= units) return false;
+      const int n = (int)(uu / tile_nch), cc = (int)(uu % tile_nch);
+      const int tp = cc * tile_cl + r;
+      if (tp >= Tm) return false;
+      xp = x + ((size_t)n * T + tp) * DD;
+      return true;
+    }
+    if (g >= frames) return false;
+    const int n = (int)(g / Tm), tp = (int)(g % Tm);
+    xp = x + ((size_t)n * T + tp) * DD;
+    return true;
+  };
+  // this thread's chunks of its row: global -> registers
+  auto load_row = [&](long long blk, float4 (&pre)[NCH]) {
+    long long g;
+    const float* xp;
+    const bool live = locate(blk, g, xp);
+#pragma unroll
+    for (int j = 0; j < NCH; j++) {
+      const int kc = 2 * j + half;
+      float4 v = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+      if (live && kc < C::KC) {
+        if ((DD & 1) == 0 && kc * 4 + 3 < DD * LL + DD) {
+          const float2 a = __ldg(reinterpret_cast<const float2*>(xp + kc * 4));
+          const float2 b = __ldg(reinterpret_cast<const float2*>(xp + kc * 4 + 2));
+          v = make_float4(a.x, a.y, b.x, b.y);
+        } else {
+          float q4[4];
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            const int p = kc * 4 + q;
+            q4[q] = (p < DD * LL + DD) ? xp[p] : (p == C::P - 1 ? 1.0f : 0.0f);
+          }
+          v = make_float4(q4[0], q4[1], q4[2], q4[3]);
+        }
+      }
+      pre[j] = v;
+    }
+  };
+  // registers -> hi / lo TF32 parts in stage `st`
+  auto store_row = [&](int st, const float4 (&pre)[NCH]) {
+    unsigned char* ah = sA + (size_t)st * 2 * C::A_BYTES + (size_t)(row / 8) * C::SBO + (row % 8) * 16;
+#pragma unroll
+    for (int j = 0; j < NCH; j++) {
+      const int kc = 2 * j + half;
+      if (kc >= C::KC) continue;
+      const float v4[4] = {pre[j].x, pre[j].y, pre[j].z, pre[j].w};
+      uint32_t hi[4], lo[4];
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        hi[q] = tf32_rna(v4[q]);
+        lo[q] = tf32_rna(v4[q] - __uint_as_float(hi[q]));
+      }
+      *reinterpret_cast<uint4*>(ah + kc * C::LBO) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+      *reinterpret_cast<uint4*>(ah + C::A_BYTES + kc * C::LBO) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    }
+  };
+  // 3xTF32 (hi*hi + hi*lo + lo*hi) of stage `st` into accumulator `st`; one thread issues
+  auto issue = [&](int st) {
+    TC_FENCE_AFTER();
+    const uint32_t ah = a_sa + (uint32_t)(st * 2 * C::A_BYTES), al = ah + (uint32_t)C::A_BYTES;
+    uint32_t acc = 0;
+#pragma unroll
+    for (int ks = 0; ks < C::KD / 8; ks++) {
+      const uint32_t koff = ks * 2 * C::LBO;
+      const uint64_t dah = umma_desc(ah + koff, C::LBO, C::SBO), dal = umma_desc(al + koff, C::LBO, C::SBO);
+      const uint64_t dbh = umma_desc(b_hi_sa + koff, C::LBO, C::SBO), dbl = umma_desc(b_lo_sa + koff, C::LBO, C::SBO);
+#pragma unroll
+      for (int term = 0; term < 3; term++) {
+        umma_tf32(tmem_base + (uint32_t)(st * 256), (term == 2) ? dal : dah, (term == 1) ? dbl : dbh, C::IDESC, acc);
+        acc = 1;
+      }
+    }
+    umma_commit(mbar_sa + 8 * st);
+  };
+
+  const long long nmine = (nblk > stripe) ? (nblk - stripe + nstripes - 1) / nstripes : 0;
+  float4 pre[NCH];
+  if (nmine > 0) {
+    load_row(stripe, pre);
+    store_row(0, pre);
+  }
+  if (nmine > 1) {
+    load_row(stripe + nstripes, pre);
+    store_row(1, pre);
+  }
+  TC_FENCE_PROXY();
+  TC_FENCE_BEFORE();
+  __syncthreads();
+  if (nmine > 0 && tid == 0) issue(0);
+  uint32_t parity[2] = {0u, 0u};
+  for (long long i = 0; i < nmine; i++) {
+    const int st = (int)(i & 1);
+    const long long blk = stripe + i * nstripes;
+    if (i + 1 < nmine && tid == 0) issue(st ^ 1);          // block i+1: its A stage was completed before the last barrier
+    if (i + 2 < nmine) load_row(blk + 2 * nstripes, pre);  // x of block i+2 on its way while we wait and read TMEM
+    mbar_wait(mbar_sa + 8 * st, st ? parity[1] : parity[0]);
+    if (st) parity[1] ^= 1u; else parity[0] ^= 1u;
+    TC_FENCE_AFTER();
+    {
+      constexpr int HS = TC_STATES / 2, HC = HS * DD, W = (HC % 16 == 0) ? 16 : 8;
+      long long g;
+      const float* xp;
+      const bool live = locate(blk, g, xp);
+      float q[HS];
+#pragma unroll
+      for (int sidx = 0; sidx < HS; sidx++) q[sidx] = 0.0f;
+      const uint32_t taddr = tmem_base + (uint32_t)(st * 256) + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(half * HC);
+      uint32_t r[HC];   // all of this thread's columns in flight at once, one wait
+#pragma unroll
+      for (int c0 = 0; c0 < HC; c0 += W) {
+        if (W == 16) tmem_ld16_nowait(taddr + (uint32_t)c0, r + c0);
+        else tmem_ld8_nowait(taddr + (uint32_t)c0, r + c0);
+      }
+      tmem_ld_wait();
+#pragma unroll
+      for (int e = 0; e < HC; e++) asm volatile("" : "+r"(r[e]));   // no use of r may be scheduled above the wait
+#pragma unroll
+      for (int e = 0; e < HC; e++) {
+        const float v = __uint_as_float(r[e]);
+        q[e / DD] = fmaf(v, v, q[e / DD]);
+      }
+      const int ks = k0 + half * HS;
+      const float* cs = s_cst + half * HS;
+      if (live && tile_cl > 0) {
+        float4* out4 = reinterpret_cast<float4*>(ll) + ((size_t)blk * (K >> 2) + (ks >> 2)) * 128 + row;
+#pragma unroll
+        for (int s4 = 0; s4 < HS; s4 += 4)
+          if (ks + s4 < K)
+            out4[(size_t)(s4 >> 2) * 128] =
+                make_float4(cs[s4] - 0.5f * q[s4], cs[s4 + 1] - 0.5f * q[s4 + 1],
+                            cs[s4 + 2] - 0.5f * q[s4 + 2], cs[s4 + 3] - 0.5f * q[s4 + 3]);
+      } else if (live) {
+        float* out = ll + g * K + ks;
+        if ((K & 3) == 0 && ks + HS <= K) {
+#pragma unroll
+          for (int s4 = 0; s4 < HS; s4 += 4)
+            *reinterpret_cast<float4*>(out + s4) =
+                make_float4(cs[s4] - 0.5f * q[s4], cs[s4 + 1] - 0.5f * q[s4 + 1],
+                            cs[s4 + 2] - 0.5f * q[s4 + 2], cs[s4 + 3] - 0.5f * q[s4 + 3]);
+        } else {
+#pragma unroll
+          for (int sidx = 0; sidx < HS; sidx++)
+            if (ks + sidx < K) out[sidx] = cs[sidx] - 0.5f * q[sidx];
+        }
+      }
+    }
+    // stage st is free (its MMAs completed): A tile of block i+2
+    if (i + 2 < nmine) store_row(st, pre);
+    TC_FENCE_PROXY();
+    TC_FENCE_BEFORE();
+    __syncthreads();
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;\n" ::"r"(tmem_base));
+  }
+}
+
 size_t kpms_ar_tc_tile_bytes(int K, int D, int L) {
   const int P = D * L + D + 1, KD = (P + 7) / 8 * 8, SBO = (KD / 4) * 128;
   const int ntiles = (K + TC_STATES - 1) / TC_STATES;
@@ -268,6 +487,23 @@ static int launch_tc(const float* x, const float* Wf, const float* cst, int N, i
   ar_tc_pack_kernel<DD, LL><<<ntiles, 256, 0, st>>>(Wf, K, tiles);
   int rc = kpms_last_launch();
   if (rc) return rc;
+  const long long nblk0 = (tile_cl > 0) ? (((long long)N * tile_nch + 127) / 128) * tile_cl
+                                        : ((long long)N * (T - LL) + TC_M - 1) / TC_M;
+  if (kpms_opts.emission_pipe && ntiles <= 148) {
+    // pipelined kernel: one CTA per SM (it owns all 512 TMEM columns; the shared-memory request is kept
+    // above half of an SM's so that two CTAs can never meet on one SM and wait for each other's columns)
+    size_t smp = 1024 + 4 * C::A_BYTES + 2 * C::B_BYTES + TC_STATES * sizeof(float) + 32;
+    if (smp < 120 * 1024) smp = 120 * 1024;
+    if (smp <= 227 * 1024) {
+      auto kp = ar_loglik_tc_pipe_kernel<DD, LL>;
+      KPMS_CUDA(cudaFuncSetAttribute(kp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smp));
+      long long stp = 148 / ntiles;
+      if (stp > nblk0) stp = nblk0;
+      if (stp < 1) stp = 1;
+      kp<<<dim3(ntiles, (unsigned)stp), TC_THREADS, smp, st>>>(x, tiles, cst, N, T, K, (int)stp, tile_cl, tile_nch, ll);
+      return kpms_last_launch();
+    }
+  }
   const size_t smem = 1024 + 2 * C::A_BYTES + 2 * C::B_BYTES + TC_STATES * sizeof(float) + 16;
   auto kern = ar_loglik_tc_kernel<DD, LL>;
   KPMS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -28,6 +28,7 @@ struct KpmsOptions {
   int location_impl; // 0 (default): exact associative scan over time; 1: chunks with a fixed warm-up (no verification)
   int kalman_warps;  // warps per CTA of the blocked Kalman filter: 8, 12 (default) or 16
   int kalman_lockstep;  // blocked filter, bit mask: 1 = the warps of a CTA step together (no gain measured), 2 = L1 prefetch of the per-state tables; default 0
+  int emission_pipe;    // 1 (default): software-pipelined emission kernel (two A stages, two TMEM accumulators); 0: one block at a time, two CTAs per SM
   int kalman_obs_mma;   // 1 (default): observation records by FP64 tensor cores when dk == 2 and k % 4 == 0; 0: thread-per-frame kernel
 };
 extern KpmsOptions kpms_opts;
@@ -61,6 +62,15 @@ __device__ __forceinline__ long long warp_sum_ll(long long v) {
   return v;
 }
 
+// 1/x for x > 0, normal: hardware seed (2^-22) and one third-order correction; relative error ~2^-66
+// before the final rounding, without the special-case handling of the IEEE division sequence.
+__device__ __forceinline__ double rcp_pos_d(double x) {
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  const double e = fma(-x, y, 1.0);
+  return fma(y, fma(e, e, e), y);
+}
+
 // ---------------------------------------------------------------- Philox4x32-10
 __device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
   const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
@@ -88,26 +98,45 @@ __device__ __forceinline__ float2 box_muller(uint32_t a, uint32_t b) {
   return make_float2(r * c, r * s);
 }
 
-// Gamma(shape, 1), shape >= 1 (Marsaglia & Tsang 2000) for GLOBAL element index e: rejection
-// rounds advance the third counter word, so the value depends on (seed, stream id, e) only.
-__device__ __forceinline__ float philox_gamma(unsigned long long e, float shape, uint2 key, uint32_t sid) {
-  const float d = shape - 1.0f / 3.0f;
-  const float c = rsqrtf(9.0f * d);
+// Gamma(shape, 1), shape >= 1 (Marsaglia & Tsang 2000) for GLOBAL element index e; the value depends
+// on (seed, stream id, e) only.  Elements 2m and 2m+1 share the Philox block of their first round
+// (counter (m, 1, sid): its two Box-Muller normals and two uniforms serve one element each), which
+// halves the cost for kernels that draw for consecutive elements; later rounds (about one element
+// in twenty needs one) are keyed by the element itself, third counter word 2 + round.
+__device__ __forceinline__ bool gamma_mt_try(float xx, float u, float d, float c, float& res) {
+  float v = 1.0f + c * xx;
+  if (v <= 0.0f) return false;
+  v = v * v * v;
+  if (logf(u) < 0.5f * xx * xx + d - d * v + d * logf(v)) {
+    res = d * v;
+    return true;
+  }
+  return false;
+}
+static __device__ __noinline__ float philox_gamma_retry(unsigned long long e, float d, float c, uint2 key, uint32_t sid) {
   float res = d;
   for (uint32_t round = 0; round < 64u; round++) {
-    uint4 r = philox4x32_10(make_uint4((uint32_t)e, (uint32_t)(e >> 32), 2u + round, sid), key);
-    float2 nn = box_muller(r.x, r.y);
-    float xx = nn.x;
-    float v = 1.0f + c * xx;
-    if (v <= 0.0f) continue;
-    v = v * v * v;
-    float u = u01_open0(r.z);
-    if (logf(u) < 0.5f * xx * xx + d - d * v + d * logf(v)) {
-      res = d * v;
-      break;
-    }
+    const uint4 r = philox4x32_10(make_uint4((uint32_t)e, (uint32_t)(e >> 32), 2u + round, sid), key);
+    const float2 nn = box_muller(r.x, r.y);
+    if (gamma_mt_try(nn.x, u01_open0(r.z), d, c, res)) break;
   }
   return res;
+}
+// the variates of elements e0 and e0 + 1, e0 even
+__device__ __forceinline__ void philox_gamma_pair(unsigned long long e0, float shape, uint2 key, uint32_t sid, float& g0,
+                                                  float& g1) {
+  const float d = shape - 1.0f / 3.0f;
+  const float c = rsqrtf(9.0f * d);
+  const unsigned long long m = e0 >> 1;
+  const uint4 r = philox4x32_10(make_uint4((uint32_t)m, (uint32_t)(m >> 32), 1u, sid), key);
+  const float2 nn = box_muller(r.x, r.y);
+  if (!gamma_mt_try(nn.x, u01_open0(r.z), d, c, g0)) g0 = philox_gamma_retry(e0, d, c, key, sid);
+  if (!gamma_mt_try(nn.y, u01_open0(r.w), d, c, g1)) g1 = philox_gamma_retry(e0 + 1, d, c, key, sid);
+}
+__device__ __forceinline__ float philox_gamma(unsigned long long e, float shape, uint2 key, uint32_t sid) {
+  float g0, g1;
+  philox_gamma_pair(e & ~1ull, shape, key, sid, g0, g1);
+  return (e & 1ull) ? g1 : g0;
 }
 // uniform [0,1) number `e` of the stream a kpms_fill_uniform(seed, sid) call would have produced
 __device__ __forceinline__ float philox_uniform_at(unsigned long long e, uint2 key, uint32_t sid) {

@@ -242,14 +242,6 @@ __global__ void kalman_tables_kernel(const double* __restrict__ Ab, const double
   }
 }
 
-// 1/x for x > 0, normal: hardware seed and one third-order correction (relative error ~2^-66 before rounding)
-__device__ __forceinline__ double rcp_pos_obs(double x) {
-  double y;
-  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
-  const double e = fma(-x, y, 1.0);
-  return fma(y, fma(e, e, e), y);
-}
-
 // ------------------------------------------------------------------ observation information
 // One thread per LDS step tau (frame tau+L-1):  J = C_D^T R^-1 C_D (packed lower),
 // e = C_D^T R^-1 (ytild - d),  c = -1/2 sum_p [log(2 pi R_p) + (ytild_p - d_p)^2 / R_p],
@@ -436,7 +428,7 @@ __global__ void __launch_bounds__(256)
         if (act) {
           const float2 yv = __ldg(Yf + kp);
           const double R = (double)__ldg(sf + kp) * sg[kp];
-          ri = rcp_pos_obs(R);
+          ri = rcp_pos_d(R);
           pr *= R;
           double y0, y1;
           rot_inv(cs, sn, (double)yv.x - v0, (double)yv.y - v1, y0, y1);

@@ -135,7 +135,7 @@ __global__ void __launch_bounds__(OV_THREADS)
               const double r = yt[dim] - yb[dim];
               e = fma(r, r, e);
             }
-            accs[kp * OV_THREADS + threadIdx.x] += m * e / (double)q.s[j];
+            accs[kp * OV_THREADS + threadIdx.x] += m * e * rcp_pos_d((double)q.s[j]);   // same arithmetic as scales_stats_kernel
           }
         }
       }
@@ -587,6 +587,17 @@ __global__ void __launch_bounds__(OV_THREADS)
       Kp4 q;
       load_kp4(Y + (size_t)f * k * dk, g ? g + (size_t)f * k : nullptr, kp0, k, dk, vec, q);   // q.s = injected gammas
       float sv4[4];
+      if (!g) {   // in-kernel variates: one Philox block per pair of elements (pairs never straddle a frame when k is even)
+        const unsigned long long el0 = elem_offset + (unsigned long long)f * k + kp0;
+        if ((el0 & 1ull) == 0 && kp0 + 3 < k) {
+          philox_gamma_pair(el0, shape, key, sid, q.s[0], q.s[1]);
+          philox_gamma_pair(el0 + 2, shape, key, sid, q.s[2], q.s[3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; j++)
+            if (kp0 + j < k) q.s[j] = philox_gamma(el0 + j, shape, key, sid);
+        }
+      }
 #pragma unroll
       for (int j = 0; j < 4; j++) {
         const int kp = kp0 + j;
@@ -602,10 +613,10 @@ __global__ void __launch_bounds__(OV_THREADS)
             e = fma(r, r, e);
           }
           const size_t el = (size_t)f * k + kp;
-          const double gg = g ? (double)q.s[j] : (double)philox_gamma(elem_offset + el, shape, key, sid);
-          sv4[j] = (float)((e * isig[kp] + base) * 0.5 / gg);
+          // gamma variates and the new scale are positive and normal: reciprocals by seed + one refinement
+          sv4[j] = (float)((e * isig[kp] + base) * 0.5 * rcp_pos_d((double)q.s[j]));
           if (!vec) s_out[el] = sv4[j];
-          if (partial && m > 0.0) accs[kp * OV_THREADS + threadIdx.x] += m * e / (double)sv4[j];
+          if (partial && m > 0.0) accs[kp * OV_THREADS + threadIdx.x] += m * e * rcp_pos_d((double)sv4[j]);
         }
       }
       if (vec) *reinterpret_cast<float4*>(s_out + (size_t)f * k + kp0) = make_float4(sv4[0], sv4[1], sv4[2], sv4[3]);

@@ -121,7 +121,29 @@ def ar_log_likelihood(*, x, Ab, Q, impl=0, **kwargs):
 # parameters (slowly early in a fit, when the states are hardly distinguishable).  A failed boundary
 # check doubles the warm-up for this and the following calls; a run of comfortable passes halves it
 # again.  `boost` multiplies the configured burn_in.
-_HMM_ADAPT = {"boost": 1, "streak": 0}
+_HMM_ADAPT = {"boost": 1, "streak": 0, "need": 8, "probing": False}
+
+
+def _hmm_adapt_update(failed, comfortable):
+    """One verdict on a chunked HMM pass -> the warm-up multiplier of the next passes.
+    A failure doubles it.  After `need` consecutive comfortable passes (mismatch < 3 % of the tolerance)
+    it is halved again, on probation: if the shorter warm-up then fails, `need` is quadrupled (cap 4096),
+    so a model that needs the longer warm-up is re-probed ever more rarely instead of paying one
+    repeated pass every `need` sweeps."""
+    A = _HMM_ADAPT
+    if failed:
+        if A["probing"]:
+            A["need"] = min(A["need"] * 4, 4096)
+        A["boost"], A["streak"], A["probing"] = min(A["boost"] * 2, HMM_MAX_BOOST), 0, False
+    elif comfortable:
+        A["streak"] += 1
+        if A["probing"] and A["streak"] >= 8:
+            A["probing"] = False
+        if A["streak"] >= A["need"] and A["boost"] > 1:
+            A["boost"] //= 2
+            A["streak"], A["probing"] = 0, True
+    else:
+        A["streak"] = 0
 HMM_MAX_BOOST = 16
 
 
@@ -135,10 +157,7 @@ def note_hmm_check(b, adaptive=True):
     tol = STATESEQ_CHUNKING["tol"]
     if b <= tol:
         if adaptive:
-            _HMM_ADAPT["streak"] = _HMM_ADAPT["streak"] + 1 if b <= 0.03 * tol else 0
-            if _HMM_ADAPT["streak"] >= 8 and _HMM_ADAPT["boost"] > 1:
-                _HMM_ADAPT["boost"] //= 2
-                _HMM_ADAPT["streak"] = 0
+            _hmm_adapt_update(False, b <= 0.03 * tol)
         return True
     FALLBACKS["stateseqs"] += 1
     FALLBACKS.setdefault("stateseqs_berr", []).append(b)
@@ -172,7 +191,8 @@ def _run_hmm_adaptive(run, berr, chunk_len, burn_in, strict, adaptive):
             run(0, 0)
             return
         if adaptive:
-            _HMM_ADAPT["boost"], _HMM_ADAPT["streak"] = boost, 0
+            _hmm_adapt_update(True, False)
+            boost = max(boost, _HMM_ADAPT["boost"])
 
 
 def _hmm_chunking(N, Tm, K, chunk_len, burn_in, strict, dev):

@@ -132,18 +132,9 @@ def _local_verdict(dev):
 
 def _apply_verdicts(failed, comfortable, reported):
     """Identical on every rank (the inputs are all-reduced sums)."""
-    A = G._HMM_ADAPT
     if reported <= 0:
         return
-    if failed > 0:
-        A["boost"], A["streak"] = min(A["boost"] * 2, G.HMM_MAX_BOOST), 0
-    elif comfortable >= reported:
-        A["streak"] += 1
-        if A["streak"] >= 8 and A["boost"] > 1:
-            A["boost"] //= 2
-            A["streak"] = 0
-    else:
-        A["streak"] = 0
+    G._hmm_adapt_update(failed > 0, comfortable >= reported)
 
 
 def _verify_and_repair(checks, flags_dev, run_from, world, group=None, st=None):

@@ -587,7 +587,7 @@ def test_hmm_backward_chunks_are_repaired(G, options):
 def test_alternative_kernel_paths_agree(G, options):
     """The kernels kept behind library options stay correct: kalman_impl=0 (CTA-per-chunk
     shared-memory Kalman filter), kalman_impl=1 (lane-per-column warp filter), kalman_obs_mma=0
-    (thread-per-frame observation records) and hmm_tc=0 (CUDA-core chunked HMM filter)."""
+    (thread-per-frame observation records), emission_pipe=0 and hmm_tc=0 (CUDA-core chunked HMM filter)."""
     import torch
     d, s, p, Gm = H.problem(seed=61, N=3, T=700, k=8, dk=2, D=10, L=3, K=8, ragged=True)
     rng = np.random.default_rng(3)
@@ -603,6 +603,16 @@ def test_alternative_kernel_paths_agree(G, options):
         assert float((x0 - x1).abs().max()) < 1e-5 * max(1.0, float(x0.abs().max())), name
         l0, l1 = N_(i0['loglik']), N_(i1['loglik'])
         assert np.all(np.abs(l0 - l1) <= 1e-9 * np.abs(l0)), (name, l0, l1)
+    # emission: the software-pipelined kernel (several blocks per CTA) against the one-block-at-a-time kernel
+    d2, s2, p2, _ = H.problem(seed=62, N=2, T=9000, k=4, dk=2, D=10, L=3, K=100, ragged=False)
+    e1 = G.ar_log_likelihood(x=T_(s2['x']), Ab=T_(p2['Ab']), Q=T_(p2['Q']))
+    options("emission_pipe", 0)
+    e0 = G.ar_log_likelihood(x=T_(s2['x']), Ab=T_(p2['Ab']), Q=T_(p2['Q']))
+    options("emission_pipe", 1)
+    assert torch.equal(e0, e1)
+    want = O.ar_log_likelihood(s2['x'], p2['Ab'], p2['Q'])
+    err = np.abs(N_(e1).astype(np.float64) - want) / np.maximum(1.0, np.abs(want))
+    assert err.max() < 5e-5, err.max()   # 1.8 M float32 entries: the tail of the rounding distribution
     ll, mask, pi, u = _hmm_case(31, N=4, T=2400, K=40, ragged=True)
     hk = dict(ll=T_(ll), mask=T_(mask), pi=T_(pi), u=T_(u), chunk_len=300, burn_in=256, strict=False, return_info=True)
     z0, l0, _ = G.sample_hmm_stateseqs(**hk)

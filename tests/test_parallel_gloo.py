@@ -106,7 +106,7 @@ def test_shared_hmm_warmup_moves_identically_from_summed_verdicts():
     from keypointmoseq_b200 import gibbs as G, parallel
     saved = dict(G._HMM_ADAPT)
     try:
-        G._HMM_ADAPT.update(boost=1, streak=0)
+        G._HMM_ADAPT.update(boost=1, streak=0, need=8, probing=False)
         parallel._apply_verdicts(1.0, 6.0, 8.0)          # one of eight ranks failed its check
         assert G._HMM_ADAPT["boost"] == 2 and G._HMM_ADAPT["streak"] == 0
         for _ in range(7):
@@ -116,9 +116,19 @@ def test_shared_hmm_warmup_moves_identically_from_summed_verdicts():
         assert G._HMM_ADAPT["streak"] == 0
         for _ in range(8):
             parallel._apply_verdicts(0.0, 8.0, 8.0)
-        assert G._HMM_ADAPT["boost"] == 1
+        assert G._HMM_ADAPT["boost"] == 1 and G._HMM_ADAPT["probing"]
         parallel._apply_verdicts(0.0, 0.0, 0.0)          # nothing reported (sequential passes): no change
-        assert G._HMM_ADAPT == {"boost": 1, "streak": 0}
+        assert G._HMM_ADAPT == {"boost": 1, "streak": 0, "need": 8, "probing": True}
+        parallel._apply_verdicts(1.0, 0.0, 8.0)          # the shorter warm-up fails: probe less often from now on
+        assert G._HMM_ADAPT == {"boost": 2, "streak": 0, "need": 32, "probing": False}
+        for _ in range(31):
+            parallel._apply_verdicts(0.0, 8.0, 8.0)
+        assert G._HMM_ADAPT["boost"] == 2
+        parallel._apply_verdicts(0.0, 8.0, 8.0)
+        assert G._HMM_ADAPT["boost"] == 1 and G._HMM_ADAPT["probing"]
+        for _ in range(8):                               # the probe survives: probation over, `need` kept
+            parallel._apply_verdicts(0.0, 8.0, 8.0)
+        assert not G._HMM_ADAPT["probing"] and G._HMM_ADAPT["need"] == 32
         for _ in range(10):
             parallel._apply_verdicts(3.0, 0.0, 8.0)
         assert G._HMM_ADAPT["boost"] == G.HMM_MAX_BOOST

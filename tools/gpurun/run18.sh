@@ -1,0 +1,10 @@
+set -x
+cd $GRAFT_REPO_ROOT
+timeout 600 python -m pytest tests/test_gpu_parity.py tests/test_gpu_sweeps.py -q -k "ar_loglik or alternative or stateseqs or hmm or sweep" > gpurun_out/r02_pytest18.log 2>&1; tail -5 gpurun_out/r02_pytest18.log
+timeout 400 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/r02_bench_k_cfg4.json 2> gpurun_out/r02_bench_k_cfg4.err; echo "bench rc=$?"
+python - <<'P'
+import json
+for f in ('gpurun_out/r02_bench_k_cfg4.json',):
+    d=json.loads(open(f).read().strip().splitlines()[-1])
+    print(f, d['ms_per_step'], d['value']); print(d['breakdown_ms'])
+P
