@@ -554,7 +554,7 @@ def main():
                **{a: sh[a] for a in ("k", "dk", "D", "L", "K")}, "total_sessions": N * world,
                "cold_start": bool(args.cold_start),
                "chunk_fallbacks_timed": fallbacks_timed, "chunk_fallbacks_all": dict(G.FALLBACKS),
-               "hmm_burn_boost": G._HMM_ADAPT["boost"], "per_rank": per_rank,
+               "hmm_burn_boost": G._HMM_ADAPT["boost"], "kalman_burn_boost": G._LAT_ADAPT["boost"], "per_rank": per_rank,
                "l2": "per-step working set (filter workspace / ll / messages, GBs) far exceeds the 126 MB L2"}
         if slds:
             cfg.update(kalman_chunk_len=(G.auto_chunk_len(N, T, L, G.LATENTS_CHUNKING["burn_in"], dev)

@@ -124,17 +124,16 @@ def ar_log_likelihood(*, x, Ab, Q, impl=0, **kwargs):
 _HMM_ADAPT = {"boost": 1, "streak": 0, "need": 8, "probing": False}
 
 
-def _hmm_adapt_update(failed, comfortable):
-    """One verdict on a chunked HMM pass -> the warm-up multiplier of the next passes.
+def _adapt_update(A, failed, comfortable, max_boost):
+    """One verdict on a chunked pass -> the warm-up multiplier of the next passes.
     A failure doubles it.  After `need` consecutive comfortable passes (mismatch < 3 % of the tolerance)
     it is halved again, on probation: if the shorter warm-up then fails, `need` is quadrupled (cap 4096),
     so a model that needs the longer warm-up is re-probed ever more rarely instead of paying one
     repeated pass every `need` sweeps."""
-    A = _HMM_ADAPT
     if failed:
         if A["probing"]:
             A["need"] = min(A["need"] * 4, 4096)
-        A["boost"], A["streak"], A["probing"] = min(A["boost"] * 2, HMM_MAX_BOOST), 0, False
+        A["boost"], A["streak"], A["probing"] = min(A["boost"] * 2, max_boost), 0, False
     elif comfortable:
         A["streak"] += 1
         if A["probing"] and A["streak"] >= 8:
@@ -144,6 +143,24 @@ def _hmm_adapt_update(failed, comfortable):
             A["streak"], A["probing"] = 0, True
     else:
         A["streak"] = 0
+
+
+def _hmm_adapt_update(failed, comfortable):
+    _adapt_update(_HMM_ADAPT, failed, comfortable, HMM_MAX_BOOST)
+
+
+# the same book-keeping for the chunked Kalman filter / sampler (multiplies LATENTS_CHUNKING["burn_in"] when
+# the caller does not pass a warm-up of its own)
+_LAT_ADAPT = {"boost": 1, "streak": 0, "need": 8, "probing": False}
+LATENTS_MAX_BOOST = 16
+
+
+def note_latents_check(b):
+    """Book-keeping after a chunked Kalman pass with boundary mismatch `b` (NaN = failure)."""
+    tol = LATENTS_CHUNKING["tol"]
+    ok = b == b and b <= tol
+    _adapt_update(_LAT_ADAPT, not ok, ok and b <= 0.03 * tol, LATENTS_MAX_BOOST)
+    return ok
 HMM_MAX_BOOST = 16
 
 
@@ -292,7 +309,8 @@ def resample_latents(key, *, Y, mask, v, h, z, s, Cd, sigmasq, Ab, Q, Gamma=None
         w_last = dist.fill_normal((N, n), seed, dist.STREAM_X_LAST, dev, session_offset)
     global last_latents_boundary_err
     chunk_len = LATENTS_CHUNKING["chunk_len"] if chunk_len is None else chunk_len
-    burn_in = LATENTS_CHUNKING["burn_in"] if burn_in is None else burn_in
+    adaptive = burn_in is None       # default warm-up: lengthened for models that were seen to forget slowly
+    burn_in = LATENTS_CHUNKING["burn_in"] * _LAT_ADAPT["boost"] if adaptive else burn_in
     strict = LATENTS_CHUNKING["strict"] if strict is None else strict
     if chunk_len == "auto":
         chunk_len = auto_chunk_len(N, T, L, int(burn_in), dev)
@@ -310,7 +328,8 @@ def resample_latents(key, *, Y, mask, v, h, z, s, Cd, sigmasq, Ab, Q, Gamma=None
             ws.numel(), _lib.stream_ptr(dev)), "kpms_resample_latents")
 
     run(chunk_len, burn_in)
-    if chunk_len > 0 and strict and strict != "defer" and not latents_check_ok(berr):
+    if chunk_len > 0 and strict and strict != "defer" and not (
+            note_latents_check(float(berr.max())) if adaptive else latents_check_ok(berr)):
         # warm-up too short for this model: once more with four times the warm-up, then exactly
         # (one warp per session)
         FALLBACKS["latents"] += 1

@@ -88,10 +88,11 @@ def _affine_combine_rev(later, earlier):
     return Ge @ Gl, (Ge @ cl[..., None])[..., 0] + ce
 
 
-def kalman_sample_scan(ys, mask, zs, m0, S0, A, B, Q, C, D, Rs, w, w_last):
+def kalman_sample_scan(ys, mask, zs, m0, S0, A, B, Q, C, D, Rs, w, w_last, return_filter=False):
     """Batched over sessions.  ys (N,T',p), mask (N,T'-1), zs (N,T'-1) int, m0 (n), S0 (n,n),
     A (K,n,n), B (K,n), Q (K,n,n), C (p,n), D (p), Rs (N,T',p), w (N,T'-1,n), w_last (N,n); float64.
-    Returns xs (N,T',n) and the innovation-form marginal log-likelihood (N)."""
+    Returns xs (N,T',n) and the innovation-form marginal log-likelihood (N); with `return_filter`
+    the filtered moments as kalman_filter emits them instead of xs (masked steps: the carry)."""
     N, Tp, p = ys.shape
     n = m0.shape[0]
     o = dict(dtype=torch.float64, device=ys.device)
@@ -129,6 +130,8 @@ def kalman_sample_scan(ys, mask, zs, m0, S0, A, B, Q, C, D, Rs, w, w_last):
     a = torch.linalg.solve_triangular(Lv, r[..., None], upper=False)[..., 0]
     lls = -0.5 * (a * a).sum(-1) - torch.log(torch.diagonal(Lv, dim1=-2, dim2=-1)).sum(-1) - 0.5 * p * math.log(2 * math.pi)
     ll = (lls * upd.to(torch.float64)).sum(1)
+    if return_filter:
+        return (torch.where(upd[..., None], m_f, m_pred), torch.where(upd[..., None, None], S_f, S_pred)), ll
     # backward sampler (kalman.py:123-156)
     x_last = m_f[:, -1] + (torch.linalg.cholesky(S_f[:, -1]) @ w_last[..., None])[..., 0]
     Qinv = torch.linalg.inv(Q)
@@ -171,3 +174,43 @@ def resample_latents_scan(key, *, Y, mask, v, h, z, s, Cd, sigmasq, Ab, Q, Gamma
                                 f64(draws["w"]), f64(draws["w_last"]))
     x = torch.cat([xs[:, 0, :-D].reshape(-1, L - 1, D), xs[:, :, -D:]], dim=1)    # :22
     return (x, {"loglik": ll}) if return_info else x
+
+
+# ------------------------------------------------------------------ the reference's generic entry points
+def _one(t, dev):
+    return torch.as_tensor(t, device=dev).to(torch.float64)
+
+
+def kalman_filter(ys, mask, zs, m0, S0, A, B, Q, C, D, Rs):
+    """kalman.py:80-120 for ONE sequence of a generic switching LDS, by the associative scan:
+    returns (filtered_ms (T',n), filtered_Ss (T',n,n)); masked steps emit the carry."""
+    dev = torch.as_tensor(ys).device
+    a = [_one(t, dev) for t in (ys, mask, m0, S0, A, B, Q, C, D, Rs)]
+    ys, mask, m0, S0, A, B, Q, C, D, Rs = a
+    n = m0.shape[0]
+    z = torch.as_tensor(zs, device=dev)
+    w = torch.zeros((1, ys.shape[0] - 1, n), dtype=torch.float64, device=dev)
+    (ms, Ss), _ = kalman_sample_scan(ys[None], mask[None], z[None], m0, S0, A, B, Q, C, D, Rs[None], w,
+                                     w[:, 0], return_filter=True)
+    return ms[0], Ss[0]
+
+
+def kalman_sample(rng, ys, mask, zs, m0, S0, A, B, Q, C, D, Rs, draws=None):
+    """kalman.py:123-156 for ONE sequence: a sample of the states given the observations.  `rng`: int
+    seed / (seed, offset) / torch.Generator as everywhere in this package; `draws={'w','w_last'}`
+    injects the standard normals (T'-1, n) and (n)."""
+    from . import distributions as dist
+    dev = torch.as_tensor(ys).device
+    ys, mask, m0, S0, A, B, Q, C, D, Rs = [_one(t, dev) for t in (ys, mask, m0, S0, A, B, Q, C, D, Rs)]
+    n, Tp = m0.shape[0], ys.shape[0]
+    if draws is not None:
+        w, wl = _one(draws["w"], dev), _one(draws["w_last"], dev)
+    elif dev.type == "cuda":
+        seed = dist.seed_of(rng)
+        w = dist.fill_normal((1, Tp - 1, n), seed, dist.STREAM_X, dev, 0)[0].double()
+        wl = dist.fill_normal((1, n), seed, dist.STREAM_X_LAST, dev, 0)[0].double()
+    else:
+        raise ValueError("kalman_sample on CPU tensors needs injected draws")
+    xs, _ = kalman_sample_scan(ys[None], mask[None], torch.as_tensor(zs, device=dev)[None], m0, S0, A, B, Q, C, D,
+                               Rs[None], w[None], wl[None])
+    return xs[0]

@@ -179,6 +179,9 @@ def _verify_and_repair(checks, flags_dev, run_from, world, group=None, st=None):
     if flags_dev is not None:                    # verdicts of an earlier sweep, summed over the ranks
         _apply_verdicts(*host[o:o + _N_FLAGS])
     tolz, tolx = G.STATESEQ_CHUNKING["tol"], G.LATENTS_CHUNKING["tol"]
+    if xc is not None or world > 1:
+        # Kalman warm-up multiplier: moved by the GLOBAL mismatch, so every rank changes it at the same sweep
+        G.note_latents_check(gvals["x"])
     any_failed = ("z" in gvals and not gvals["z"] <= tolz) or ("x" in gvals and not gvals["x"] <= tolx)
     if any_failed and st is not None:
         st.pop(NEXT_PARAMS_KEY, None)

@@ -45,6 +45,7 @@ def long_problem():
 
 def _reset_adapt(G):
     G._HMM_ADAPT.update(boost=1, streak=0, need=8, probing=False)
+    G._LAT_ADAPT.update(boost=1, streak=0, need=8, probing=False)
     for a in list(G.FALLBACKS):
         G.FALLBACKS[a] = [] if isinstance(G.FALLBACKS[a], list) else 0
 
@@ -363,6 +364,7 @@ def test_gibbs_sweep_repairs_a_failed_chunk_check(G):
         G.LATENTS_CHUNKING.update(chunk_len=300, burn_in=2)       # hopeless warm-up: must be caught and redone
         st1, pr1 = parallel.gibbs_sweep((1, 1), dd, ss, pp, hp, Gamma=T_(Gm))
         assert G.FALLBACKS["latents"] >= 1
+        assert G._LAT_ADAPT["boost"] >= 2          # the next sweeps start from a longer warm-up
         for name in ('z', 'x', 'h', 'v', 's'):
             assert torch.equal(st0[name], st1[name]), name
     finally:

@@ -71,3 +71,28 @@ def test_chunked_cuda_kernels_against_the_scan(chunk_len, burn_in):
     assert float((x.double() - xs).abs().max()) < 2e-6 * scale
     ls, lc = info_s['loglik'].cpu().numpy(), info['loglik'].cpu().numpy()
     assert np.all(np.abs(ls - lc) <= 1e-9 * np.abs(ls)), (ls, lc)
+
+
+def test_generic_kalman_entry_points_equal_oracle():
+    """`keypoint_moseq.kalman.kalman_filter / kalman_sample` (one sequence, generic LDS) against the
+    oracle's restatement of kalman.py:80-156, with a masked stretch in the middle of the sequence."""
+    from keypoint_moseq.kalman import kalman_filter, kalman_sample
+    rng = np.random.default_rng(3)
+    Tp, n, p, K = 40, 5, 4, 3
+    A = 0.8 * np.eye(n)[None] + 0.1 * rng.standard_normal((K, n, n))
+    B = 0.1 * rng.standard_normal((K, n))
+    Q = np.stack([np.eye(n) * 0.3 + 0.05 * (lambda m: m @ m.T)(rng.standard_normal((n, n))) for _ in range(K)])
+    C, D = rng.standard_normal((p, n)), rng.standard_normal(p)
+    Rs = 0.5 + rng.random((Tp, p))
+    ys = rng.standard_normal((Tp, p))
+    zs = rng.integers(0, K, Tp - 1)
+    mask = np.ones(Tp - 1)
+    mask[17:23] = 0
+    m0, S0 = np.zeros(n), 10 * np.eye(n)
+    w, wl = rng.standard_normal((Tp - 1, n)), rng.standard_normal(n)
+    ms_o, Ss_o, _ = O.kalman_filter(ys, mask, zs, m0, S0, A, B, Q, C, D, Rs)
+    xs_o, _ = O.kalman_sample(ys, mask, zs, m0, S0, A, B, Q, C, D, Rs, w, wl)
+    ms, Ss = kalman_filter(ys, mask, zs, m0, S0, A, B, Q, C, D, Rs)
+    xs = kalman_sample(0, ys, mask, zs, m0, S0, A, B, Q, C, D, Rs, draws={'w': w, 'w_last': wl})
+    assert np.abs(ms.numpy() - ms_o).max() < 1e-10 and np.abs(Ss.numpy() - Ss_o).max() < 1e-10
+    assert np.abs(xs.numpy() - xs_o).max() < 1e-10
