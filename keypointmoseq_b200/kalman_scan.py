@@ -12,7 +12,7 @@ cuBLAS / cuSOLVER through torch (library kernels, like the MNIW draws), 2-3x the
 sequential step per level and 22 KB per element, which is why the n = 30 filter of the sweep stays
 chunked.
 
-Reference semantics reproduced (kalman.py:80-156, as restated in oracle/kpms_oracle.py): the carry
+Reference semantics reproduced (kalman.py:80-156): the carry
 is the PREDICTED moment; step t conditions on y_t and then predicts with z_t; masked steps leave
 the carry untouched and emit zeros; the final update is unconditional.
 
