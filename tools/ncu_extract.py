@@ -26,6 +26,11 @@ KEEP = {
     "dram_write_GB": "dram__bytes_write.sum",
     "dram_pct_of_peak": "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
     "sm_throughput_pct": "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+    "tensor_pipe_cycles_active_pct_of_elapsed": "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed",
+    "tf32_tensor_ops_pct_of_peak_elapsed": "sm__ops_path_tensor_src_tf32_dst_fp32.sum.pct_of_peak_sustained_elapsed",
+    "fp64_tensor_ops_pct_of_peak_elapsed": "sm__ops_path_tensor_src_fp64.sum.pct_of_peak_sustained_elapsed",
+    "utcmma_instructions": "smsp__sass_inst_executed_op_utcmma.sum",
+    "tmem_load_instructions": "smsp__sass_inst_executed_op_tmem_ldt.sum",
     "tensor_pipe_tc_pct_active": "sm__inst_executed_pipe_tc.avg.pct_of_peak_sustained_active",
     "tmem_pipe_pct_active": "sm__inst_executed_pipe_tmem.avg.pct_of_peak_sustained_active",
     "dmma_subpipe_pct_active": "sm__inst_executed_pipe_tensor_subpipe_dmma.avg.pct_of_peak_sustained_active",
@@ -79,7 +84,7 @@ with open(os.path.join(ROOT, "profiles", "r02_sweep_kernels_ncu.json"), "w") as 
 GB = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
 lat = {}
 for name, rec in out["kernels"].items():
-    if name.startswith(("kalman_obs_kernel", "kalman_forward_blk_kernel", "kalman_backward_kernel")):
+    if name.startswith(("kalman_obs", "kalman_forward_blk_kernel", "kalman_backward_kernel")):
         sr = GB[out["units"]["dram_read_GB"]]
         sw = GB[out["units"]["dram_write_GB"]]
         lat[name.split("<")[0]] = {"dram_read": rec["dram_read_GB"] * sr, "dram_write": rec["dram_write_GB"] * sw}
