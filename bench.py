@@ -67,8 +67,12 @@ def parse():
     ap.add_argument("--sessions-per-gpu", type=int, default=0, help="override the config's sessions per GPU")
     ap.add_argument("--frames", type=int, default=0, help="override the config's frames per session")
     ap.add_argument("--cold-start", action="store_true")
+    ap.add_argument("--settle", type=int, default=6,
+                    help="untimed sweeps before the warm-up sweeps, in which the adaptive chunk warm-up of the filters "
+                         "settles (a fit runs hundreds of sweeps; the timed region measures its steady state)")
     ap.add_argument("--chunk-len", default="auto", help="Kalman chunk length: auto, 0 (= one warp per session) or steps")
-    ap.add_argument("--burn-in", type=int, default=256, help="Kalman chunk warm-up steps")
+    ap.add_argument("--burn-in", type=int, default=0, help="Kalman chunk warm-up steps (0 = the package default)")
+    ap.add_argument("--hmm-burn-in", type=int, default=0, help="HMM chunk warm-up frames (0 = the package default)")
     ap.add_argument("--cpu-sessions", type=int, default=0, help="0 = one per host core (max 16)")
     ap.add_argument("--cpu-frames", type=int, default=0, help="0 = sized from --steps so that the run takes minutes")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -304,7 +308,10 @@ def main():
         td.init_process_group("nccl", device_id=dev)
     lib = _lib.load()
     G.LATENTS_CHUNKING["chunk_len"] = args.chunk_len if args.chunk_len == "auto" else int(args.chunk_len)
-    G.LATENTS_CHUNKING["burn_in"] = args.burn_in
+    if args.burn_in > 0:
+        G.LATENTS_CHUNKING["burn_in"] = args.burn_in
+    if args.hmm_burn_in > 0:
+        G.STATESEQ_CHUNKING["burn_in"] = args.hmm_burn_in
 
     sh = shape_of(args)
     slds = sh["model"] == "slds"
@@ -357,6 +364,10 @@ def main():
 
     # ---- device-resident arm
     ss, pp = s, p
+    if args.cold_start:
+        args.settle = 0                         # the cold regime IS the first sweeps
+    for i in range(args.settle):                # the adaptive warm-up multipliers settle (not timed)
+        ss, pp = sweep(1000 + i, d, ss, pp)
     for i in range(args.warmup):
         ss, pp = sweep(i, d, ss, pp)
     barrier()
@@ -552,7 +563,7 @@ def main():
     if rank == 0:
         cfg = {"workload": args.config, "model": sh["model"], "sessions_per_gpu": N, "frames": T,
                **{a: sh[a] for a in ("k", "dk", "D", "L", "K")}, "total_sessions": N * world,
-               "cold_start": bool(args.cold_start),
+               "cold_start": bool(args.cold_start), "settle_sweeps": args.settle,
                "chunk_fallbacks_timed": fallbacks_timed, "chunk_fallbacks_all": dict(G.FALLBACKS),
                "hmm_burn_boost": G._HMM_ADAPT["boost"], "kalman_burn_boost": G._LAT_ADAPT["boost"], "per_rank": per_rank,
                "l2": "per-step working set (filter workspace / ll / messages, GBs) far exceeds the 126 MB L2"}

@@ -51,7 +51,9 @@ def save_checkpoint(directory, iteration, states, params, history, rank=0, phase
     torch.save({"iteration": int(iteration), "phase": phase,
                 "states": {a: b.detach().cpu() for a, b in states.items() if torch.is_tensor(b)},
                 "params": {a: b.detach().cpu() for a, b in params.items()},
-                "history": history}, tmp)
+                "history": history,
+                # warm-up multipliers of the chunked passes: a resumed fit continues exactly where it stopped
+                "adapt": {"hmm": dict(G._HMM_ADAPT), "kalman": dict(G._LAT_ADAPT)}}, tmp)
     os.replace(tmp, path)     # a crash mid-write leaves the previous checkpoint intact
     return path
 
@@ -63,6 +65,9 @@ def load_checkpoint(directory, rank=0, device="cuda"):
     ck = torch.load(path, map_location="cpu", weights_only=False)
     ck["states"] = to_device(ck["states"], device)
     ck["params"] = to_device(ck["params"], device)
+    if "adapt" in ck:
+        G._HMM_ADAPT.update(ck["adapt"]["hmm"])
+        G._LAT_ADAPT.update(ck["adapt"]["kalman"])
     return ck
 
 

@@ -124,7 +124,7 @@ def ar_log_likelihood(*, x, Ab, Q, impl=0, **kwargs):
 _HMM_ADAPT = {"boost": 1, "streak": 0, "need": 8, "probing": False}
 
 
-def _adapt_update(A, failed, comfortable, max_boost):
+def _adapt_update(A, failed, comfortable, max_boost, min_boost=1):
     """One verdict on a chunked pass -> the warm-up multiplier of the next passes.
     A failure doubles it.  After `need` consecutive comfortable passes (mismatch < 3 % of the tolerance)
     it is halved again, on probation: if the shorter warm-up then fails, `need` is quadrupled (cap 4096),
@@ -133,13 +133,15 @@ def _adapt_update(A, failed, comfortable, max_boost):
     if failed:
         if A["probing"]:
             A["need"] = min(A["need"] * 4, 4096)
-        A["boost"], A["streak"], A["probing"] = min(A["boost"] * 2, max_boost), 0, False
+        dbl = A["boost"] * 2
+        A["boost"], A["streak"], A["probing"] = min(int(dbl) if dbl >= 1 else dbl, max_boost), 0, False
     elif comfortable:
         A["streak"] += 1
         if A["probing"] and A["streak"] >= 8:
             A["probing"] = False
-        if A["streak"] >= A["need"] and A["boost"] > 1:
-            A["boost"] //= 2
+        if A["streak"] >= A["need"] and A["boost"] > min_boost:
+            half = A["boost"] / 2
+            A["boost"] = int(half) if half >= 1 else half
             A["streak"], A["probing"] = 0, True
     else:
         A["streak"] = 0
@@ -151,15 +153,20 @@ def _hmm_adapt_update(failed, comfortable):
 
 # the same book-keeping for the chunked Kalman filter / sampler (multiplies LATENTS_CHUNKING["burn_in"] when
 # the caller does not pass a warm-up of its own)
-_LAT_ADAPT = {"boost": 1, "streak": 0, "need": 8, "probing": False}
+# The Kalman multiplier may also go BELOW one: the default warm-up (256 steps) is safe for every model
+# measured (mismatch at rounding level), half of it is enough where the observations are informative
+# (16 keypoints: 4e-14 at 128 steps) but not where they are few (8 keypoints: above the tolerance), so a
+# fit starts safe and tries the shorter warm-up after `need` comfortable sweeps.
+_LAT_ADAPT = {"boost": 1, "streak": 0, "need": 3, "probing": False}
 LATENTS_MAX_BOOST = 16
+LATENTS_MIN_BOOST = 0.5
 
 
 def note_latents_check(b):
     """Book-keeping after a chunked Kalman pass with boundary mismatch `b` (NaN = failure)."""
     tol = LATENTS_CHUNKING["tol"]
     ok = b == b and b <= tol
-    _adapt_update(_LAT_ADAPT, not ok, ok and b <= 0.03 * tol, LATENTS_MAX_BOOST)
+    _adapt_update(_LAT_ADAPT, not ok, ok and b <= 0.03 * tol, LATENTS_MAX_BOOST, LATENTS_MIN_BOOST)
     return ok
 HMM_MAX_BOOST = 16
 
@@ -310,7 +317,7 @@ def resample_latents(key, *, Y, mask, v, h, z, s, Cd, sigmasq, Ab, Q, Gamma=None
     global last_latents_boundary_err
     chunk_len = LATENTS_CHUNKING["chunk_len"] if chunk_len is None else chunk_len
     adaptive = burn_in is None       # default warm-up: lengthened for models that were seen to forget slowly
-    burn_in = LATENTS_CHUNKING["burn_in"] * _LAT_ADAPT["boost"] if adaptive else burn_in
+    burn_in = int(LATENTS_CHUNKING["burn_in"] * _LAT_ADAPT["boost"]) if adaptive else burn_in
     strict = LATENTS_CHUNKING["strict"] if strict is None else strict
     if chunk_len == "auto":
         chunk_len = auto_chunk_len(N, T, L, int(burn_in), dev)

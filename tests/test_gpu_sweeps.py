@@ -45,7 +45,7 @@ def long_problem():
 
 def _reset_adapt(G):
     G._HMM_ADAPT.update(boost=1, streak=0, need=8, probing=False)
-    G._LAT_ADAPT.update(boost=1, streak=0, need=8, probing=False)
+    G._LAT_ADAPT.update(boost=1, streak=0, need=3, probing=False)
     for a in list(G.FALLBACKS):
         G.FALLBACKS[a] = [] if isinstance(G.FALLBACKS[a], list) else 0
 

@@ -135,3 +135,26 @@ def test_shared_hmm_warmup_moves_identically_from_summed_verdicts():
     finally:
         G._HMM_ADAPT.clear()
         G._HMM_ADAPT.update(saved)
+
+
+def test_kalman_warmup_multiplier_probes_below_one_and_backs_off():
+    from keypointmoseq_b200 import gibbs as G
+    saved = dict(G._LAT_ADAPT)
+    tol = G.LATENTS_CHUNKING["tol"]
+    try:
+        G._LAT_ADAPT.update(boost=1, streak=0, need=3, probing=False)
+        for _ in range(3):
+            assert G.note_latents_check(1e-15)
+        assert G._LAT_ADAPT["boost"] == 0.5 and G._LAT_ADAPT["probing"]      # comfortable three times: try half
+        assert G.note_latents_check(0.02 * tol)                              # the shorter warm-up holds
+        for _ in range(20):
+            G.note_latents_check(1e-15)
+        assert G._LAT_ADAPT["boost"] == 0.5                                  # never below the floor
+        G._LAT_ADAPT.update(boost=0.5, streak=0, need=3, probing=True)
+        assert not G.note_latents_check(10 * tol)                            # the probe fails: back to 1, re-probe later
+        assert G._LAT_ADAPT["boost"] == 1 and G._LAT_ADAPT["need"] == 12
+        assert not G.note_latents_check(float("nan"))                        # NaN is a failure
+        assert G._LAT_ADAPT["boost"] == 2
+    finally:
+        G._LAT_ADAPT.clear()
+        G._LAT_ADAPT.update(saved)
