@@ -20,6 +20,10 @@
 #define TC_STATES 16   // states per weight tile
 #define TC_M 128       // frames per block (UMMA M)
 #define TC_THREADS 256 // thread = (frame row, half of the K chunks / half of the states)
+// pipelined kernel: threads per frame row (each builds 1/PARTS of the row's chunks and reads 1/PARTS of the states).
+// Two: with four (512 threads; possible when 4 states x D is a whole number of 8-column TMEM loads) the kernel was
+// measured slower, 2.86 vs 2.68 ms on the bench shard.
+#define TCP_PARTS_OF(DD) 2
 
 template <int DD, int LL>
 struct TC {
@@ -260,12 +264,13 @@ __global__ void __launch_bounds__(TC_THREADS)
 // loaded into registers before the epilogue, so its latency is covered as well.  Per block the CTA costs
 // max(MMA, epilogue + A build) instead of their sum.
 template <int DD, int LL>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(128 * TCP_PARTS_OF(DD), 1)
     ar_loglik_tc_pipe_kernel(const float* __restrict__ x, const unsigned char* __restrict__ tiles,
                              const float* __restrict__ cst, int N, int T, int K, int nstripes,
                              int tile_cl, int tile_nch, float* __restrict__ ll) {
   using C = TC<DD, LL>;
-  constexpr int NCH = (C::KC + 1) / 2;   // 16-byte chunks of a row built by one thread
+  constexpr int TCP_PARTS = TCP_PARTS_OF(DD), TCP_THREADS = 128 * TCP_PARTS;
+  constexpr int NCH = (C::KC + TCP_PARTS - 1) / TCP_PARTS;   // 16-byte chunks of a row built by one thread
   extern __shared__ __align__(1024) unsigned char smem[];
   unsigned char* sA = smem;                                   // [stage][hi | lo]
   unsigned char* sB_hi = sA + 4 * C::A_BYTES;
@@ -274,7 +279,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
   uint64_t* mbar = reinterpret_cast<uint64_t*>(s_cst + TC_STATES);   // two barriers, one per stage
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mbar + 2);
   const int tid = threadIdx.x, warp = tid >> 5;
-  const int row = tid & (TC_M - 1), half = tid >> 7;
+  const int row = tid & (TC_M - 1), half = tid >> 7;   // `half`: which of the TCP_PARTS threads of a row
   const int tile = blockIdx.x, stripe = blockIdx.y;
   const int k0 = tile * TC_STATES;
   const int Tm = T - LL;
@@ -284,7 +289,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
   {
     const uint4* src = reinterpret_cast<const uint4*>(tiles + (size_t)tile * 2 * C::B_BYTES);
     uint4* dst = reinterpret_cast<uint4*>(sB_hi);
-    for (int i = tid; i < 2 * C::B_BYTES / 16; i += TC_THREADS) dst[i] = src[i];
+    for (int i = tid; i < 2 * C::B_BYTES / 16; i += TCP_THREADS) dst[i] = src[i];
     if (tid < TC_STATES) s_cst[tid] = (k0 + tid < K) ? cst[k0 + tid] : 0.0f;
   }
   const uint32_t mbar_sa = (uint32_t)__cvta_generic_to_shared(mbar);
@@ -334,7 +339,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
     const bool live = locate(blk, g, xp);
 #pragma unroll
     for (int j = 0; j < NCH; j++) {
-      const int kc = 2 * j + half;
+      const int kc = TCP_PARTS * j + half;
       float4 v = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
       if (live && kc < C::KC) {
         if ((DD & 1) == 0 && kc * 4 + 3 < DD * LL + DD) {
@@ -359,7 +364,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
     unsigned char* ah = sA + (size_t)st * 2 * C::A_BYTES + (size_t)(row / 8) * C::SBO + (row % 8) * 16;
 #pragma unroll
     for (int j = 0; j < NCH; j++) {
-      const int kc = 2 * j + half;
+      const int kc = TCP_PARTS * j + half;
       if (kc >= C::KC) continue;
       const float v4[4] = {pre[j].x, pre[j].y, pre[j].z, pre[j].w};
       uint32_t hi[4], lo[4];
@@ -415,7 +420,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
     if (st) parity[1] ^= 1u; else parity[0] ^= 1u;
     TC_FENCE_AFTER();
     {
-      constexpr int HS = TC_STATES / 2, HC = HS * DD, W = (HC % 16 == 0) ? 16 : 8;
+      constexpr int HS = TC_STATES / TCP_PARTS, HC = HS * DD, W = (HC % 16 == 0) ? 16 : 8;
+      static_assert(HC % 8 == 0 && HS % 4 == 0, "a thread reads whole 8-column groups and writes whole float4s");
       long long g;
       const float* xp;
       const bool live = locate(blk, g, xp);
@@ -500,7 +506,7 @@ static int launch_tc(const float* x, const float* Wf, const float* cst, int N, i
       long long stp = 148 / ntiles;
       if (stp > nblk0) stp = nblk0;
       if (stp < 1) stp = 1;
-      kp<<<dim3(ntiles, (unsigned)stp), TC_THREADS, smp, st>>>(x, tiles, cst, N, T, K, (int)stp, tile_cl, tile_nch, ll);
+      kp<<<dim3(ntiles, (unsigned)stp), 128 * TCP_PARTS_OF(DD), smp, st>>>(x, tiles, cst, N, T, K, (int)stp, tile_cl, tile_nch, ll);
       return kpms_last_launch();
     }
   }
