@@ -67,6 +67,8 @@ def parse():
     ap.add_argument("--sessions-per-gpu", type=int, default=0, help="override the config's sessions per GPU")
     ap.add_argument("--frames", type=int, default=0, help="override the config's frames per session")
     ap.add_argument("--cold-start", action="store_true")
+    ap.add_argument("--e2e-groups", type=int, default=0,
+                    help="session groups of the host-driven sweep (gibbs_sweep_host(groups=)); 0 = its default (2, or 4 with more than 2 ranks)")
     ap.add_argument("--settle", type=int, default=6,
                     help="untimed sweeps before the warm-up sweeps, in which the adaptive chunk warm-up of the filters "
                          "settles (a fit runs hundreds of sweeps; the timed region measures its steady state)")
@@ -510,16 +512,22 @@ def main():
     e2e = e2e_res = None
     if not args.no_e2e:
         out_host = {a: torch.empty_like(b).pin_memory() for a, b in host_st.items() if (slds or a == "z")}
-        nbytes = lambda dct: sum(b.numel() * b.element_size() for b in dct.values())
+        out_alt = {a: torch.empty_like(b).pin_memory() for a, b in out_host.items()}
+        nbytes = lambda dct: sum(b.numel() * b.element_size() for a, b in dct.items() if not a.startswith("_"))
         h2d = nbytes(host) + nbytes(host_st)
         par_host = None
+        cur = {"in": host_st, "out": out_host, "spare": out_alt}
 
         def e2e_step(i, pp_, resident=None):
             nonlocal par_host
-            # public host-side API: uploads ordered by first use, downloads as states become final
+            # public host-side API: uploads ordered by first use, downloads as states become final.  The loop of a
+            # fit: every sweep is fed the host tensors the previous sweep wrote (two sets of pinned buffers, used
+            # alternately), so from the second sweep on the pose steps run session group by session group.
             if slds:
-                _, p_new, _ = parallel.gibbs_sweep_host((0, i), host, host_st, pp_, hyp, Gamma=Gm, session_offset=off,
-                                                        out=out_host, device=dev, resident=resident)
+                o, p_new, _ = parallel.gibbs_sweep_host((0, i), host, cur["in"], pp_, hyp, Gamma=Gm, session_offset=off,
+                                                        out=cur["out"], device=dev, resident=resident,
+                                                        groups=args.e2e_groups or None)
+                cur["in"], cur["out"], cur["spare"] = o, cur["spare"], cur["out"]
             else:
                 _, p_new, _ = parallel.arhmm_sweep_host((0, i), host, host_st, pp_, hyp, session_offset=off,
                                                         out=out_host, device=dev)
@@ -528,6 +536,9 @@ def main():
 
         def run_e2e(resident):
             pe = p
+            cur.update({"in": host_st, "out": out_host, "spare": out_alt})
+            for o_ in (out_host, out_alt):
+                o_.pop("_carry", None)
             for i in range(min(args.warmup, 2)):
                 pe = e2e_step(200 + i, pe, resident)
             barrier()
@@ -563,7 +574,7 @@ def main():
     if rank == 0:
         cfg = {"workload": args.config, "model": sh["model"], "sessions_per_gpu": N, "frames": T,
                **{a: sh[a] for a in ("k", "dk", "D", "L", "K")}, "total_sessions": N * world,
-               "cold_start": bool(args.cold_start), "settle_sweeps": args.settle,
+               "cold_start": bool(args.cold_start), "settle_sweeps": args.settle, "e2e_session_groups": args.e2e_groups or (2 if world <= 2 else 4),
                "chunk_fallbacks_timed": fallbacks_timed, "chunk_fallbacks_all": dict(G.FALLBACKS),
                "hmm_burn_boost": G._HMM_ADAPT["boost"], "kalman_burn_boost": G._LAT_ADAPT["boost"], "per_rank": per_rank,
                "l2": "per-step working set (filter workspace / ll / messages, GBs) far exceeds the 126 MB L2"}

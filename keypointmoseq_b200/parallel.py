@@ -250,8 +250,49 @@ def _draw_dynamics_params(key, data, st, pr, hyp, group, world, with_obs=None):
     return out, S_y, msum, flags_dev
 
 
+def _pose_steps_grouped(key, data, states, st, pr, hyp, Gamma, off, groups, checks, done, mark):
+    """Steps 5-8 of a sweep (latents, heading, location, scales) one session group at a time: a group
+    starts as soon as ITS data have arrived and its new states leave while the next group computes.
+    Per-session steps with draws keyed by the global session index: the grouping changes nothing but
+    the Kalman chunk layout (chosen per launch) and the summation order of the statistics."""
+    parts = {a: [] for a in ("x", "h", "v", "s")}
+    berrs, S_parts, m_parts = [], [], []
+    for lo, hi, wait_group in groups:
+        wait_group()
+        sl = lambda t: t[lo:hi]
+        kw = dict(Cd=pr["Cd"], sigmasq=pr["sigmasq"], Gamma=Gamma, session_offset=off + lo)
+        x_g, info = G.resample_latents(key, Y=sl(data["Y"]), mask=sl(data["mask"]), v=sl(states["v"]),
+                                       h=sl(states["h"]), z=sl(st["z"]), s=sl(states["s"]), Ab=pr["Ab"], Q=pr["Q"],
+                                       strict="defer", return_info=True, **kw)
+        if info["chunk_len"] > 0:
+            berrs.append(info["boundary_err"].reshape(-1)[:2].to(torch.float64))
+        done("x", x_g, lo, hi)
+        h_g = G.resample_heading(key, Y=sl(data["Y"]), v=sl(states["v"]), x=x_g, s=sl(states["s"]), **kw)
+        done("h", h_g, lo, hi)
+        v_g = G.resample_location(key, mask=sl(data["mask"]), Y=sl(data["Y"]), h=h_g, x=x_g, s=sl(states["s"]),
+                                  sigmasq_loc=hyp["sigmasq_loc"], **kw)
+        done("v", v_g, lo, hi)
+        s_g, (S_g, m_g) = G.resample_scales(key, x=x_g, v=v_g, h=h_g, Y=sl(data["Y"]), nu_s=hyp["nu_s"],
+                                            s_0=hyp["s_0"], mask=sl(data["mask"]), return_stats=True, **kw)
+        done("s", s_g, lo, hi)
+        for a, t in (("x", x_g), ("h", h_g), ("v", v_g), ("s", s_g)):
+            parts[a].append(t)
+        S_parts.append(S_g)
+        m_parts.append(m_g)
+    mark("x")
+    for a in parts:
+        st[a] = torch.cat(parts[a], dim=0)
+    checks["x"] = torch.stack(berrs).amax(0) if berrs else None
+    S_loc, m_loc = torch.stack(S_parts).sum(0), torch.stack(m_parts).sum(0)
+    st.pop(NEXT_PARAMS_KEY, None)
+    st[OBS_STATS_KEY] = {"S_y": S_loc, "msum": m_loc, "reduced": False, "S_local": S_loc, "m_local": m_loc,
+                         "tag": _obs_stats_tag(data, st, pr)}
+    mark("hvs")
+
+
 def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessions_global=None,
-                session_offset=None, next_key=None, _wait=None, _done=None, _mark=None):
+                session_offset=None, next_key=None, _wait=None, _done=None, _mark=None, _groups=None,
+                _obs_carry=None):
     """One full sweep.  `data`/`states` hold this rank's shard; `params` are replicated.
     Returns new (states, params) dicts; inputs are not mutated.
 
@@ -269,10 +310,18 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
     called before x, z and mask are first read, `_wait("all")` before Y, v, h and s are, and
     `_done` as soon as a state is final.  With hooks the observation-noise statistics are taken
     after the state sequences (they do not depend on z, so the sweep is unchanged) — by then
-    the large arrays have arrived."""
+    the large arrays have arrived.
+
+    `_groups` / `_obs_carry` (host driver only): the per-session steps after the state sequences —
+    latents, heading, location, scales — run session group by session group, `_groups` = [(lo, hi,
+    wait)] with `wait()` blocking the stream until that group's Y, v, h, s have arrived, and every
+    group's new states go back (`_done(name, tensor, lo, hi)`) while the next group computes.  That
+    needs the observation-noise statistics before any of the data has arrived: `_obs_carry` =
+    (S_y, mask sum), the statistics the previous sweep's scales pass left behind (already summed over
+    the ranks).  Draws are keyed by the global session index, so grouping does not change them."""
     rank, world = _world(group)
     wait = _wait or (lambda g: None)
-    done = _done or (lambda name, t: None)
+    done = _done or (lambda name, t, lo=None, hi=None: None)
     mark = _mark or (lambda label: None)
     defer_obs = _wait is not None
     st, pr = dict(states), dict(params)
@@ -328,14 +377,21 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
             done("z", z_new)
             mark("z")
             if defer_obs and "sigmasq_done" not in checks:
-                wait("all")
-                S_y, msum, reduced = obs_stats()     # uses the OLD x (st["x"]), exactly as step 2 of the sweep does
-                if world > 1 and not reduced:
-                    S_y, msum = all_reduce_obs_stats(S_y, msum, group)
+                if _obs_carry is not None:
+                    S_y, msum = _obs_carry            # left behind by the previous sweep, summed over the ranks
+                else:
+                    wait("all")
+                    S_y, msum, reduced = obs_stats()     # uses the OLD x (st["x"]), exactly as step 2 of the sweep does
+                    if world > 1 and not reduced:
+                        S_y, msum = all_reduce_obs_stats(S_y, msum, group)
                 pr["sigmasq"] = G.sample_obs_variance(key, S_y, msum, nu_sigma=hyp["nu_sigma"],
                                                       sigmasq_0=hyp["sigmasq_0"])
                 checks["sigmasq_done"] = None
             st["z"] = z_new
+        if _groups is not None and strict == "defer":
+            _pose_steps_grouped(key, data, states, st, pr, hyp, Gamma, off, _groups, checks, done, mark)
+            return
+        wait("all")
         st["x"], info = G.resample_latents(key, Y=data["Y"], mask=data["mask"], v=states["v"], h=states["h"],
                                            z=st["z"], s=states["s"], Cd=pr["Cd"], sigmasq=pr["sigmasq"],
                                            Ab=pr["Ab"], Q=pr["Q"], Gamma=Gamma, strict=strict,
@@ -419,9 +475,13 @@ def _copy_streams(dev):
     return _COPY_STREAMS[key]
 
 
+def _host_id(t):
+    return (t.data_ptr(), t._version, tuple(t.shape))
+
+
 def gibbs_sweep_host(key, host_data, host_states, params, hyp, Gamma=None, group=None,
                      n_sessions_global=None, session_offset=None, out=None, device=None, timeline=None,
-                     resident=None):
+                     resident=None, groups=None):
     """One sweep driven from HOST arrays (the drop-in situation: the caller keeps data and states
     in host memory, e.g. as NumPy / JAX-CPU arrays).
 
@@ -432,18 +492,48 @@ def gibbs_sweep_host(key, host_data, host_states, params, hyp, Gamma=None, group
     `out` (dict of pinned host tensors, allocated when None) receives z, x, h, v, s.
     `resident`: optional dict of DEVICE tensors (e.g. {'Y': ..., 'mask': ...}) that the caller keeps
     on the GPU across sweeps; those arrays are not uploaded again.
+
+    `groups` (default: 2 for one or two ranks, 4 when more ranks share the host — measured: one B200 65.3 /
+    57.7 / 59.4 / 61.5 ms per sweep with 1 / 2 / 3 / 4 groups, eight B200 135 / 101 / 93 ms with 1 / 2 / 4):
+    session-group pipelining.  When the states passed in are the very tensors the
+    previous call wrote (the loop of a fit: `host_states = out` of the last sweep, untouched — checked
+    by storage pointer and torch version counter, and agreed between the ranks), the observation-noise
+    statistics of those states are already known from that call, so nothing in the sweep needs ALL of
+    Y and s before it can start: the latents / heading / location / scales steps then run group by
+    group, each as soon as its part of Y, v, h, s has arrived, and each group's results travel back
+    while the next group computes.  Upload, compute and download overlap instead of following each
+    other, which is what matters when several ranks share the host's PCIe bandwidth.  The first
+    sweep of a loop (or any sweep whose states were modified) runs ungrouped.
     Returns (out, params_on_device, states_on_device); the host copies are complete on return."""
+    import torch.distributed as td
+    rank, world = _world(group)
+    if groups is None:
+        groups = 2 if world <= 2 else 4
     dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
     main = torch.cuda.current_stream(dev)
     cs_in, cs_out = _copy_streams(dev)
     resident = resident or {}
     hd = {a: torch.as_tensor(b) for a, b in host_data.items() if a not in resident}
-    hs = {a: torch.as_tensor(b) for a, b in host_states.items()}
+    hs = {a: torch.as_tensor(b) for a, b in host_states.items() if not a.startswith("_")}
+    N = hs["x"].shape[0]
+    # ---- may this sweep use what the previous one left behind?
+    carry = host_states.get("_carry") if isinstance(host_states, dict) else None
+    use = (groups > 1 and N >= 2 * groups and carry is not None and carry["world"] == world and
+           all(_host_id(hs[a]) == carry["ids"].get(a) for a in ("x", "v", "h", "s")) and
+           carry["Cd"] == _tensor_id(params["Cd"]) and
+           carry["data"] == tuple((a, torch.as_tensor(b).data_ptr()) for a, b in sorted(host_data.items())))
+    if world > 1:      # every rank takes the same path (the two paths issue different collectives)
+        flag = torch.tensor([1.0 if use else 0.0], device=dev)
+        td.all_reduce(flag, op=td.ReduceOp.MIN, group=group)
+        use = bool(flag.item() > 0)
+    bounds = [(g * N // groups, (g + 1) * N // groups) for g in range(groups)] if use else [(0, N)]
+
     dd = {a: torch.empty(b.shape, dtype=b.dtype, device=dev) for a, b in hd.items()}
     dd.update(resident)
     ds = {a: torch.empty(b.shape, dtype=b.dtype, device=dev) for a, b in hs.items()}
     cs_in.wait_stream(main)     # the fresh buffers may alias memory that queued kernels still use
     first = [("s", "x"), ("s", "z"), ("d", "mask")]
+    ev_groups = []
     with torch.cuda.stream(cs_in):
         for kind, a in first:
             if kind == "d" and a not in hd:
@@ -451,14 +541,17 @@ def gibbs_sweep_host(key, host_data, host_states, params, hyp, Gamma=None, group
             (ds if kind == "s" else dd)[a].copy_((hs if kind == "s" else hd)[a], non_blocking=True)
         ev_xz = torch.cuda.Event()
         ev_xz.record(cs_in)
-        for a in hd:
-            if ("d", a) not in first:
-                dd[a].copy_(hd[a], non_blocking=True)
-        for a in hs:
-            if ("s", a) not in first:
-                ds[a].copy_(hs[a], non_blocking=True)
-        ev_all = torch.cuda.Event()
-        ev_all.record(cs_in)
+        for lo, hi in bounds:                      # the rest, session group by session group
+            for a in hd:
+                if ("d", a) not in first:
+                    dd[a][lo:hi].copy_(hd[a][lo:hi], non_blocking=True)
+            for a in hs:
+                if ("s", a) not in first:
+                    ds[a][lo:hi].copy_(hs[a][lo:hi], non_blocking=True)
+            e = torch.cuda.Event()
+            e.record(cs_in)
+            ev_groups.append(e)
+        ev_all = ev_groups[-1]
     if out is None:
         out = {}
 
@@ -478,24 +571,43 @@ def gibbs_sweep_host(key, host_data, host_states, params, hyp, Gamma=None, group
         main.wait_event(ev_xz if (g == "xz" and os.environ.get("KPMS_E2E_NO_OVERLAP") != "1") else ev_all)
         mark("after_wait_" + g)
 
-    def done(name, t):
+    def done(name, t, lo=None, hi=None):
         if name not in out:
-            out[name] = torch.empty(t.shape, dtype=t.dtype).pin_memory()
+            out[name] = torch.empty((N,) + tuple(t.shape[1:]), dtype=t.dtype).pin_memory()
         mark("done_" + name)
         ev = torch.cuda.Event()
         ev.record(main)
         cs_out.wait_event(ev)
+        dst = out[name] if lo is None else out[name][lo:hi]
         with torch.cuda.stream(cs_out):
-            if out[name].dtype == t.dtype:
-                out[name].copy_(t, non_blocking=True)
+            if dst.dtype == t.dtype:
+                dst.copy_(t, non_blocking=True)
             else:
-                out[name].copy_(t.to(out[name].dtype), non_blocking=True)
+                dst.copy_(t.to(dst.dtype), non_blocking=True)
         t.record_stream(cs_out)
 
+    grp = None
+    if use:
+        grp = [(lo, hi, (lambda e=e: main.wait_event(e))) for (lo, hi), e in zip(bounds, ev_groups)]
     st, pr = gibbs_sweep(key, dd, ds, params, hyp, Gamma=Gamma, group=group,
                          n_sessions_global=n_sessions_global, session_offset=session_offset,
-                         _wait=wait, _done=done, _mark=mark)
+                         _wait=wait, _done=done, _mark=mark, _groups=grp,
+                         _obs_carry=(carry["S_y"], carry["msum"]) if use else None)
+    # ---- what the next sweep may reuse: the statistics of the states just produced, summed over the ranks
+    oc = st.get(OBS_STATS_KEY)
+    new_carry = None
+    if oc is not None:
+        S_y, msum = oc["S_local"], oc["m_local"]
+        if world > 1:
+            S_y, msum = all_reduce_obs_stats(S_y, msum, group)
+        new_carry = {"S_y": S_y, "msum": msum, "world": world, "Cd": _tensor_id(pr["Cd"]),
+                     "data": tuple((a, torch.as_tensor(b).data_ptr()) for a, b in sorted(host_data.items()))}
     cs_out.synchronize()
+    if new_carry is not None:
+        new_carry["ids"] = {a: _host_id(out[a]) for a in ("x", "v", "h", "s")}
+        out["_carry"] = new_carry
+    else:
+        out.pop("_carry", None)
     if timeline is not None:
         main.synchronize()
         for label, e in marks:

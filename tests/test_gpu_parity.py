@@ -450,6 +450,49 @@ def test_host_pipelined_sweep_equals_device_sweep(G):
     assert out2 is out and torch.equal(st1['x'].cpu(), out['x'])
 
 
+def test_host_sweep_session_groups(G):
+    """A loop of host sweeps that feeds every sweep the previous one's output tensors runs the pose
+    steps session group by session group (uploads, kernels and downloads overlapping).  Against the
+    ungrouped sweep from the same inputs: state sequences and parameters identical (the carried
+    observation statistics are bit-identical to recomputed ones), continuous states equal up to the
+    Kalman chunk layout, which is chosen per launch."""
+    import torch
+    from keypointmoseq_b200 import parallel
+    N, T, k, dk, D, L, K = 6, 1500, 8, 2, 10, 3, 10
+    d, s, p, Gm = H.problem(seed=78, N=N, T=T, k=k, dk=dk, D=D, L=L, K=K, ragged=True)
+    hpt = {a: (T_(b) if isinstance(b, np.ndarray) else b) for a, b in H.hyp(D, L, K).items()}
+    host_d = {a: torch.as_tensor(b, dtype=torch.float32).pin_memory() for a, b in d.items()}
+    host_s = {a: (torch.as_tensor(b, dtype=torch.float32) if a != 'z' else torch.as_tensor(b.astype(np.int32))).pin_memory()
+              for a, b in s.items()}
+    pr = {a: T_(b) for a, b in p.items()}
+    out1, pr1, _ = parallel.gibbs_sweep_host((3, 1), host_d, host_s, pr, hpt, Gamma=T_(Gm), groups=3)
+    assert "_carry" in out1                       # first sweep of the loop: ungrouped, leaves its statistics
+    # second sweep, twice from the same inputs: grouped (out1 passed back untouched) and ungrouped
+    outg, prg, stg = parallel.gibbs_sweep_host((3, 2), host_d, out1, pr1, hpt, Gamma=T_(Gm), groups=3)
+    plain = {a: b.clone().pin_memory() for a, b in out1.items() if not a.startswith("_")}
+    outp, prp, stp = parallel.gibbs_sweep_host((3, 2), host_d, plain, pr1, hpt, Gamma=T_(Gm), groups=3)
+    torch.cuda.synchronize()
+    assert torch.equal(outg['z'], outp['z'])
+    for name in prg:
+        assert torch.equal(prg[name], prp[name]), name
+    for name in ('x', 'h', 'v', 's'):
+        a, b = outg[name].double(), outp[name].double()
+        tol = 2e-6 * max(1.0, float(b.abs().max())) if name != 's' else 1e-5 * float(b.abs().max())
+        if name == 'h':                            # angles: compare on the circle
+            dlt = torch.remainder(a - b + np.pi, 2 * np.pi) - np.pi
+            assert float(dlt.abs().max()) < 1e-4, name
+        else:
+            assert float((a - b).abs().max()) < tol, (name, float((a - b).abs().max()))
+        assert torch.equal(stg[name].cpu(), outg[name]), name      # every group's part reached the host buffer
+    # a caller who changes a state in place gets the ungrouped path again (and correct results)
+    outg['v'].mul_(1.0)
+    out3, _, _ = parallel.gibbs_sweep_host((3, 3), host_d, outg, prg, hpt, Gamma=T_(Gm), groups=3)
+    ref3 = {a: b.clone().pin_memory() for a, b in outg.items() if not a.startswith("_")}
+    out4, _, _ = parallel.gibbs_sweep_host((3, 3), host_d, ref3, prg, hpt, Gamma=T_(Gm), groups=1)
+    for name in ('z', 'x', 'h', 'v', 's'):
+        assert torch.equal(out3[name], out4[name]), name
+
+
 def test_cpu_tensor_is_rejected(G):
     import torch
     from keypointmoseq_b200._lib import KpmsError

@@ -1,10 +1,9 @@
 set -x
 cd $GRAFT_REPO_ROOT
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1"
-timeout 900 $TR --master-port 29544 bench.py --gpus 8 --steps 5 --warmup 3 --no-breakdown > gpurun_out/r02_bench_f_8gpu.json 2> gpurun_out/r02_bench_f_8gpu.err; echo "bench8 rc=$?"; tail -3 gpurun_out/r02_bench_f_8gpu.err
-timeout 300 $TR --master-port 29545 tools/pcie_probe_ranks.py gpurun_out/r02_pcie_8ranks.json > gpurun_out/r02_pcie8.log 2>&1; tail -1 gpurun_out/r02_pcie8.log | cut -c1-600
+timeout 900 $TR --master-port 29544 bench.py --gpus 8 --steps 5 --warmup 3 --no-breakdown > gpurun_out/r02_final_cfg4_8gpu.json 2> gpurun_out/r02_final_cfg4_8gpu.err; echo "bench8 rc=$?"; tail -3 gpurun_out/r02_final_cfg4_8gpu.err
 python - <<'P'
 import json
-d=json.loads(open('gpurun_out/r02_bench_f_8gpu.json').read().strip().splitlines()[-1])
+d=json.loads(open('gpurun_out/r02_final_cfg4_8gpu.json').read().strip().splitlines()[-1])
 print(d['ms_per_step'], d['value'], d['e2e'], d['e2e_resident']); print(d['config']['per_rank']); print(d.get("breakdown_ms"))
 P
