@@ -124,18 +124,32 @@ def ar_log_likelihood(*, x, Ab, Q, impl=0, **kwargs):
 _HMM_ADAPT = {"boost": 1, "streak": 0, "need": 8, "probing": False}
 
 
+SPORADIC_GAP = 6
+
+
 def _adapt_update(A, failed, comfortable, max_boost, min_boost=1):
     """One verdict on a chunked pass -> the warm-up multiplier of the next passes.
-    A failure doubles it.  After `need` consecutive comfortable passes (mismatch < 3 % of the tolerance)
-    it is halved again, on probation: if the shorter warm-up then fails, `need` is quadrupled (cap 4096),
-    so a model that needs the longer warm-up is re-probed ever more rarely instead of paying one
-    repeated pass every `need` sweeps."""
+    A failed pass is always redone with twice the warm-up (by the caller).  The multiplier itself
+    doubles only when failures come close together (two within SPORADIC_GAP passes) or when a probe
+    of a shorter warm-up fails: a lone failure — one chunk boundary among thousands that needed
+    longer, as happens every few sweeps with K = 500 nearly identical states — costs its repeat and
+    nothing more.  After `need` consecutive comfortable passes (mismatch < 3 % of the tolerance) the
+    multiplier is halved again, on probation: if the shorter warm-up then fails, `need` is quadrupled
+    (cap 4096), so a model that needs the longer warm-up is re-probed ever more rarely."""
+    if A.get("frozen"):
+        return
     if failed:
+        recent = A.get("since_fail", 10 ** 9) < SPORADIC_GAP
+        A["since_fail"] = 0
         if A["probing"]:
             A["need"] = min(A["need"] * 4, 4096)
-        dbl = A["boost"] * 2
-        A["boost"], A["streak"], A["probing"] = min(int(dbl) if dbl >= 1 else dbl, max_boost), 0, False
-    elif comfortable:
+        if A["probing"] or recent:
+            dbl = A["boost"] * 2
+            A["boost"] = min(int(dbl) if dbl >= 1 else dbl, max_boost)
+        A["streak"], A["probing"] = 0, False
+        return
+    A["since_fail"] = A.get("since_fail", 10 ** 9) + 1
+    if comfortable:
         A["streak"] += 1
         if A["probing"] and A["streak"] >= 8:
             A["probing"] = False

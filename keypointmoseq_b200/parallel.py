@@ -202,17 +202,22 @@ def _verify_and_repair(checks, flags_dev, run_from, world, group=None, st=None):
         _HMM_SHARED["verdict"] = verdict
     else:
         _apply_verdicts(*verdict)
+    def redo(A, step, max_boost):
+        # the failed pass again, verified, with twice the warm-up (then the ladder of the step itself);
+        # the multiplier proper moves through the verdicts only, identically on every rank
+        saved = dict(A)
+        A.update(boost=min(saved["boost"] * 2, max_boost), frozen=True)
+        try:
+            run_from(step, True)
+        finally:
+            A.clear()
+            A.update(saved)
+
     if z_failed:
-        # redo the state sequences with verification on (longer warm-up, finally sequential) and
-        # everything that consumed them; the shared multiplier itself moves through _apply_verdicts
-        saved = dict(G._HMM_ADAPT)
-        G._HMM_ADAPT["boost"] = min(saved["boost"] * 2, G.HMM_MAX_BOOST) if world > 1 else saved["boost"]
-        run_from("z", True)
-        if world > 1:
-            G._HMM_ADAPT.update(saved)
+        redo(G._HMM_ADAPT, "z", G.HMM_MAX_BOOST)      # ... and everything that consumed the state sequences
     elif "x" in vals and not (vals["x"] <= tolx):
         G.FALLBACKS["latents"] += 1
-        run_from("x", True)
+        redo(G._LAT_ADAPT, "x", G.LATENTS_MAX_BOOST)
 
 
 OBS_STATS_KEY = "_obs_stats"   # entry of the states dict that carries next sweep's (S_y, mask sum)

@@ -53,6 +53,8 @@ def _fresh_warmup_adaptation(request):
         yield
         return
     from keypointmoseq_b200 import gibbs as G
+    G._HMM_ADAPT.clear()
     G._HMM_ADAPT.update(boost=1, streak=0, need=8, probing=False)
+    G._LAT_ADAPT.clear()
     G._LAT_ADAPT.update(boost=1, streak=0, need=3, probing=False)
     yield

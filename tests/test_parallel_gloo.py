@@ -105,9 +105,14 @@ def test_shared_hmm_warmup_moves_identically_from_summed_verdicts():
     only, so every rank changes it at the same sweep."""
     from keypointmoseq_b200 import gibbs as G, parallel
     saved = dict(G._HMM_ADAPT)
+    fresh = dict(boost=1, streak=0, need=8, probing=False)
     try:
-        G._HMM_ADAPT.update(boost=1, streak=0, need=8, probing=False)
-        parallel._apply_verdicts(1.0, 6.0, 8.0)          # one of eight ranks failed its check
+        G._HMM_ADAPT.clear()
+        G._HMM_ADAPT.update(fresh)
+        parallel._apply_verdicts(1.0, 6.0, 8.0)          # one of eight ranks failed its check: a lone failure,
+        assert G._HMM_ADAPT["boost"] == 1                # redone by that rank, the multiplier stays
+        parallel._apply_verdicts(0.0, 8.0, 8.0)
+        parallel._apply_verdicts(2.0, 6.0, 8.0)          # a second failure two sweeps later: systematic
         assert G._HMM_ADAPT["boost"] == 2 and G._HMM_ADAPT["streak"] == 0
         for _ in range(7):
             parallel._apply_verdicts(0.0, 8.0, 8.0)
@@ -117,10 +122,11 @@ def test_shared_hmm_warmup_moves_identically_from_summed_verdicts():
         for _ in range(8):
             parallel._apply_verdicts(0.0, 8.0, 8.0)
         assert G._HMM_ADAPT["boost"] == 1 and G._HMM_ADAPT["probing"]
+        before = dict(G._HMM_ADAPT)
         parallel._apply_verdicts(0.0, 0.0, 0.0)          # nothing reported (sequential passes): no change
-        assert G._HMM_ADAPT == {"boost": 1, "streak": 0, "need": 8, "probing": True}
+        assert G._HMM_ADAPT == before
         parallel._apply_verdicts(1.0, 0.0, 8.0)          # the shorter warm-up fails: probe less often from now on
-        assert G._HMM_ADAPT == {"boost": 2, "streak": 0, "need": 32, "probing": False}
+        assert (G._HMM_ADAPT["boost"], G._HMM_ADAPT["need"], G._HMM_ADAPT["probing"]) == (2, 32, False)
         for _ in range(31):
             parallel._apply_verdicts(0.0, 8.0, 8.0)
         assert G._HMM_ADAPT["boost"] == 2
@@ -132,6 +138,9 @@ def test_shared_hmm_warmup_moves_identically_from_summed_verdicts():
         for _ in range(10):
             parallel._apply_verdicts(3.0, 0.0, 8.0)
         assert G._HMM_ADAPT["boost"] == G.HMM_MAX_BOOST
+        G._HMM_ADAPT.update(frozen=True)                 # while a failed pass is being redone nothing moves
+        parallel._apply_verdicts(0.0, 8.0, 8.0)
+        assert G._HMM_ADAPT["streak"] == 0
     finally:
         G._HMM_ADAPT.clear()
         G._HMM_ADAPT.update(saved)
@@ -153,7 +162,7 @@ def test_kalman_warmup_multiplier_probes_below_one_and_backs_off():
         G._LAT_ADAPT.update(boost=0.5, streak=0, need=3, probing=True)
         assert not G.note_latents_check(10 * tol)                            # the probe fails: back to 1, re-probe later
         assert G._LAT_ADAPT["boost"] == 1 and G._LAT_ADAPT["need"] == 12
-        assert not G.note_latents_check(float("nan"))                        # NaN is a failure
+        assert not G.note_latents_check(float("nan"))                        # NaN is a failure, the second in a row
         assert G._LAT_ADAPT["boost"] == 2
     finally:
         G._LAT_ADAPT.clear()

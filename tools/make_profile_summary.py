@@ -48,16 +48,21 @@ ref = line("r02_bench_reference_arm.json")
 if ref:
     out += ["", "## reference arm (`bench.py --impl reference`, `r02_bench_reference_arm.json`)", "",
             "%.4g frames·sweeps/s on %s — %s" % (ref["value"], ref["cpu_baseline"]["sample"], ref["config"].get("note", ""))]
-d8 = line("r02_bench_cfg4_8gpu.json")
-if d8 and d4:
-    out += ["", "## 8 GPUs (cfg4 = 1000 sessions x 36k frames, `r02_bench_cfg4_8gpu.json`)", "",
-            "| | 1 GPU | 8 GPUs | efficiency |", "|---|---|---|---|",
-            "| device-resident frames·sweeps/s | %.4g | %.4g | %.3f |" % (d4["value"], d8["value"], d8["value"] / (8 * d4["value"])),
-            "| e2e (host buffers every sweep) | %.4g | %.4g | %.3f |" % (d4["e2e"]["value"], d8["e2e"]["value"],
-                                                                       d8["e2e"]["value"] / (8 * d4["e2e"]["value"])),
-            "| e2e, Y and mask resident | %.4g | %.4g | %.3f |" % (d4["e2e_resident"]["value"], d8["e2e_resident"]["value"],
-                                                                  d8["e2e_resident"]["value"] / (8 * d4["e2e_resident"]["value"])),
-            "", "(the 8-GPU line was taken a few commits before the final 1-GPU line; the device-side sweep was 50.98 ms per rank on all 8 ranks.)"]
+scale = {n: line("r02_bench_cfg4_%dgpu.json" % n) for n in (2, 4, 8)}
+if d4 and any(scale.values()):
+    out += ["", "## 1 / 2 / 4 / 8 GPUs, weak scaling (125 sessions x 36k frames per GPU; `r02_bench_cfg4_<N>gpu.json`)", "",
+            "| GPUs | ms / sweep | device-resident frames·sweeps/s | efficiency | e2e (host buffers every sweep) | efficiency | e2e, Y and mask resident | session groups |",
+            "|---|---|---|---|---|---|---|---|",
+            "| 1 | %.2f | %.4g | 1 | %.4g | 1 | %.4g | %s |" % (d4["ms_per_step"], d4["value"], d4["e2e"]["value"], d4["e2e_resident"]["value"],
+                                                              d4["config"].get("e2e_session_groups", 1))]
+    for n, dn in scale.items():
+        if dn is None:
+            continue
+        out.append("| %d | %.2f | %.4g | %.3f | %.4g | %.3f | %.4g | %s |" % (
+            n, dn["ms_per_step"], dn["value"], dn["value"] / (n * d4["value"]), dn["e2e"]["value"],
+            dn["e2e"]["value"] / (n * d4["e2e"]["value"]), dn["e2e_resident"]["value"], dn["config"].get("e2e_session_groups", 1)))
+    out += ["", "(the 2- and 4-GPU lines predate the session-group pipelining of the host-driven sweep, the 1- and 8-GPU lines include it; "
+            "`r02_e2e_groups.txt` has the 1 / 2 / 3 / 4 / 6-group comparison.)"]
 pc = os.path.join(P, "r02_pcie_8ranks.json")
 if os.path.exists(pc):
     pj = json.load(open(pc))
