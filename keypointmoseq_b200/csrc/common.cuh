@@ -29,6 +29,8 @@ struct KpmsOptions {
   int kalman_warps;  // warps per CTA of the blocked Kalman filter: 8, 12 (default) or 16
   int kalman_lockstep;  // blocked filter, bit mask: 1 = the warps of a CTA step together (no gain measured), 2 = L1 prefetch of the per-state tables; default 0
   int emission_pipe;    // 1 (default): software-pipelined emission kernel (two A stages, two TMEM accumulators); 0: one block at a time, two CTAs per SM
+  int hmm_repair_rounds;   // K > 128 forward filter: rounds of device-side re-filtering of mismatched chunks (default 4; 0 = off)
+  int hmm_repair_tol_ppm;  // ... and the mismatch (in 1e-6 of probability mass) above which a chunk is re-filtered (default 1000)
   int kalman_obs_mma;   // 1 (default): observation records by FP64 tensor cores when dk == 2 and k % 4 == 0; 0: thread-per-frame kernel
 };
 extern KpmsOptions kpms_opts;

@@ -37,7 +37,14 @@ struct HmmBigArgs {
   int* carry_out;
   int N, Tm, K, Kl, chunk_len, burn_in, nch;
   int bwd_burn;          // warm-up of the sampler's chunks (normally = burn_in)
+  // forward repair (see hmm_big_mark_kernel): rlist[0] = number of chunks to re-filter, rlist[1..] their
+  // unit ids n*nch + c; rmode = 1: the forward kernel processes exactly those, each from the carry its
+  // predecessor left behind (no warm-up)
+  int* rlist;
+  int rmode;
+  float rtol;
 };
+#define HB_RMAX 128      // chunks one repair round can take (4 CTAs)
 
 __global__ void hmm_big_prep_pi_kernel(const double* __restrict__ pi, int K, int KP, float* __restrict__ pf,
                                        float* __restrict__ pT) {
@@ -85,31 +92,44 @@ __global__ void __launch_bounds__(HB_NT, 1) hmm_big_forward_kernel(HmmBigArgs p)
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int sg = tid & 63, cg = tid >> 6, wpair = warp & 1;
   const int K = p.K, Tm = p.Tm, nch = p.nch;
+  const int rcount = p.rmode ? min(p.rlist[0], HB_RMAX) : 0;
+  if (p.rmode && (int)blockIdx.x * HB_CH >= rcount) return;   // nothing (left) to repair: the whole CTA leaves
   if (tid == 0) s_S = 0;
   __syncthreads();
   if (tid < HB_CH) {
-    const long long unit = (long long)blockIdx.x * HB_CH + tid;
+    long long unit = (long long)blockIdx.x * HB_CH + tid;
+    bool valid = unit < (long long)p.N * nch;
+    if (p.rmode) {
+      valid = unit < rcount;
+      unit = valid ? p.rlist[1 + unit] : 0;
+    }
     int n = 0, cc = 0, t0 = 0, tb = 0, tend = 0;
-    if (unit < (long long)p.N * nch) {
+    if (valid) {
       n = (int)(unit / nch);
       cc = (int)(unit % nch);
       t0 = cc * p.chunk_len;
       const int t1 = min(Tm, t0 + p.chunk_len);
       const int tvn = p.tv[n];
-      tb = (cc > 0) ? max(0, min(t0, tvn) - p.burn_in) : 0;
+      tb = (cc > 0) ? max(0, min(t0, tvn) - (p.rmode ? 0 : p.burn_in)) : 0;
       tend = min(t1, tvn);  // trailing padding: the chain stops at the first masked frame
     }
     s_info[tid][0] = n; s_info[tid][1] = cc; s_info[tid][2] = t0; s_info[tid][3] = tb; s_info[tid][4] = tend;
+    s_info[tid][5] = valid ? 1 : 0;
     atomicMax(&s_S, max(tend - tb, 0));
   }
   __syncthreads();
   const int S = s_S;
   int cn[8], ccc[8], ct0[8], ctb[8], cte[8];
+  bool cva[8];
 #pragma unroll
   for (int c = 0; c < 8; c++) {
     const int ch = cg * 8 + c;
     cn[c] = s_info[ch][0]; ccc[c] = s_info[ch][1]; ct0[c] = s_info[ch][2]; ctb[c] = s_info[ch][3]; cte[c] = s_info[ch][4];
+    cva[c] = s_info[ch][5] != 0;
   }
+  // chains of this thread's group that carry work: all eight in a normal pass; in a repair round the listed
+  // chunks fill the slots in order, so the first `nact` of the group are the live ones
+  const int nact = p.rmode ? max(0, min(8, rcount - ((int)blockIdx.x * HB_CH + cg * 8))) : 8;
   const unsigned pis_sa = (unsigned)__cvta_generic_to_shared(pi_s);
   auto issue_tile = [&](int g) {  // global tile counter g: tile (g % NTILE) into buffer (g & 1)
     const float* src = p.pf + (size_t)(g % NTILE) * HB_TK * KP;
@@ -146,6 +166,13 @@ __global__ void __launch_bounds__(HB_NT, 1) hmm_big_forward_kernel(HmmBigArgs p)
     logtot[c] = 0.0;
 #pragma unroll
     for (int q = 0; q < SN; q++) T[c][q] = (q * 64 + sg < K) ? 1.0f : 0.0f;
+    if (p.rmode && cva[c] && ccc[c] > 0) {
+      // repair: start from the (normalised) carry the predecessor chunk left behind
+      const float* pe = p.bnd + ((size_t)(cn[c] * nch + ccc[c] - 1) * 2 + 1) * p.Kl;
+      inv[c] = 1.0f;
+#pragma unroll
+      for (int q = 0; q < SN; q++) T[c][q] = (q * 64 + sg < K) ? pe[q * 64 + sg] : 0.0f;
+    }
   }
   load_ll(0, lln);
   issue_tile(0);
@@ -214,17 +241,30 @@ __global__ void __launch_bounds__(HB_NT, 1) hmm_big_forward_kernel(HmmBigArgs p)
       __syncthreads();
       issue_tile(g + 1);
       const float* pt = pi_s + (size_t)(g & 1) * HB_TK * KP;
+      if (nact > 2) {
 #pragma unroll
-      for (int ii = 0; ii < HB_TK; ii++) {
-        const float* ar = a_s + (size_t)(tile * HB_TK + ii) * HB_AS + cg * 8;
-        const float4 a0 = *reinterpret_cast<const float4*>(ar);
-        const float4 a1 = *reinterpret_cast<const float4*>(ar + 4);
-        const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+        for (int ii = 0; ii < HB_TK; ii++) {
+          const float* ar = a_s + (size_t)(tile * HB_TK + ii) * HB_AS + cg * 8;
+          const float4 a0 = *reinterpret_cast<const float4*>(ar);
+          const float4 a1 = *reinterpret_cast<const float4*>(ar + 4);
+          const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
 #pragma unroll
-        for (int q = 0; q < SN; q++) {
-          const float pv = pt[ii * KP + q * 64 + sg];
+          for (int q = 0; q < SN; q++) {
+            const float pv = pt[ii * KP + q * 64 + sg];
 #pragma unroll
-          for (int c = 0; c < 8; c++) T[c][q] = fmaf(av[c], pv, T[c][q]);
+            for (int c = 0; c < 8; c++) T[c][q] = fmaf(av[c], pv, T[c][q]);
+          }
+        }
+      } else if (nact > 0) {   // a repair round with one or two chunks in this group: an eighth / a quarter of the products
+#pragma unroll
+        for (int ii = 0; ii < HB_TK; ii++) {
+          const float2 a0 = *reinterpret_cast<const float2*>(a_s + (size_t)(tile * HB_TK + ii) * HB_AS + cg * 8);
+#pragma unroll
+          for (int q = 0; q < SN; q++) {
+            const float pv = pt[ii * KP + q * 64 + sg];
+            T[0][q] = fmaf(a0.x, pv, T[0][q]);
+            T[1][q] = fmaf(a0.y, pv, T[1][q]);
+          }
         }
       }
     }
@@ -246,8 +286,7 @@ __global__ void __launch_bounds__(HB_NT, 1) hmm_big_forward_kernel(HmmBigArgs p)
   asm volatile("cp.async.wait_group 0;\n" ::);
 #pragma unroll
   for (int c = 0; c < 8; c++) {
-    const long long unit = (long long)blockIdx.x * HB_CH + cg * 8 + c;
-    if (unit < (long long)p.N * nch && sg == 0) p.llpart[(size_t)cn[c] * nch + ccc[c]] = logtot[c];
+    if (cva[c] && sg == 0) p.llpart[(size_t)cn[c] * nch + ccc[c]] = logtot[c];
   }
 }
 
@@ -356,6 +395,35 @@ __global__ void __launch_bounds__(HBB_WARPS * 32) hmm_big_brepair_kernel(HmmBigA
   }
 }
 
+// Forward repair, step 1: list the chunks whose warmed-up start differs from the carry their predecessor
+// arrived with by more than rtol (a NaN counts).  One CTA per session.
+__global__ void hmm_big_mark_kernel(HmmBigArgs p) {
+  const int n = blockIdx.x, nch = p.nch;
+  const int tvn = p.tv[n];
+  __shared__ float red[4];
+  for (int c = 0; c + 1 < nch; c++) {
+    if ((c + 1) * p.chunk_len >= tvn) break;   // the next chunk starts inside the trailing padding
+    const float* a = p.bnd + ((size_t)(n * nch + c) * 2 + 1) * p.Kl;
+    const float* b = p.bnd + ((size_t)(n * nch + c + 1) * 2 + 0) * p.Kl;
+    float worst = 0.0f;
+    for (int e = threadIdx.x; e < p.K; e += blockDim.x) {
+      const float d = fabsf(a[e] - b[e]);
+      worst = (d != d) ? INFINITY : fmaxf(worst, d);
+    }
+    for (int o = 16; o > 0; o >>= 1) worst = fmaxf(worst, __shfl_xor_sync(0xffffffffu, worst, o));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = worst;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const float w = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
+      if (w > p.rtol) {
+        const int idx = atomicAdd(p.rlist, 1);
+        if (idx < HB_RMAX) p.rlist[1 + idx] = n * nch + c + 1;
+      }
+    }
+    __syncthreads();
+  }
+}
+
 template <int KP>
 static int launch_hmm_big(const HmmBigArgs& a, int* z, int forward_only, cudaStream_t st) {
   const size_t smem = ((size_t)KP * HB_AS + 2 * HB_TK * KP + HB_CH * 2) * sizeof(float);
@@ -364,7 +432,26 @@ static int launch_hmm_big(const HmmBigArgs& a, int* z, int forward_only, cudaStr
   const long long units = (long long)a.N * a.nch;
   kf<<<(unsigned)((units + HB_CH - 1) / HB_CH), HB_NT, smem, st>>>(a);
   int rc = kpms_last_launch();
-  if (rc || forward_only) return rc;
+  if (rc) return rc;
+  // Forward repair: a chunk whose warm-up did not reach the true carry (a numerically reducible chain: which of
+  // two similar states it sits in can depend on history further back than any warm-up) is filtered again from
+  // its predecessor's end.  Each round fixes the listed chunks; a chunk whose new end no longer matches its
+  // successor's start is listed in the next round.  No host round trip: a round with an empty list costs two
+  // empty launches.  What is still mismatched afterwards is reported through boundary_err as before.
+  if (a.nch > 1 && a.rlist != nullptr) {
+    HmmBigArgs r = a;
+    r.rmode = 1;
+    for (int round = 0; round < kpms_opts.hmm_repair_rounds; round++) {
+      KPMS_CUDA(cudaMemsetAsync(a.rlist, 0, sizeof(int), st));
+      hmm_big_mark_kernel<<<a.N, 128, 0, st>>>(a);
+      rc = kpms_last_launch();
+      if (rc) return rc;
+      kf<<<HB_RMAX / HB_CH, HB_NT, smem, st>>>(r);
+      rc = kpms_last_launch();
+      if (rc) return rc;
+    }
+  }
+  if (forward_only) return rc;
   hmm_big_backward_kernel<KP><<<(unsigned)((units + HBB_WARPS - 1) / HBB_WARPS), HBB_WARPS * 32, 0, st>>>(a, z);
   rc = kpms_last_launch();
   if (rc || a.nch == 1) return rc;
@@ -384,12 +471,13 @@ int kpms_hmm_big_kp(int K) { return K <= 256 ? 256 : 512; }
 int kpms_hmm_big(const float* ll, const float* mask, long long mask_stride, const double* pi, const float* u,
                  const int* tv, int N, int Tm, int K, int Kl, int chunk_len, int burn_in, int bwd_burn, int nch,
                  float* pf, float* pT, float* alphan, double* llpart, float* bnd, int* carry_warm, int* carry_out,
-                 int* z, int forward_only, cudaStream_t st) {
+                 int* z, int forward_only, int* repair_scratch, cudaStream_t st) {
   const int KP = kpms_hmm_big_kp(K);
   hmm_big_prep_pi_kernel<<<(KP * KP + 255) / 256, 256, 0, st>>>(pi, K, KP, pf, pT);
   int rc = kpms_last_launch();
   if (rc) return rc;
   HmmBigArgs a{ll, mask, mask_stride, pf, pT, u, tv, alphan, llpart, bnd, carry_warm, carry_out,
-               N, Tm, K, Kl, chunk_len, burn_in, nch, bwd_burn >= 0 ? bwd_burn : burn_in};
+               N, Tm, K, Kl, chunk_len, burn_in, nch, bwd_burn >= 0 ? bwd_burn : burn_in,
+               repair_scratch, 0, 1e-6f * (float)kpms_opts.hmm_repair_tol_ppm};
   return (KP == 256) ? launch_hmm_big<256>(a, z, forward_only, st) : launch_hmm_big<512>(a, z, forward_only, st);
 }

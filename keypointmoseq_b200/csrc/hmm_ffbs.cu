@@ -27,7 +27,7 @@ int kpms_hmm_big_kp(int K);
 int kpms_hmm_big(const float* ll, const float* mask, long long mask_stride, const double* pi, const float* u,
                  const int* tv, int N, int Tm, int K, int Kl, int chunk_len, int burn_in, int bwd_burn, int nch,
                  float* pf, float* pT, float* alphan, double* llpart, float* bnd, int* carry_warm, int* carry_out,
-                 int* z, int forward_only, cudaStream_t st);
+                 int* z, int forward_only, int* repair_scratch, cudaStream_t st);
 
 #define HMM_STAGE 16    // frames of ll / mask / u staged ahead by the forward pass
 #define HMM_BRING 128   // frames of stay bits / u / mask staged ahead by the backward sampler
@@ -677,7 +677,7 @@ int kpms_hmm_ffbs_impl(const float* ll, int ll_tiled, const float* mask, int64_t
     if (rc) return rc;
     rc = kpms_hmm_big(ll, mask, mask_stride, pi, u, ws.tv, N, Tm, K, ws.Kl, chunk_len, burn_in, kpms_opts.hmm_bwd_burn,
                       nch, ws.pf, ws.pT, ws.alphan, ws.llpart, ws.bnd, ws.carry_warm, ws.carry_out, z,
-                      kpms_opts.hmm_flags & 1, st);
+                      kpms_opts.hmm_flags & 1, (int*)ws.stay /* no stay words on this path: repair list */, st);
     if (rc) return rc;
     hmm_finish_kernel<<<N, 128, 0, st>>>(ws, nch, K, chunk_len, loglik, (unsigned*)boundary_err);
     return kpms_last_launch();

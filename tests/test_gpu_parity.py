@@ -111,7 +111,7 @@ def test_hmm_chunked_tensor_core_any_state_count(G, K):
 
 
 @pytest.mark.parametrize("K", [130, 200, 256, 500])
-def test_hmm_chunked_large_state_counts(G, K):
+def test_hmm_chunked_large_state_counts(G, options, K):
     """128 < K <= 512: chunk-parallel filter with 32 chains per CTA and transition tiles streamed from
     L2 (hmm_big.cu), sampler without stay bits; against the oracle and against the sequential
     K-generic kernel."""
@@ -127,7 +127,14 @@ def test_hmm_chunked_large_state_counts(G, K):
     assert (N_(z)[valid] == zo[valid]).mean() >= 0.999 and int(z.max()) < K
     assert np.all(N_(z)[~valid] == 0)
     assert float((z != z_seq)[torch.as_tensor(valid, device="cuda")].float().mean()) < 1e-3
-    # a warm-up that is too short shows up in the reported mismatch
+    # a warm-up that is too short is repaired on the device (chunks re-filtered from their predecessor's end;
+    # five chunks per session: a cascade of four rounds) ...
+    z_r, lg_r, rep = G.sample_hmm_stateseqs(chunk_len=300, burn_in=1, strict=False, **kw)
+    assert float(rep["boundary_err"]) < 1e-4
+    assert np.all(np.abs(N_(lg_r) - lo) <= 1e-5 * np.abs(lo))
+    assert float((z_r != z_seq)[torch.as_tensor(valid, device="cuda")].float().mean()) < 1e-3
+    # ... and shows up in the reported mismatch when the repair is switched off
+    options("hmm_repair_rounds", 0)
     _, _, bad = G.sample_hmm_stateseqs(chunk_len=300, burn_in=1, strict=False, **kw)
     assert float(bad["boundary_err"]) > 1e-3
 
@@ -625,6 +632,24 @@ def test_hmm_backward_chunks_are_repaired(G, options):
     zo, lo = O._hmm_batch(ll, mask, pi, u)
     valid = mask > 0
     assert (N_(z_rep)[valid] == zo[valid]).mean() >= 0.999
+
+
+def test_hmm_forward_chunks_are_repaired_large_K(G, options):
+    """K > 128: a chunk whose warmed-up start does not match the carry of its predecessor is filtered
+    again on the device from that carry (one round per chunk of a cascade; four chunks per session here, so three rounds).  With a hopeless
+    warm-up of 2 frames every boundary fails; after the repair the chunked pass equals the sequential one."""
+    import torch
+    ll, mask, pi, u = _hmm_case(41, N=2, T=1200, K=200, ragged=True)
+    kw = dict(ll=T_(ll), mask=T_(mask), pi=T_(pi), u=T_(u), return_info=True)
+    z0, l0, _ = G.sample_hmm_stateseqs(chunk_len=0, **kw)
+    z1, l1, i1 = G.sample_hmm_stateseqs(chunk_len=300, burn_in=2, strict=False, **kw)
+    torch.cuda.synchronize()
+    assert float(i1['boundary_err']) < 1e-6
+    assert float((z0 != z1).float().mean()) < 1e-3
+    assert np.all(np.abs(N_(l0) - N_(l1)) <= 1e-5 * np.abs(N_(l0)))
+    options("hmm_repair_rounds", 0)
+    _, _, i2 = G.sample_hmm_stateseqs(chunk_len=300, burn_in=2, strict=False, **kw)
+    assert float(i2['boundary_err']) > 1e-3          # without the repair the mismatch is there and is reported
 
 
 def test_alternative_kernel_paths_agree(G, options):
