@@ -14,7 +14,7 @@ static int env_int(const char* name, int dflt) {
 }
 KpmsOptions kpms_opts = {env_int("KPMS_KALMAN_IMPL", 2), env_int("KPMS_HMM_TC", 1), env_int("KPMS_HMM_BWD_BURN", -1),
                          env_int("KPMS_LL_TILED", 0), env_int("KPMS_HMM_FLAGS", 0), env_int("KPMS_LOCATION_IMPL", 0), env_int("KPMS_KALMAN_WARPS", 12),
-                         env_int("KPMS_KALMAN_LOCKSTEP", 0), env_int("KPMS_EMISSION_PIPE", 1), env_int("KPMS_HMM_REPAIR_ROUNDS", 4), env_int("KPMS_HMM_REPAIR_TOL_PPM", 1000),
+                         env_int("KPMS_KALMAN_LOCKSTEP", 0), env_int("KPMS_EMISSION_PIPE", 1), env_int("KPMS_HMM_REPAIR_ROUNDS", 4), env_int("KPMS_HMM_REPAIR_TOL_PPM", 1000), env_int("KPMS_HMM_LL_ROWMAJOR", 0),
                          env_int("KPMS_KALMAN_OBS_MMA", 1)};
 
 static int* option_slot(const char* name) {
@@ -31,6 +31,7 @@ static int* option_slot(const char* name) {
   if (!strcmp(name, "emission_pipe")) return &kpms_opts.emission_pipe;
   if (!strcmp(name, "hmm_repair_rounds")) return &kpms_opts.hmm_repair_rounds;
   if (!strcmp(name, "hmm_repair_tol_ppm")) return &kpms_opts.hmm_repair_tol_ppm;
+  if (!strcmp(name, "hmm_ll_rowmajor")) return &kpms_opts.hmm_ll_rowmajor;
   return nullptr;
 }
 extern "C" int kpms_set_option(const char* name, int value) {

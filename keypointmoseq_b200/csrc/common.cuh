@@ -31,6 +31,7 @@ struct KpmsOptions {
   int emission_pipe;    // 1 (default): software-pipelined emission kernel (two A stages, two TMEM accumulators); 0: one block at a time, two CTAs per SM
   int hmm_repair_rounds;   // K > 128 forward filter: rounds of device-side re-filtering of mismatched chunks (default 4; 0 = off)
   int hmm_repair_tol_ppm;  // ... and the mismatch (in 1e-6 of probability mass) above which a chunk is re-filtered (default 1000)
+  int hmm_ll_rowmajor;     // K <= 104 filter: 1 = read a row-major ll in place when K % 4 == 0 instead of re-tiling it first
   int kalman_obs_mma;   // 1 (default): observation records by FP64 tensor cores when dk == 2 and k % 4 == 0; 0: thread-per-frame kernel
 };
 extern KpmsOptions kpms_opts;

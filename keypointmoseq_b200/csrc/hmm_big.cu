@@ -20,6 +20,8 @@
 #define HB_CH 32
 #define HB_TK 16
 #define HB_NT 256
+#define HB_RING 4  // transition-table tiles in shared memory: three in flight while one is read (a repair round with one
+                   // live chain is a pure stream of the table: its rate is the depth of this ring over the L2 latency)
 #define HB_AS 36  // row stride (floats) of the state-major message buffer: 144 B keeps 16-byte stores conflict-free
 
 struct HmmBigArgs {
@@ -85,8 +87,8 @@ __global__ void __launch_bounds__(HB_NT, 1) hmm_big_forward_kernel(HmmBigArgs p)
   constexpr int NTILE = KP / HB_TK;  // pi tiles per frame
   extern __shared__ __align__(16) float smf[];
   float* a_s = smf;                          // [KP][HB_AS]: a_s[i*HB_AS + chain]
-  float* pi_s = a_s + (size_t)KP * HB_AS;    // 2 x [HB_TK][KP]
-  float* red = pi_s + 2 * HB_TK * KP;        // [HB_CH][2]
+  float* pi_s = a_s + (size_t)KP * HB_AS;    // HB_RING x [HB_TK][KP]
+  float* red = pi_s + HB_RING * HB_TK * KP;  // [HB_CH][2]
   __shared__ int s_info[HB_CH][6];           // n, cc, t0, tb, tend, -
   __shared__ int s_S;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -131,9 +133,9 @@ __global__ void __launch_bounds__(HB_NT, 1) hmm_big_forward_kernel(HmmBigArgs p)
   // chunks fill the slots in order, so the first `nact` of the group are the live ones
   const int nact = p.rmode ? max(0, min(8, rcount - ((int)blockIdx.x * HB_CH + cg * 8))) : 8;
   const unsigned pis_sa = (unsigned)__cvta_generic_to_shared(pi_s);
-  auto issue_tile = [&](int g) {  // global tile counter g: tile (g % NTILE) into buffer (g & 1)
+  auto issue_tile = [&](int g) {  // global tile counter g: tile (g % NTILE) into buffer (g % HB_RING)
     const float* src = p.pf + (size_t)(g % NTILE) * HB_TK * KP;
-    const unsigned dst = pis_sa + (unsigned)((g & 1) * HB_TK * KP * 4);
+    const unsigned dst = pis_sa + (unsigned)((g % HB_RING) * HB_TK * KP * 4);
 #pragma unroll
     for (int e = 0; e < HB_TK * KP / 4 / HB_NT; e++) {
       const int piece = tid + e * HB_NT;
@@ -175,7 +177,8 @@ __global__ void __launch_bounds__(HB_NT, 1) hmm_big_forward_kernel(HmmBigArgs p)
     }
   }
   load_ll(0, lln);
-  issue_tile(0);
+#pragma unroll
+  for (int g0 = 0; g0 < HB_RING - 1; g0++) issue_tile(g0);   // HB_RING - 1 tiles in flight
   int g = 0;  // global tile counter
   for (int s = 0; s < S; s++) {
     // ---- message of frame tb + s:  a = in_pot * exp(ll - max ll),  norm = sum a + 1e-16
@@ -237,10 +240,10 @@ __global__ void __launch_bounds__(HB_NT, 1) hmm_big_forward_kernel(HmmBigArgs p)
       for (int q = 0; q < SN; q++) T[c][q] = 0.0f;
 #pragma unroll 1
     for (int tile = 0; tile < NTILE; tile++, g++) {
-      asm volatile("cp.async.wait_group 0;\n" ::);
+      asm volatile("cp.async.wait_group %0;\n" ::"n"(HB_RING - 2));   // tile g has landed (the newer ones may be on their way)
       __syncthreads();
-      issue_tile(g + 1);
-      const float* pt = pi_s + (size_t)(g & 1) * HB_TK * KP;
+      issue_tile(g + HB_RING - 1);   // into the buffer tile g-1 has just been read from
+      const float* pt = pi_s + (size_t)(g % HB_RING) * HB_TK * KP;
       if (nact > 2) {
 #pragma unroll
         for (int ii = 0; ii < HB_TK; ii++) {
@@ -426,7 +429,7 @@ __global__ void hmm_big_mark_kernel(HmmBigArgs p) {
 
 template <int KP>
 static int launch_hmm_big(const HmmBigArgs& a, int* z, int forward_only, cudaStream_t st) {
-  const size_t smem = ((size_t)KP * HB_AS + 2 * HB_TK * KP + HB_CH * 2) * sizeof(float);
+  const size_t smem = ((size_t)KP * HB_AS + HB_RING * HB_TK * KP + HB_CH * 2) * sizeof(float);
   auto kf = hmm_big_forward_kernel<KP>;
   KPMS_CUDA(cudaFuncSetAttribute(kf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const long long units = (long long)a.N * a.nch;

@@ -34,6 +34,7 @@ struct HmmTcArgs {
   int N, Tm, K, chunk_len, burn_in, nch;
   int Kt;  // true number of states; K is the layout width (Kt rounded up to a multiple of 4, padded
            // states carry ll = -inf and zero transition probability)
+  int ll_rowmajor;  // 1: `ll` is the caller's (N, Tm, K) row-major array, read in place (K % 4 == 0, 16-byte aligned)
 };
 
 template <int KD, int NP>
@@ -181,14 +182,17 @@ __global__ void __launch_bounds__(HTC_THREADS, 1) hmm_forward_tc_kernel(HmmTcArg
     const int tt = act ? t : 0;
     const int co = tt / p.chunk_len, ro = tt - co * p.chunk_len;
     const int uo = n * nch + co;
-    const float4* src = ll4 + ((size_t)(uo >> 7) * p.chunk_len + ro) * KC4f * 128 + (uo & 127);
+    // interleaved tiles: float4 piece kc of a frame at stride 128; row-major: consecutive
+    const float4* src = p.ll_rowmajor ? ll4 + ((size_t)n * Tm + tt) * KC4f
+                                      : ll4 + ((size_t)(uo >> 7) * p.chunk_len + ro) * KC4f * 128 + (uo & 127);
+    const size_t kstride = p.ll_rowmajor ? 1 : 128;
 #pragma unroll
     for (int i = 0; i < HG::MAXG; i++) {
       const int gi = part + 4 * i;
       const int c = 8 * gi;
       const float f = act ? -INFINITY : 0.0f;  // columns beyond K contribute exp(-inf) = 0
-      dst[i][0] = (act && c < K) ? __ldg(src + (size_t)(2 * gi) * 128) : make_float4(f, f, f, f);
-      dst[i][1] = (act && c + 4 < K) ? __ldg(src + (size_t)(2 * gi + 1) * 128) : make_float4(f, f, f, f);
+      dst[i][0] = (act && c < K) ? __ldg(src + (size_t)(2 * gi) * kstride) : make_float4(f, f, f, f);
+      dst[i][1] = (act && c + 4 < K) ? __ldg(src + (size_t)(2 * gi + 1) * kstride) : make_float4(f, f, f, f);
     }
   };
   auto row_max = [&](const float4 (&v)[HG::MAXG][2]) {
@@ -574,7 +578,9 @@ int kpms_hmm_forward_tc(const float* ll, int ll_tiled, float* ll_scratch, const 
   (void)mask; (void)mask_stride; (void)err_bits;  // the caller has run kpms_hmm_mask_check
   const int Kl = (K + 3) & ~3;
   if (ll_tiled && Kl != K) return KPMS_ERR_UNSUPPORTED;
-  if (!ll_tiled) {
+  // row-major ll can be read in place when its rows are whole float4s (no re-tiling pass, no second copy of ll)
+  const int rowmajor = !ll_tiled && Kl == K && kpms_aligned(ll, 16) && kpms_opts.hmm_ll_rowmajor;
+  if (!ll_tiled && !rowmajor) {
     const long long tiles = (((long long)N * nch + 127) / 128) * chunk_len;
     const size_t smem = (size_t)(Kl >> 2) * 129 * sizeof(float4);
     KPMS_CUDA(cudaFuncSetAttribute(hmm_ll_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -583,7 +589,7 @@ int kpms_hmm_forward_tc(const float* ll, int ll_tiled, float* ll_scratch, const 
     if (rc) return rc;
     ll = ll_scratch;
   }
-  HmmTcArgs a{ll, pi, u, tv, a_out, T_out, stay, llpart, bnd, N, Tm, Kl, chunk_len, burn_in, nch, K};
+  HmmTcArgs a{ll, pi, u, tv, a_out, T_out, stay, llpart, bnd, N, Tm, Kl, chunk_len, burn_in, nch, K, rowmajor};
   if (Kl <= 32) return launch_hmm_tc<32, 32>(a, st);
   if (Kl <= 64) return launch_hmm_tc<64, 64>(a, st);
   return launch_hmm_tc<104, 112>(a, st);
