@@ -336,7 +336,9 @@ def resample_latents(key, *, Y, mask, v, h, z, s, Cd, sigmasq, Ab, Q, Gamma=None
     if chunk_len == "auto":
         chunk_len = auto_chunk_len(N, T, L, int(burn_in), dev)
     x = torch.empty((N, T, D), dtype=torch.float32, device=dev)
-    loglik = torch.empty((N,), dtype=torch.float64, device=dev) if return_info else None
+    # return_info="check": the boundary mismatch only (a sweep has no use for the marginal log-likelihood,
+    # which costs the filter a product over the pivots and a float64 log per step)
+    loglik = torch.empty((N,), dtype=torch.float64, device=dev) if return_info is True else None
     berr = torch.zeros((2,), dtype=torch.float64, device=dev)
 
     def run(cl, bi):

@@ -268,7 +268,7 @@ def _pose_steps_grouped(key, data, states, st, pr, hyp, Gamma, off, groups, chec
         kw = dict(Cd=pr["Cd"], sigmasq=pr["sigmasq"], Gamma=Gamma, session_offset=off + lo)
         x_g, info = G.resample_latents(key, Y=sl(data["Y"]), mask=sl(data["mask"]), v=sl(states["v"]),
                                        h=sl(states["h"]), z=sl(st["z"]), s=sl(states["s"]), Ab=pr["Ab"], Q=pr["Q"],
-                                       strict="defer", return_info=True, **kw)
+                                       strict="defer", return_info="check", **kw)
         if info["chunk_len"] > 0:
             berrs.append(info["boundary_err"].reshape(-1)[:2].to(torch.float64))
         done("x", x_g, lo, hi)
@@ -400,7 +400,7 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
         st["x"], info = G.resample_latents(key, Y=data["Y"], mask=data["mask"], v=states["v"], h=states["h"],
                                            z=st["z"], s=states["s"], Cd=pr["Cd"], sigmasq=pr["sigmasq"],
                                            Ab=pr["Ab"], Q=pr["Q"], Gamma=Gamma, strict=strict,
-                                           session_offset=off, return_info=True)
+                                           session_offset=off, return_info="check")
         checks["x"] = info["boundary_err"] if (strict == "defer" and info["chunk_len"] > 0) else None
         done("x", st["x"])
         mark("x")
