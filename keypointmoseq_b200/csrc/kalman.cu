@@ -358,7 +358,7 @@ __global__ void __launch_bounds__(256)
     kalman_obs_mma_kernel(const float* __restrict__ Y, const float* __restrict__ v,
                           const float* __restrict__ h, const float* __restrict__ s,
                           const double* __restrict__ Cdfull, const double* __restrict__ sigmasq,
-                          int N, int T, int k, int Lg, double* __restrict__ obs) {
+                          int N, int T, int k, int Lg, int want_c, double* __restrict__ obs) {
   using Y_ = KL<NN, DD>;
   constexpr int NJ = Y_::NJ, NJB = (NJ + 7) / 8, NEB = (DD + 7) / 8;
   constexpr int NJP = 8 * NJB + 4;   // row strides (doubles) of the two tables: the four k rows of a B
@@ -439,7 +439,7 @@ __global__ void __launch_bounds__(256)
           qq = fma(y0, w0, qq);
           qq = fma(y1, w1, qq);
         }
-        if ((ks & 3) == 3) {   // fold the running product of R into a log before it can leave the double range
+        if (want_c && (ks & 3) == 3) {   // fold the running product of R into a log before it can leave the double range
           lr += log(pr);
           pr = 1.0;
         }
@@ -453,12 +453,16 @@ __global__ void __launch_bounds__(256)
           KO_DMMA(Ea[nb], w1, c0[CSP + 8 * nb]);
         }
       }
-      if (KS & 3) lr += log(pr);
-      // c = -1/2 sum_p [log(2 pi R_p) + (ytild_p - d_p)^2 / R_p], two coordinates per keypoint
-      double ct = -lr - 0.5 * qq;
-      ct += __shfl_xor_sync(FULL, ct, 1);
-      ct += __shfl_xor_sync(FULL, ct, 2);
-      ct -= (double)k * KPMS_LOG_2PI;
+      // c = -1/2 sum_p [log(2 pi R_p) + (ytild_p - d_p)^2 / R_p], two coordinates per keypoint; only the marginal
+      // log-likelihood reads it
+      double ct = 0.0;
+      if (want_c) {
+        if (KS & 3) lr += log(pr);
+        ct = -lr - 0.5 * qq;
+        ct += __shfl_xor_sync(FULL, ct, 1);
+        ct += __shfl_xor_sync(FULL, ct, 2);
+        ct -= (double)k * KPMS_LOG_2PI;
+      }
       if (act) {
         double* o = obs + (size_t)(g0 + src) * Y_::OBS_SIZE;
 #pragma unroll
@@ -1326,7 +1330,7 @@ static int launch_latents(const float* Y, const float* mask, const float* v, con
       const long long groups = (tot + 31) / 32;
       const long long want = (groups + 7) / 8;
       const unsigned grid = (unsigned)(want < 148LL * 8 ? (want > 0 ? want : 1) : 148LL * 8);
-      kern<<<grid, 256, smem, st>>>(Y, v, h, s, Cdfull, sigmasq, N, T, k, Lg, ws.obs);
+      kern<<<grid, 256, smem, st>>>(Y, v, h, s, Cdfull, sigmasq, N, T, k, Lg, loglik != nullptr, ws.obs);
     } else {
       const size_t smem = ((size_t)k * dk * (DD + 1) + (size_t)k * YL::NJ + k + 4 * 32 * (size_t)(YL::OBS_SIZE | 1)) * sizeof(double);
       auto kern = kalman_obs_kernel<NN, DD>;

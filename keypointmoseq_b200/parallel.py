@@ -347,7 +347,12 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
     flags_dev = None
     if (ahead is not None and ahead["key"] == key and ahead["world"] == world and
             ahead["tag"] == tuple(_tensor_id(t) for t in (states["x"], states["z"], data["mask"], params["betas"]))):
-        # steps 1 and 3 were drawn at the end of the previous sweep, from these very states
+        # steps 1 and 3 were drawn at the end of the previous sweep, from these very states (on a side stream)
+        if ahead.get("event") is not None:
+            cur = torch.cuda.current_stream(states["x"].device)
+            cur.wait_event(ahead["event"])
+            for t in list(ahead["params"].values()) + ([ahead["flags"]] if torch.is_tensor(ahead["flags"]) else []):
+                t.record_stream(cur)
         pr.update(ahead["params"])
         flags_dev = ahead["flags"]
         if not defer_obs:
@@ -408,8 +413,18 @@ def gibbs_sweep(key, data, states, params, hyp, Gamma=None, group=None, n_sessio
         if next_key is not None and not defer_obs and strict == "defer":
             # next sweep's steps 1 and 3 depend on the new z and x only: enqueue them now (not in a
             # repair pass, which runs on the failing ranks alone and must not issue collectives)
-            nxt, _, _, nflags = _draw_dynamics_params(next_key, data, st, pr, hyp, group, world, None)
-            st[NEXT_PARAMS_KEY] = {"key": next_key, "world": world, "params": nxt, "flags": nflags,
+            # ... on a side stream: ~60 small launches (statistics, all-reduce, K-sized draws) that run next to
+            # the frame-parallel pose kernels instead of between them
+            main = torch.cuda.current_stream(st["x"].device)
+            side = _side_stream(st["x"].device)
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                nxt, _, _, nflags = _draw_dynamics_params(next_key, data, st, pr, hyp, group, world, None)
+                ev_side = torch.cuda.Event()
+                ev_side.record(side)
+            for t in (st["x"], st["z"], data["mask"], pr["betas"]):
+                t.record_stream(side)
+            st[NEXT_PARAMS_KEY] = {"key": next_key, "world": world, "params": nxt, "flags": nflags, "event": ev_side,
                                    "tag": tuple(_tensor_id(t) for t in (st["x"], st["z"], data["mask"], pr["betas"]))}
             mark("ahead")
         st["h"] = G.resample_heading(key, Y=data["Y"], v=states["v"], x=st["x"], s=states["s"], Cd=pr["Cd"],
@@ -471,6 +486,15 @@ def arhmm_sweep(key, data, states, params, hyp, group=None, session_offset=None)
 
 
 _COPY_STREAMS = {}
+_SIDE_STREAMS = {}
+
+
+def _side_stream(dev):
+    key = (dev.type, dev.index)
+    if key not in _SIDE_STREAMS:
+        _SIDE_STREAMS[key] = torch.cuda.Stream(dev)
+    return _SIDE_STREAMS[key]
+
 
 
 def _copy_streams(dev):
