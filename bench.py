@@ -246,7 +246,7 @@ def run_reference(args, rank):
     line = {"impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus,
             "steps": len(times), "warmup": args.warmup, "ms_per_step": per * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": args.config, "model": sh["model"], "sessions": ns, "frames": fr, **shape,
+            "config": {"workload": args.config, "sweep": sh["model"], "sessions": ns, "frames": fr, **shape,
                        "extrapolated_from": {"sessions_per_gpu": sh["sessions"], "frames": sh["frames"],
                                              "why": "the metric is a per-frame rate and the sweep is linear in "
                                                     "sessions x frames; the full shard is hours per sweep on CPU"},
@@ -572,7 +572,7 @@ def main():
                    ns, fr, sh["model"], per)}
 
     if rank == 0:
-        cfg = {"workload": args.config, "model": sh["model"], "sessions_per_gpu": N, "frames": T,
+        cfg = {"workload": args.config, "sweep": sh["model"], "sessions_per_gpu": N, "frames": T,
                **{a: sh[a] for a in ("k", "dk", "D", "L", "K")}, "total_sessions": N * world,
                "cold_start": bool(args.cold_start), "settle_sweeps": args.settle, "e2e_session_groups": args.e2e_groups or (2 if world <= 2 else 4),
                "chunk_fallbacks_timed": fallbacks_timed, "chunk_fallbacks_all": dict(G.FALLBACKS),

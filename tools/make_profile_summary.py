@@ -16,7 +16,7 @@ def line(name):
 
 out = ["# Round 2 — measured on B200 (files in this directory; regenerate with tools/make_profile_summary.py)", ""]
 out += ["## bench.py lines, one B200 (`r02_bench_<config>.json`)", "",
-        "| config | model | sessions x frames | K | ms / sweep | frames·sweeps/s (device) | e2e (host buffers) | CPU oracle, 16 threads | e2e / CPU | chunk fallbacks (timed) |",
+        "| config | sweep | sessions x frames | K | ms / sweep | frames·sweeps/s (device) | e2e (host buffers) | CPU oracle, 16 threads | e2e / CPU | chunk fallbacks (timed) |",
         "|---|---|---|---|---|---|---|---|---|---|"]
 for c in ("cfg1", "cfg2", "cfg3", "cfg4-shard", "cfg4-shard_cold", "cfg5-K20", "cfg5-K100", "cfg5-K500"):
     d = line("r02_bench_%s.json" % c)
@@ -26,7 +26,7 @@ for c in ("cfg1", "cfg2", "cfg3", "cfg4-shard", "cfg4-shard_cold", "cfg5-K20", "
     e2e = (d.get("e2e") or {}).get("value")
     cpu = (d.get("cpu_baseline") or {}).get("value")
     out.append("| %s | %s | %d x %d | %d | %.2f | %.3g | %s | %s | %s | %s |" % (
-        c, cf["model"], cf["sessions_per_gpu"], cf["frames"], cf["K"], d["ms_per_step"], d["value"],
+        c, cf.get("sweep", cf.get("model")), cf["sessions_per_gpu"], cf["frames"], cf["K"], d["ms_per_step"], d["value"],
         "%.3g" % e2e if e2e else "-", "%.3g" % cpu if cpu else "-", "%.0fx" % (e2e / cpu) if e2e and cpu else "-",
         cf.get("chunk_fallbacks_timed")))
 d4 = line("r02_bench_cfg4-shard.json")
