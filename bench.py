@@ -584,7 +584,9 @@ def main():
                        kalman_burn_in=G.LATENTS_CHUNKING["burn_in"], kalman_boundary_err=boundary_err)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f64 (Kalman, statistics) / f32 (HMM messages, emission GEMM)",
+                "vs_baseline": None, "dtype": "f64",
+                "dtype_note": "f64: Kalman filter / sampler, all statistics and parameters; f32 storage of per-frame arrays; "
+                              "HMM messages f32, emission GEMM 3xTF32 with fp32 accumulate",
                 "data": "synthetic", "config": cfg, "clocks": clocks, "e2e": e2e, "e2e_resident": e2e_res,
                 "gpu_launches": launches, "roofline": roofline, "roofline_per_kernel": per_kernel,
                 "cpu_baseline": cpu, "breakdown_ms": bd, "sweep_timeline": timeline}
