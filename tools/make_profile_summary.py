@@ -61,8 +61,7 @@ if d4 and any(scale.values()):
         out.append("| %d | %.2f | %.4g | %.3f | %.4g | %.3f | %.4g | %s |" % (
             n, dn["ms_per_step"], dn["value"], dn["value"] / (n * d4["value"]), dn["e2e"]["value"],
             dn["e2e"]["value"] / (n * d4["e2e"]["value"]), dn["e2e_resident"]["value"], dn["config"].get("e2e_session_groups", 1)))
-    out += ["", "(the 2- and 4-GPU lines were taken a few commits before the 1- and 8-GPU lines, which include the last millisecond saved in the "
-            "Kalman filter; `r02_e2e_groups.txt` has the comparison of 1 / 2 / 3 / 4 / 6 session groups in the host-driven sweep.)"]
+    out += ["", "(`r02_e2e_groups.txt` has the comparison of 1 / 2 / 3 / 4 / 6 session groups in the host-driven sweep.)"]
 pc = os.path.join(P, "r02_pcie_8ranks.json")
 if os.path.exists(pc):
     pj = json.load(open(pc))
